@@ -1,0 +1,332 @@
+"""ctypes binding of libvo_b200.so (include/vo_b200.h) + a Python mirror of the reference's Matcher.
+
+This module is host-side plumbing only: every operator call goes through the C ABI into
+hand-written sm_100a kernels.  There is no Python/numpy/torch implementation of any operator here
+and no CPU fallback: if the library is missing or no B200 is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+P_MATCH_DTYPE = np.dtype([
+    ("u1p", "<f4"), ("v1p", "<f4"), ("i1p", "<i4"),
+    ("u2p", "<f4"), ("v2p", "<f4"), ("i2p", "<i4"),
+    ("u1c", "<f4"), ("v1c", "<f4"), ("i1c", "<i4"),
+    ("u2c", "<f4"), ("v2c", "<f4"), ("i2c", "<i4"),
+])  # == Matcher::p_match, /root/reference/src/matcher.h:89-104
+
+VO_OK, VO_ERR_INVALID, VO_ERR_UNSUPPORTED, VO_ERR_CUDA, VO_ERR_CAPACITY, VO_ERR_STATE = range(6)
+
+
+class VoError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"vo_b200 status {status}: {msg}")
+        self.status = status
+
+
+class VoConfig(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bin_w", C.c_int32), ("bin_h", C.c_int32),
+                ("nms_tau", C.c_int32), ("max_frames", C.c_int32), ("max_pairs", C.c_int32),
+                ("max_matches", C.c_int32), ("match_rows_per_cta", C.c_int32), ("reserved", C.c_int32 * 7)]
+
+
+class VoGeometry(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("pitch", C.c_int32), ("bin_w", C.c_int32),
+                ("bin_h", C.c_int32), ("u_bins", C.c_int32), ("v_bins", C.c_int32), ("bin_cap", C.c_int32),
+                ("col_cap", C.c_int32), ("bin_num", C.c_int32), ("max_frames", C.c_int32),
+                ("max_pairs", C.c_int32), ("max_matches", C.c_int32), ("reserved", C.c_int32 * 3)]
+
+
+# every symbol include/vo_b200.h declares (tests/test_abi.py checks the header against this list)
+EXPORTS = [
+    "vo_engine_create", "vo_engine_destroy", "vo_engine_geometry", "vo_engine_synchronize", "vo_last_error",
+    "vo_version", "vo_compute_features", "vo_matching", "vo_bucket_matches", "vo_push_back", "vo_match_features",
+    "vo_bucket_features", "vo_get_matches", "vo_num_matches", "vo_set_matches", "vo_dump_features",
+    "vo_batch_extract_host", "vo_batch_extract_device", "vo_batch_match", "vo_batch_counts",
+    "vo_batch_get_matches", "vo_batch_download_async", "vo_slot_dump_features", "vo_slot_feature_count",
+    "vo_launch_count", "vo_profile_enable", "vo_profile_read", "vo_host_alloc", "vo_host_free",
+]
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load libvo_b200.so (building it in-tree first if nvcc is available and sources are newer)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    try:
+        path = _build.build_library()
+    except Exception:
+        if not os.path.exists(path):
+            raise
+    lib = C.CDLL(path)
+    lib.vo_last_error.restype = C.c_char_p
+    lib.vo_version.restype = C.c_char_p
+    lib.vo_engine_destroy.restype = None
+    vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+    sigs = {
+        "vo_engine_create": [C.POINTER(VoConfig), i32, vp, C.POINTER(vp)],
+        "vo_engine_destroy": [vp],
+        "vo_engine_geometry": [vp, C.POINTER(VoGeometry)],
+        "vo_engine_synchronize": [vp],
+        "vo_compute_features": [vp, vp, i32, vp, vp, i32],
+        "vo_matching": [vp, vp, vp, vp, vp, i32, vp, i32, C.POINTER(i32)],
+        "vo_bucket_matches": [vp, vp, i32, i32, f32, f32, vp, i32, C.POINTER(i32)],
+        "vo_push_back": [vp, vp, vp, C.POINTER(i32), i32],
+        "vo_match_features": [vp, i32],
+        "vo_bucket_features": [vp, i32, f32, f32],
+        "vo_get_matches": [vp, vp, i32, C.POINTER(i32)],
+        "vo_num_matches": [vp, C.POINTER(i32)],
+        "vo_set_matches": [vp, vp, i32],
+        "vo_dump_features": [vp, i32, vp, vp, i32],
+        "vo_batch_extract_host": [vp, i32, i32, vp, i64, i32],
+        "vo_batch_extract_device": [vp, i32, i32, vp, i64, i32],
+        "vo_batch_match": [vp, i32, vp, vp, i32, f32, f32],
+        "vo_batch_counts": [vp, i32, vp, vp],
+        "vo_batch_get_matches": [vp, i32, i32, vp, i32, C.POINTER(i32)],
+        "vo_batch_download_async": [vp, i32, i32, vp, vp, i64, i32],
+        "vo_slot_dump_features": [vp, i32, vp, vp, i32],
+        "vo_slot_feature_count": [vp, i32, C.POINTER(i32)],
+        "vo_launch_count": [vp, C.POINTER(i64)],
+        "vo_profile_enable": [vp, i32],
+        "vo_profile_read": [vp, C.POINTER(C.c_double), C.POINTER(i64), i32],
+        "vo_host_alloc": [C.POINTER(vp), i64],
+        "vo_host_free": [vp],
+    }
+    for name, args in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        if name != "vo_engine_destroy":
+            fn.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))
+
+
+class Engine:
+    """One vo_engine: frame slots + pair buffers on one GPU, one CUDA stream."""
+
+    def __init__(self, width: int, height: int, max_frames: int = 2, max_pairs: int = 1, device: int = 0,
+                 stream: int | None = None, max_matches: int = 0, match_rows_per_cta: int = 0, nms_tau: int = 0,
+                 bin_w: int = 0, bin_h: int = 0):
+        self.lib = load_library()
+        cfg = VoConfig(width=width, height=height, bin_w=bin_w, bin_h=bin_h, nms_tau=nms_tau,
+                       max_frames=max_frames, max_pairs=max_pairs, max_matches=max_matches,
+                       match_rows_per_cta=match_rows_per_cta)
+        h = C.c_void_p()
+        self.h = None
+        self._check(self.lib.vo_engine_create(C.byref(cfg), device, C.c_void_p(stream or 0), C.byref(h)))
+        self.h = h
+        g = VoGeometry()
+        self._check(self.lib.vo_engine_geometry(self.h, C.byref(g)))
+        self.geom = g
+        self.W, self.H, self.U, self.V = g.width, g.height, g.u_bins, g.v_bins
+        self.CAP, self.BIN_NUM, self.max_matches = g.bin_cap, g.bin_num, g.max_matches
+
+    def _check(self, st: int):
+        if st != VO_OK:
+            raise VoError(st, self.lib.vo_last_error().decode())
+
+    def close(self):
+        if self.h:
+            self.lib.vo_engine_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self._check(self.lib.vo_engine_synchronize(self.h))
+
+    # ---- operator level ------------------------------------------------------------------
+    def new_feature_arrays(self, cap_stride: int | None = None):
+        cap = cap_stride or self.CAP
+        return (np.zeros((self.V, self.U, 4, cap, 12), np.int32), np.zeros((self.V, self.U, 4), np.int32))
+
+    def compute_features(self, img: np.ndarray, cap_stride: int | None = None):
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        max2, num = self.new_feature_arrays(cap_stride)
+        self._check(self.lib.vo_compute_features(self.h, _ptr(img), img.strides[0], _ptr(max2), _ptr(num),
+                                                 max2.shape[3]))
+        return max2, num
+
+    def matching(self, m1p, n1p, m1c, n1c, cap: int | None = None):
+        cap = cap or self.max_matches
+        out = np.zeros(cap, P_MATCH_DTYPE)
+        n = C.c_int32(0)
+        assert m1p.shape == m1c.shape
+        self._check(self.lib.vo_matching(self.h, _ptr(m1p), _ptr(n1p), _ptr(m1c), _ptr(n1c), m1p.shape[3],
+                                         _ptr(out), cap, C.byref(n)))
+        return out[: n.value].copy()
+
+    def bucket_matches(self, matches: np.ndarray, max_features=2, bw=50.0, bh=50.0):
+        matches = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)
+        out = np.zeros(max(len(matches), 1), P_MATCH_DTYPE)
+        n = C.c_int32(0)
+        self._check(self.lib.vo_bucket_matches(self.h, _ptr(matches) if len(matches) else None, len(matches),
+                                               max_features, bw, bh, _ptr(out), len(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    # ---- Matcher level -------------------------------------------------------------------
+    def push_back(self, img: np.ndarray, replace: bool = False, img2=None):
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        dims = (C.c_int32 * 3)(img.shape[1], img.shape[0], img.strides[0])
+        self._check(self.lib.vo_push_back(self.h, _ptr(img), _ptr(img2), dims, int(replace)))
+
+    def match_features(self, method: int = 0):
+        self._check(self.lib.vo_match_features(self.h, method))
+
+    def bucket_features(self, max_features=2, bw=50.0, bh=50.0):
+        self._check(self.lib.vo_bucket_features(self.h, max_features, bw, bh))
+
+    def num_matches(self) -> int:
+        n = C.c_int32(0)
+        self._check(self.lib.vo_num_matches(self.h, C.byref(n)))
+        return n.value
+
+    def get_matches(self) -> np.ndarray:
+        out = np.zeros(self.max_matches, P_MATCH_DTYPE)
+        n = C.c_int32(0)
+        self._check(self.lib.vo_get_matches(self.h, _ptr(out), len(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    def set_matches(self, matches: np.ndarray):
+        matches = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)
+        self._check(self.lib.vo_set_matches(self.h, _ptr(matches) if len(matches) else None, len(matches)))
+
+    def dump_features(self, which: int, cap_stride: int | None = None):
+        max2, num = self.new_feature_arrays(cap_stride)
+        self._check(self.lib.vo_dump_features(self.h, which, _ptr(max2), _ptr(num), max2.shape[3]))
+        return max2, num
+
+    # ---- batch level ---------------------------------------------------------------------
+    def batch_extract_host(self, first_slot: int, frames, n: int | None = None, frame_stride: int | None = None,
+                           pitch: int | None = None):
+        """frames: (n,H,W) uint8 ndarray, or a raw host address with n/frame_stride/pitch given."""
+        if isinstance(frames, np.ndarray):
+            assert frames.dtype == np.uint8 and frames.ndim == 3 and frames.strides[2] == 1
+            n, frame_stride, pitch = frames.shape[0], frames.strides[0], frames.strides[1]
+        self._check(self.lib.vo_batch_extract_host(self.h, first_slot, n, _ptr(frames), frame_stride, pitch))
+
+    def batch_extract_device(self, first_slot: int, d_ptr: int, n: int, frame_stride: int, pitch: int):
+        self._check(self.lib.vo_batch_extract_device(self.h, first_slot, n, C.c_void_p(d_ptr), frame_stride, pitch))
+
+    def batch_match(self, prev_slots, curr_slots, max_features=0, bw=50.0, bh=50.0):
+        pv = np.ascontiguousarray(prev_slots, dtype=np.int32)
+        cu = np.ascontiguousarray(curr_slots, dtype=np.int32)
+        self._check(self.lib.vo_batch_match(self.h, len(pv), _ptr(pv), _ptr(cu), max_features, bw, bh))
+
+    def batch_counts(self, n_pairs: int):
+        raw = np.zeros(n_pairs, np.int32)
+        bk = np.zeros(n_pairs, np.int32)
+        self._check(self.lib.vo_batch_counts(self.h, n_pairs, _ptr(raw), _ptr(bk)))
+        return raw, bk
+
+    def batch_get_matches(self, pair: int, which: int = 0):
+        out = np.zeros(self.max_matches, P_MATCH_DTYPE)
+        n = C.c_int32(0)
+        self._check(self.lib.vo_batch_get_matches(self.h, pair, which, _ptr(out), len(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    def batch_download_async(self, n_pairs: int, which: int, counts, out, stride_matches: int, max_per_pair: int):
+        self._check(self.lib.vo_batch_download_async(self.h, n_pairs, which, _ptr(counts), _ptr(out), stride_matches,
+                                                     max_per_pair))
+
+    def slot_dump_features(self, slot: int, cap_stride: int | None = None):
+        max2, num = self.new_feature_arrays(cap_stride)
+        self._check(self.lib.vo_slot_dump_features(self.h, slot, _ptr(max2), _ptr(num), max2.shape[3]))
+        return max2, num
+
+    def slot_feature_count(self, slot: int) -> int:
+        n = C.c_int32(0)
+        self._check(self.lib.vo_slot_feature_count(self.h, slot, C.byref(n)))
+        return n.value
+
+    # ---- instrumentation -----------------------------------------------------------------
+    def launch_count(self) -> int:
+        n = C.c_int64(0)
+        self._check(self.lib.vo_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    def profile_enable(self, on: bool = True):
+        self._check(self.lib.vo_profile_enable(self.h, int(on)))
+
+    def profile_read(self, reset: bool = True):
+        ms = (C.c_double * 4)()
+        calls = (C.c_int64 * 4)()
+        self._check(self.lib.vo_profile_read(self.h, ms, calls, int(reset)))
+        names = ("extract", "match", "emit", "bucket")
+        return {k: (ms[i], calls[i]) for i, k in enumerate(names)}
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """numpy array backed by page-locked host memory from vo_host_alloc (never freed: bench lifetime)."""
+    lib = load_library()
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    p = C.c_void_p()
+    st = lib.vo_host_alloc(C.byref(p), max(n, 1))
+    if st != VO_OK:
+        raise VoError(st, lib.vo_last_error().decode())
+    buf = (C.c_uint8 * max(n, 1)).from_address(p.value)
+    return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+
+class Matcher:
+    """Python mirror of the reference's Matcher facade (/root/reference/src/matcher.h:40-143): same
+    method names, argument meaning and error behaviour; every call is a C-ABI call."""
+
+    class parameters:  # /root/reference/src/matcher.h:45-72 (dead on the reference's executed path)
+        def __init__(self):
+            self.nms_n = 2
+            self.nms_tau = 50
+            self.match_binsize = 50
+            self.match_radius = 200
+            self.match_disp_tolerance = 2
+            self.outlier_disp_tolerance = 5
+            self.outlier_flow_tolerance = 5
+            self.multi_stage = 0
+            self.half_resolution = 0
+            self.refinement = 0
+            self.f = self.cu = self.cv = self.base = 0.0
+
+    def __init__(self, width: int, height: int, param: "Matcher.parameters | None" = None, device: int = 0):
+        self.param = param or Matcher.parameters()
+        self.engine = Engine(width, height, device=device)
+
+    def setIntrinsics(self, f, cu, cv, base):
+        self.param.f, self.param.cu, self.param.cv, self.param.base = f, cu, cv, base
+
+    def pushBack(self, I1, dims=None, replace=False, I2=None):
+        I1 = np.ascontiguousarray(I1, dtype=np.uint8)
+        if dims is not None and (dims[0] <= 0 or dims[1] <= 0 or dims[2] < dims[0]):
+            import sys
+            print("ERROR: Image dimension mismatch!", file=sys.stderr)  # src/matcher.cpp:59-62: message, return
+            return
+        self.engine.push_back(I1, replace)
+
+    def matchFeatures(self, method=0, Tr_delta=None):
+        self.engine.match_features(method)
+
+    def bucketFeatures(self, max_features, bucket_width, bucket_height):
+        self.engine.bucket_features(max_features, bucket_width, bucket_height)
+
+    def getMatches(self):
+        return self.engine.get_matches()

@@ -1,0 +1,80 @@
+"""In-tree build of libvo_b200.so (hand-written CUDA for sm_100a + the C ABI of include/vo_b200.h)
+and of the C++ host shim (host/libvo_host.so: drop-in Matcher / VisualOdometryMono classes).
+
+nvcc cross-compiles without a GPU, so this runs on the CPU build box; the resulting .so files are
+git-ignored but travel to the GPU box with the repository snapshot.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_PKG)
+CSRC = os.path.join(_PKG, "csrc")
+HOST = os.path.join(_PKG, "host")
+LIB = os.path.join(_PKG, "libvo_b200.so")
+HOST_LIB = os.path.join(_PKG, "libvo_host.so")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall",
+]
+
+
+def _nvcc() -> str:
+    for cand in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def _sources(d: str, exts) -> list[str]:
+    return sorted(os.path.join(d, f) for f in os.listdir(d) if f.endswith(exts))
+
+
+def _stale(target: str, deps: list[str]) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    srcs = _sources(CSRC, (".cu",))
+    deps = srcs + _sources(CSRC, (".cuh",)) + [os.path.join(_ROOT, "include", "vo_b200.h")]
+    if force or _stale(LIB, deps):
+        cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", LIB, *srcs]
+        if verbose:
+            cmd.insert(1, "-Xptxas")
+            cmd.insert(2, "-v")
+        subprocess.check_call(cmd)
+    return LIB
+
+
+def build_host(force: bool = False) -> str | None:
+    if not os.path.isdir(HOST):
+        return None
+    srcs = _sources(HOST, (".cpp",))
+    if not srcs:
+        return None
+    deps = srcs + _sources(HOST, (".h",)) + [LIB]
+    if force or _stale(HOST_LIB, deps):
+        subprocess.check_call([
+            "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-I", os.path.join(_ROOT, "include"),
+            "-o", HOST_LIB, *srcs, "-L", _PKG, "-lvo_b200", "-Wl,-rpath,$ORIGIN",
+        ])
+    return HOST_LIB
+
+
+def build_all(force: bool = False) -> None:
+    build_library(force)
+    build_host(force)
+
+
+if __name__ == "__main__":
+    import sys
+    build_library(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    build_host(force="--force" in sys.argv)
+    print(LIB)

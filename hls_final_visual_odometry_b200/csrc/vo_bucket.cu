@@ -1,0 +1,176 @@
+// K4: match bucketing (sm_100a).
+//
+// Replaces, bit-exactly, Matcher::bucketFeatures + random_shuffle + rand_number
+// (src/matcher.cpp:113-187; FPGA: second half of removeOutliers,
+// hls_opencl/kernel/remove_outliers.cpp:104-182).
+//
+// The reference distributes the matches into 2-D buckets in input order, Fisher-Yates-shuffles
+// every bucket with one LFSR stream that starts at 5 and carries across buckets, and keeps the
+// first max_features of each.  The LFSR stream is input independent, so it is a precomputed table
+// (built with the bit model of the reference's x86 double->int behaviour);
+// bucket b consumes entries [S_b, S_b + len_b - 1) with S_b = sum over earlier buckets of
+// max(len-1, 0).  Nothing is physically shuffled: for each kept output slot the swap sequence is
+// traced BACKWARDS to the bucket-local rank of the match that ends up there, and a stable
+// segmented rank (32 ordered segments, warp match_any inside) tells every match its own rank.
+#include "vo_common.cuh"
+
+namespace vo {
+
+constexpr int K4_THREADS = 1024;
+constexpr int K4_WARPS = K4_THREADS / 32;
+
+// per-pair scratch layout (int32 units): hist[nb_max][32] | cnt[nb_max] | soff[nb_max+1] | ooff[nb_max+1] | q[q_cap]
+__host__ __device__ inline int64_t k4_scratch_ints(int nb_max, int q_cap) {
+  return (int64_t)nb_max * 32 + nb_max + 2 * (int64_t)(nb_max + 1) + q_cap;
+}
+
+__device__ __forceinline__ float block_max(float v, float* red) {
+  for (int d = 16; d > 0; d >>= 1) v = fmaxf(v, __shfl_xor_sync(0xFFFFFFFFu, v, d));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = red[0];
+  for (int w = 1; w < K4_WARPS; w++) r = fmaxf(r, red[w]);
+  __syncthreads();
+  return r;
+}
+
+// in: lists of 48-byte p_match records (3 x uint4), u1c/v1c are words 6/7
+__global__ void __launch_bounds__(K4_THREADS)
+k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t* __restrict__ n_in,
+          int32_t max_features, float bucket_w, float bucket_h, const uint32_t* __restrict__ lfsr, int32_t lfsr_len,
+          int32_t* __restrict__ scratch, int64_t scratch_stride, int32_t nb_max, int32_t q_cap,
+          uint4* __restrict__ out, int64_t out_stride_matches, int32_t out_cap, int32_t* __restrict__ n_out,
+          int32_t* __restrict__ status) {
+  __shared__ float red[K4_WARPS];
+  __shared__ int32_t s_carry[2];
+  __shared__ int32_t s_scan[K4_WARPS][2];
+  const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = n_in[pair];
+  const uint4* src = in + (int64_t)pair * in_stride_matches * 3;
+  uint4* dst = out + (int64_t)pair * out_stride_matches * 3;
+  int32_t* hist = scratch + (int64_t)pair * scratch_stride;
+  int32_t* cnt = hist + (int64_t)nb_max * 32;
+  int32_t* soff = cnt + nb_max;
+  int32_t* ooff = soff + nb_max + 1;
+  int32_t* q = ooff + nb_max + 1;
+
+  // ---- extent of the current-image coordinates (src/matcher.cpp:143-152) -------------------
+  float um = 0.f, vm = 0.f;
+  for (int i = tid; i < n; i += K4_THREADS) {
+    const uint4 w1 = src[(int64_t)i * 3 + 1];
+    um = fmaxf(um, __uint_as_float(w1.z));
+    vm = fmaxf(vm, __uint_as_float(w1.w));
+  }
+  um = block_max(um, red);
+  vm = block_max(vm, red);
+  const int cols = (int)floorf(__fdiv_rn(um, bucket_w)) + 1;
+  const int rows = (int)floorf(__fdiv_rn(vm, bucket_h)) + 1;
+  const int nb = cols * rows;
+  const int keep = max(max_features, 1);  // the refill loop always takes one (src/matcher.cpp:178-184)
+  if (nb > nb_max || n > lfsr_len || nb <= 0) {
+    if (tid == 0) { n_out[pair] = 0; atomicExch(status, 2); }
+    return;
+  }
+
+  // ---- pass 1: histogram per (bucket, ordered segment) --------------------------------------
+  for (int i = tid; i < nb * 32; i += K4_THREADS) hist[i] = 0;
+  __syncthreads();
+  const int seg_len = (n + K4_WARPS - 1) / K4_WARPS;
+  const int seg_lo = min(warp * seg_len, n), seg_hi = min(seg_lo + seg_len, n);
+  for (int i = seg_lo + lane; i < seg_hi; i += 32) {
+    const uint4 w1 = src[(int64_t)i * 3 + 1];
+    const int bu = (int)floorf(__fdiv_rn(__uint_as_float(w1.z), bucket_w));
+    const int bv = (int)floorf(__fdiv_rn(__uint_as_float(w1.w), bucket_h));
+    atomicAdd(&hist[(bv * cols + bu) * 32 + warp], 1);
+  }
+  __syncthreads();
+  // exclusive scan over the 32 segments of every bucket (warp per bucket)
+  for (int b = warp; b < nb; b += K4_WARPS) {
+    const int v = hist[b * 32 + lane];
+    int incl = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    hist[b * 32 + lane] = incl - v;
+    if (lane == 31) cnt[b] = incl;
+  }
+  __syncthreads();
+  // ---- exclusive scans over buckets: LFSR offsets and output offsets -----------------------
+  if (tid == 0) { s_carry[0] = 0; s_carry[1] = 0; }
+  __syncthreads();
+  for (int base = 0; base < nb; base += K4_THREADS) {
+    const int b = base + tid;
+    const int len = (b < nb) ? cnt[b] : 0;
+    const int a0 = max(len - 1, 0), a1 = min(len, keep);
+    int i0 = a0, i1 = a1;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o0 = __shfl_up_sync(0xFFFFFFFFu, i0, d), o1 = __shfl_up_sync(0xFFFFFFFFu, i1, d);
+      if (lane >= d) { i0 += o0; i1 += o1; }
+    }
+    if (lane == 31) { s_scan[warp][0] = i0; s_scan[warp][1] = i1; }
+    __syncthreads();
+    int p0 = s_carry[0], p1 = s_carry[1];
+    for (int w = 0; w < warp; w++) { p0 += s_scan[w][0]; p1 += s_scan[w][1]; }
+    if (b < nb) { soff[b] = p0 + i0 - a0; ooff[b] = p1 + i1 - a1; }
+    __syncthreads();
+    if (tid == K4_THREADS - 1) { s_carry[0] = p0 + i0; s_carry[1] = p1 + i1; }
+    __syncthreads();
+  }
+  const int total_keep = s_carry[1];
+  if (total_keep > q_cap || total_keep > out_cap) {
+    if (tid == 0) { n_out[pair] = 0; atomicExch(status, 3); }
+    return;
+  }
+  // ---- backward trace of the shuffle for every kept slot -----------------------------------
+  for (int b = tid; b < nb; b += K4_THREADS) {
+    const int len = cnt[b], kept = min(len, keep), s0 = soff[b], o0 = ooff[b];
+    for (int t = 0; t < kept; t++) {
+      int pos = t;
+      for (int i = len - 1; i >= 1; i--) {  // undo swap(p[i], p[rand % (i+1)]) (src/matcher.cpp:128-136)
+        const int j = (int)(lfsr[s0 + i - 1] % (uint32_t)(i + 1));
+        pos = (pos == i) ? j : ((pos == j) ? i : pos);
+      }
+      q[o0 + t] = pos;
+    }
+  }
+  __syncthreads();
+  // ---- pass 2: stable rank of every match inside its bucket; copy the selected ones -------
+  for (int i0 = seg_lo; i0 < seg_hi; i0 += 32) {
+    const int i = i0 + lane;
+    const bool act = i < seg_hi;
+    const uint32_t amask = __ballot_sync(0xFFFFFFFFu, act);
+    if (act) {
+      const uint4 w0 = src[(int64_t)i * 3], w1 = src[(int64_t)i * 3 + 1], w2 = src[(int64_t)i * 3 + 2];
+      const int bu = (int)floorf(__fdiv_rn(__uint_as_float(w1.z), bucket_w));
+      const int bv = (int)floorf(__fdiv_rn(__uint_as_float(w1.w), bucket_h));
+      const int b = bv * cols + bu;
+      const uint32_t same = __match_any_sync(amask, b);
+      const int rank = hist[b * 32 + warp] + __popc(same & ((1u << lane) - 1u));
+      __syncwarp(amask);
+      if ((same & ((1u << lane) - 1u)) == 0) hist[b * 32 + warp] += __popc(same);
+      const int kept = min(cnt[b], keep), o0 = ooff[b];
+      for (int t = 0; t < kept; t++)
+        if (q[o0 + t] == rank) {
+          uint4* rec = dst + (int64_t)(o0 + t) * 3;
+          rec[0] = w0; rec[1] = w1; rec[2] = w2;
+        }
+    }
+    __syncwarp();
+  }
+  if (tid == 0) n_out[pair] = total_keep;
+}
+
+int64_t k4_scratch_ints_host(int nb_max, int q_cap) { return k4_scratch_ints(nb_max, q_cap); }
+
+cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* n_in, int n_pairs, int32_t max_features,
+                      float bw, float bh, const uint32_t* lfsr, int32_t lfsr_len, int32_t* scratch, int64_t scratch_stride,
+                      int32_t nb_max, int32_t q_cap, void* out, int64_t out_stride_matches, int32_t out_cap,
+                      int32_t* n_out, int32_t* status, cudaStream_t st) {
+  k4_bucket<<<n_pairs, K4_THREADS, 0, st>>>((const uint4*)in, in_stride_matches, n_in, max_features, bw, bh, lfsr,
+                                            lfsr_len, scratch, scratch_stride, nb_max, q_cap, (uint4*)out,
+                                            out_stride_matches, out_cap, n_out, status);
+  return cudaGetLastError();
+}
+
+}  // namespace vo

@@ -1,0 +1,774 @@
+// libvo_b200: engine + C ABI (include/vo_b200.h).  Host side only -- all arithmetic of the hot path
+// lives in vo_extract.cu / vo_match.cu / vo_bucket.cu.  There is no CPU implementation of any
+// operator in this library: without a usable CUDA device vo_engine_create fails.
+#include "../../include/vo_b200.h"
+#include "vo_common.cuh"
+
+#include <cuda.h>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+namespace vo {
+size_t k1_smem_bytes();
+cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
+                      cudaStream_t st);
+cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t* max2, int32_t* max2_num,
+                        int cap_stride, int32_t* overflow, cudaStream_t st);
+cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
+                        int cap_stride, cudaStream_t st);
+cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
+                      int rows_per_group, int cand_cap, cudaStream_t st);
+cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
+                      uint8_t* flags, int32_t* list_cnt, void* out, int64_t out_stride_matches, int32_t max_matches,
+                      int32_t* n_raw, int32_t* status, cudaStream_t st);
+int64_t k4_scratch_ints_host(int nb_max, int q_cap);
+cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* n_in, int n_pairs, int32_t max_features,
+                      float bw, float bh, const uint32_t* lfsr, int32_t lfsr_len, int32_t* scratch, int64_t scratch_stride,
+                      int32_t nb_max, int32_t q_cap, void* out, int64_t out_stride_matches, int32_t out_cap,
+                      int32_t* n_out, int32_t* status, cudaStream_t st);
+}  // namespace vo
+
+namespace {
+
+thread_local std::string g_err;
+
+vo_status fail(vo_status s, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return s;
+}
+
+#define CU_TRY(expr)                                                                              \
+  do {                                                                                            \
+    cudaError_t _e = (expr);                                                                      \
+    if (_e != cudaSuccess) return fail(VO_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e));     \
+  } while (0)
+
+constexpr int kLfsrLen = 1 << 18;
+constexpr int kNbMax = 4096;   // buckets per list supported by K4
+constexpr int kQCap = 16384;   // kept matches per list supported by K4
+
+enum Family { F_EXTRACT = 0, F_MATCH = 1, F_EMIT = 2, F_BUCKET = 3 };
+
+}  // namespace
+
+struct vo_engine {
+  vo_config cfg{};
+  vo::Geom g{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int n_slots = 0, n_pairbuf = 0;       // incl. the operator-level scratch slots / pair
+  int op_slot_a = 0, op_slot_b = 0, op_pair = 0;
+  int rows_per_group = 0, cand_cap = 0;
+  vo::FrameArrays fa{};
+  CUtensorMap tmap_slots;
+  // pair buffers
+  int2* d_pairs = nullptr;
+  int2* h_pairs = nullptr;              // pinned
+  uint32_t* d_best = nullptr;
+  uint8_t* d_flags = nullptr;
+  int32_t* d_list_cnt = nullptr;
+  vo_p_match* d_raw = nullptr;          // [n_pairbuf][max_matches]
+  vo_p_match* d_bucketed = nullptr;     // [n_pairbuf][max_matches]
+  int32_t* d_n_raw = nullptr;           // [n_pairbuf]
+  int32_t* d_n_bucketed = nullptr;      // [n_pairbuf]
+  int32_t* d_status = nullptr;          // sticky device-side status word
+  int32_t* h_counts = nullptr;          // pinned [2*n_pairbuf + 4]
+  int32_t* d_scratch = nullptr;
+  int64_t scratch_stride = 0;
+  uint32_t* d_lfsr = nullptr;
+  // operator-level staging
+  int32_t* d_max2 = nullptr; size_t d_max2_bytes = 0;
+  int32_t* d_max2b = nullptr; size_t d_max2b_bytes = 0;
+  int32_t* d_num = nullptr;             // [2][bin_num]
+  // Matcher-level state
+  int ring_prev = 0, ring_curr = 1;
+  int frames_pushed = 0;
+  int cur_which = 0;                    // 0: raw list is current, 1: bucketed list
+  int last_batch_pairs = 0;
+  // instrumentation
+  int64_t launches = 0;
+  bool profiling = false;
+  struct Ev { cudaEvent_t a, b; int fam; };
+  std::vector<Ev> evs;
+  size_t ev_used = 0;
+  double prof_ms[4] = {0, 0, 0, 0};
+  int64_t prof_calls[4] = {0, 0, 0, 0};
+};
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 3-D u8 tensor (x, y, frame) with a 96x59x1 box; out-of-bounds reads return zeros.
+vo_status make_tmap(CUtensorMap* m, const void* base, int W, int H, int n, int64_t pitch, int64_t frame_stride) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return fail(VO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
+  cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
+  cuuint32_t box[3] = {96, 59, 1};
+  cuuint32_t es[3] = {1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(VO_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return VO_OK;
+}
+
+// bit model of Matcher::rand_number (src/matcher.cpp:113-124) on x86; see oracle/vo_oracle.c
+uint32_t lfsr_next(uint32_t x) {
+  uint32_t t0 = (x >= 0x80000000u) ? 0u : (x & 1u);
+  uint32_t b = (t0 ^ (x >> 10) ^ (x >> 30) ^ (x >> 31)) & 1u;
+  return (x >> 1) | (b << 31);
+}
+
+struct Scope {  // brackets one kernel family launch with CUDA events when profiling is on
+  vo_engine* e; int fam; size_t idx = (size_t)-1;
+  Scope(vo_engine* e_, int fam_) : e(e_), fam(fam_) {
+    if (!e->profiling) return;
+    if (e->ev_used == e->evs.size()) {
+      vo_engine::Ev ev{};
+      cudaEventCreate(&ev.a); cudaEventCreate(&ev.b);
+      e->evs.push_back(ev);
+    }
+    idx = e->ev_used++;
+    e->evs[idx].fam = fam;
+    cudaEventRecord(e->evs[idx].a, e->stream);
+  }
+  ~Scope() {
+    if (idx != (size_t)-1) cudaEventRecord(e->evs[idx].b, e->stream);
+  }
+};
+
+void drain_events(vo_engine* e) {
+  for (size_t i = 0; i < e->ev_used; i++) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e->evs[i].a, e->evs[i].b) == cudaSuccess) {
+      e->prof_ms[e->evs[i].fam] += ms;
+      e->prof_calls[e->evs[i].fam] += 1;
+    }
+  }
+  e->ev_used = 0;
+}
+
+vo_status check_device_status(vo_engine* e) {
+  int32_t st = 0;
+  CU_TRY(cudaMemcpyAsync(&e->h_counts[2 * e->n_pairbuf], e->d_status, 4, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  st = e->h_counts[2 * e->n_pairbuf];
+  if (st != 0) {
+    cudaMemsetAsync(e->d_status, 0, 4, e->stream);
+    return fail(VO_ERR_CAPACITY, "device capacity flag %d (1: raw match list, 2: bucket grid/LFSR table, 3: bucketed list)", st);
+  }
+  return VO_OK;
+}
+
+vo_status do_extract(vo_engine* e, const CUtensorMap& tm, int first_slot, int z_base, int n) {
+  const vo::Geom& g = e->g;
+  // v-bins the reference never flushes read as empty: clear all counts of the target slots
+  CU_TRY(cudaMemsetAsync(e->fa.cnt + (int64_t)first_slot * e->fa.cnt_stride, 0, sizeof(int32_t) * g.bin_num * (size_t)n,
+                         e->stream));
+  {
+    Scope sc(e, F_EXTRACT);
+    CU_TRY(vo::launch_k1(tm, g, e->fa, first_slot, z_base, n, e->stream));
+    e->launches += 1;
+  }
+  return VO_OK;
+}
+
+vo_status upload_images(vo_engine* e, int first_slot, int n, const uint8_t* images, int64_t frame_stride, int pitch,
+                        cudaMemcpyKind kind) {
+  const vo::Geom& g = e->g;
+  uint8_t* dst = e->fa.img + (int64_t)first_slot * e->fa.img_stride;
+  if (frame_stride == (int64_t)pitch * g.H) {
+    CU_TRY(cudaMemcpy2DAsync(dst, g.pitch, images, pitch, g.W, (size_t)g.H * n, kind, e->stream));
+  } else {
+    for (int i = 0; i < n; i++)
+      CU_TRY(cudaMemcpy2DAsync(dst + (int64_t)i * e->fa.img_stride, g.pitch, images + (int64_t)i * frame_stride, pitch,
+                               g.W, g.H, kind, e->stream));
+  }
+  return VO_OK;
+}
+
+vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float bw, float bh) {
+  const vo::Geom& g = e->g;
+  {
+    Scope sc(e, F_MATCH);
+    CU_TRY(vo::launch_k2(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
+                         e->rows_per_group, e->cand_cap, e->stream));
+    e->launches += 1;
+  }
+  {
+    Scope sc(e, F_EMIT);
+    CU_TRY(vo::launch_k3(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
+                         e->d_flags + (int64_t)pair0 * g.U * 4 * g.col_cap, e->d_list_cnt + (int64_t)pair0 * g.U * 4,
+                         e->d_raw + (int64_t)pair0 * e->cfg.max_matches, e->cfg.max_matches, e->cfg.max_matches,
+                         e->d_n_raw + pair0, e->d_status, e->stream));
+    e->launches += 2;
+  }
+  if (max_features > 0) {
+    Scope sc(e, F_BUCKET);
+    CU_TRY(vo::launch_k4(e->d_raw + (int64_t)pair0 * e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + pair0, n_pairs,
+                         max_features, bw, bh, e->d_lfsr, kLfsrLen, e->d_scratch + (int64_t)pair0 * e->scratch_stride,
+                         e->scratch_stride, kNbMax, kQCap, e->d_bucketed + (int64_t)pair0 * e->cfg.max_matches,
+                         e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + pair0, e->d_status, e->stream));
+    e->launches += 1;
+  }
+  return VO_OK;
+}
+
+vo_status set_pairs(vo_engine* e, int pair0, int n, const int32_t* prev, const int32_t* curr) {
+  for (int i = 0; i < n; i++) {
+    if (prev[i] < 0 || prev[i] >= e->n_slots || curr[i] < 0 || curr[i] >= e->n_slots)
+      return fail(VO_ERR_INVALID, "pair %d: slot out of range", i);
+    e->h_pairs[pair0 + i] = make_int2(prev[i], curr[i]);
+  }
+  CU_TRY(cudaMemcpyAsync(e->d_pairs + pair0, e->h_pairs + pair0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->stream));
+  return VO_OK;
+}
+
+vo_status ensure(int32_t** p, size_t* have, size_t need) {
+  if (*have >= need) return VO_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *have = 0;
+  CU_TRY(cudaMalloc(p, need));
+  *have = need;
+  return VO_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* vo_last_error(void) { return g_err.c_str(); }
+const char* vo_version(void) { return "vo_b200 0.1 (sm_100a)"; }
+
+vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream, vo_engine** out) {
+  if (!cfg_in || !out) return fail(VO_ERR_INVALID, "null argument");
+  *out = nullptr;
+  vo_config cfg = *cfg_in;
+  if (cfg.bin_w == 0) cfg.bin_w = 60;
+  if (cfg.bin_h == 0) cfg.bin_h = 45;
+  if (cfg.nms_tau == 0) cfg.nms_tau = 50;
+  if (cfg.max_frames == 0) cfg.max_frames = 2;
+  if (cfg.max_pairs == 0) cfg.max_pairs = 1;
+  if (cfg.width < 128 || cfg.height < 64 || cfg.width > 16384 || cfg.height > 16384)
+    return fail(VO_ERR_INVALID, "image size %dx%d outside [128..16384]x[64..16384]", cfg.width, cfg.height);
+  if (cfg.bin_w != 60 || cfg.bin_h != 45)
+    return fail(VO_ERR_UNSUPPORTED, "bin size %dx%d: the reference path (src/size.h:10-11) and the sm_100a tile "
+                "kernel are specialised for 60x45", cfg.bin_w, cfg.bin_h);
+  if (cfg.nms_tau < 1 || cfg.nms_tau > 32767) return fail(VO_ERR_INVALID, "nms_tau out of range");
+  if (cfg.max_frames < 2 || cfg.max_pairs < 1) return fail(VO_ERR_INVALID, "max_frames >= 2 and max_pairs >= 1 required");
+
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(VO_ERR_CUDA, "no CUDA device: libvo_b200 has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(VO_ERR_INVALID, "device %d of %d", device, ndev);
+  CU_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(VO_ERR_CUDA, "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
+
+  vo_engine* e = new (std::nothrow) vo_engine();
+  if (!e) return fail(VO_ERR_INVALID, "out of host memory");
+  e->device = device;
+  vo::Geom& g = e->g;
+  g.W = cfg.width; g.H = cfg.height; g.pitch = (cfg.width + 15) & ~15;
+  g.bin_w = cfg.bin_w; g.bin_h = cfg.bin_h;
+  const int last_i = 9 + 3 * ((g.W - 10 - 9) / 3);
+  g.U = last_i / g.bin_w + 1;
+  g.V = g.H / g.bin_h + 1;
+  g.cap = (g.bin_w / 3) * (g.bin_h / 3);
+  g.col_cap = g.cap * g.V;
+  g.bin_num = g.U * g.V * 4;
+  g.tau = cfg.nms_tau;
+  g.j_last = 9 + 3 * ((g.H - 10 - 9) / 3);
+  g.v_rem = g.H / g.bin_h;
+  g.rad_u = 3 * g.bin_w; g.rad_v = 3 * g.bin_h;
+  if (g.V > 64 || g.col_cap > 65535 || g.U < 2) {
+    const int gu = g.U, gv = g.V;
+    delete e;
+    return fail(VO_ERR_UNSUPPORTED, "geometry U=%d V=%d exceeds kernel tables (V<=64, cap*V<=65535)", gu, gv);
+  }
+  if (cfg.max_matches == 0) cfg.max_matches = g.U * g.V * g.cap;
+  e->cfg = cfg;
+  e->n_slots = cfg.max_frames + 2; e->op_slot_a = cfg.max_frames; e->op_slot_b = cfg.max_frames + 1;
+  e->n_pairbuf = cfg.max_pairs + 1; e->op_pair = cfg.max_pairs;
+  e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : 3;
+  e->cand_cap = 2560;  // >= 6*cap (one full row of the window always fits)
+  if (e->cand_cap < 6 * g.cap) e->cand_cap = 6 * g.cap;
+
+  if (stream) { e->stream = (cudaStream_t)stream; e->own_stream = false; }
+  else {
+    if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { delete e; return fail(VO_ERR_CUDA, "stream create"); }
+    e->own_stream = true;
+  }
+
+#define ALLOC(ptr, bytes)                                                                        \
+  do {                                                                                           \
+    cudaError_t _e = cudaMalloc((void**)&(ptr), (bytes));                                        \
+    if (_e != cudaSuccess) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "cudaMalloc(%zu): %s", (size_t)(bytes), cudaGetErrorString(_e)); } \
+  } while (0)
+
+  const int64_t S = e->n_slots, P = e->n_pairbuf;
+  e->fa.img_stride = (int64_t)g.pitch * g.H;
+  e->fa.cnt_stride = g.bin_num;
+  e->fa.rec_stride = (int64_t)g.bin_num * g.cap;
+  ALLOC(e->fa.img, (size_t)(S * e->fa.img_stride + 256));
+  ALLOC(e->fa.cnt, sizeof(int32_t) * S * e->fa.cnt_stride);
+  ALLOC(e->fa.xy, sizeof(uint32_t) * S * e->fa.rec_stride);
+  ALLOC(e->fa.meta, sizeof(uint32_t) * S * e->fa.rec_stride);
+  ALLOC(e->fa.desc, sizeof(uint4) * 2 * S * e->fa.rec_stride);
+  cudaMemsetAsync(e->fa.cnt, 0, sizeof(int32_t) * S * e->fa.cnt_stride, e->stream);
+  cudaMemsetAsync(e->fa.img, 0, (size_t)(S * e->fa.img_stride + 256), e->stream);
+  const int64_t lists = (int64_t)g.U * 4 * g.col_cap;
+  ALLOC(e->d_pairs, sizeof(int2) * P);
+  ALLOC(e->d_best, sizeof(uint32_t) * P * 2 * lists);
+  ALLOC(e->d_flags, (size_t)(P * lists));
+  ALLOC(e->d_list_cnt, sizeof(int32_t) * P * g.U * 4);
+  ALLOC(e->d_raw, sizeof(vo_p_match) * P * cfg.max_matches);
+  ALLOC(e->d_bucketed, sizeof(vo_p_match) * P * cfg.max_matches);
+  ALLOC(e->d_n_raw, sizeof(int32_t) * P);
+  ALLOC(e->d_n_bucketed, sizeof(int32_t) * P);
+  ALLOC(e->d_status, sizeof(int32_t));
+  ALLOC(e->d_num, sizeof(int32_t) * 2 * g.bin_num);
+  cudaMemsetAsync(e->d_n_raw, 0, sizeof(int32_t) * P, e->stream);
+  cudaMemsetAsync(e->d_n_bucketed, 0, sizeof(int32_t) * P, e->stream);
+  cudaMemsetAsync(e->d_status, 0, sizeof(int32_t), e->stream);
+  cudaMemsetAsync(e->d_best, 0xFF, sizeof(uint32_t) * P * 2 * lists, e->stream);
+  e->scratch_stride = vo::k4_scratch_ints_host(kNbMax, kQCap);
+  ALLOC(e->d_scratch, sizeof(int32_t) * P * e->scratch_stride);
+  ALLOC(e->d_lfsr, sizeof(uint32_t) * kLfsrLen);
+  {
+    std::vector<uint32_t> tab(kLfsrLen);
+    uint32_t x = 5;  // src/matcher.cpp:170
+    for (int i = 0; i < kLfsrLen; i++) { tab[i] = x; x = lfsr_next(x); }
+    if (cudaMemcpy(e->d_lfsr, tab.data(), sizeof(uint32_t) * kLfsrLen, cudaMemcpyHostToDevice) != cudaSuccess) {
+      vo_engine_destroy(e);
+      return fail(VO_ERR_CUDA, "lfsr upload");
+    }
+  }
+  if (cudaMallocHost((void**)&e->h_pairs, sizeof(int2) * P) != cudaSuccess ||
+      cudaMallocHost((void**)&e->h_counts, sizeof(int32_t) * (2 * P + 4)) != cudaSuccess) {
+    vo_engine_destroy(e);
+    return fail(VO_ERR_CUDA, "pinned alloc");
+  }
+  vo_status s = make_tmap(&e->tmap_slots, e->fa.img, g.W, g.H, (int)S, g.pitch, e->fa.img_stride);
+  if (s != VO_OK) { vo_engine_destroy(e); return s; }
+  if (cudaStreamSynchronize(e->stream) != cudaSuccess) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "init sync"); }
+  *out = e;
+  return VO_OK;
+#undef ALLOC
+}
+
+void vo_engine_destroy(vo_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc);
+  cudaFree(e->d_pairs); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
+  cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
+  cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);
+  if (e->h_pairs) cudaFreeHost(e->h_pairs);
+  if (e->h_counts) cudaFreeHost(e->h_counts);
+  for (auto& ev : e->evs) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
+  if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+vo_status vo_engine_geometry(const vo_engine* e, vo_geometry* out) {
+  if (!e || !out) return fail(VO_ERR_INVALID, "null argument");
+  std::memset(out, 0, sizeof(*out));
+  out->width = e->g.W; out->height = e->g.H; out->pitch = e->g.pitch;
+  out->bin_w = e->g.bin_w; out->bin_h = e->g.bin_h;
+  out->u_bins = e->g.U; out->v_bins = e->g.V; out->bin_cap = e->g.cap; out->col_cap = e->g.col_cap;
+  out->bin_num = e->g.bin_num;
+  out->max_frames = e->cfg.max_frames; out->max_pairs = e->cfg.max_pairs; out->max_matches = e->cfg.max_matches;
+  return VO_OK;
+}
+
+vo_status vo_engine_synchronize(vo_engine* e) {
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  return VO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// operator level
+// ---------------------------------------------------------------------------------------------
+
+static vo_status dump_slot(vo_engine* e, int slot, int32_t* max2, int32_t* max2_num, int32_t cap_stride) {
+  const vo::Geom& g = e->g;
+  if (!max2 || !max2_num || cap_stride < 1) return fail(VO_ERR_INVALID, "bad dump arguments");
+  const size_t bytes = sizeof(int32_t) * 12 * (size_t)g.bin_num * cap_stride;
+  vo_status s = ensure(&e->d_max2, &e->d_max2_bytes, bytes);
+  if (s != VO_OK) return s;
+  int32_t* d_ovf = e->d_num + g.bin_num;  // reuse second half's first word as the overflow flag
+  CU_TRY(cudaMemsetAsync(d_ovf, 0, 4, e->stream));
+  CU_TRY(cudaMemsetAsync(e->d_max2, 0, bytes, e->stream));
+  CU_TRY(vo::launch_dump(g, e->fa, slot, e->d_max2, e->d_num, cap_stride, d_ovf, e->stream));
+  e->launches += 1;
+  CU_TRY(cudaMemcpyAsync(max2, e->d_max2, bytes, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaMemcpyAsync(max2_num, e->d_num, sizeof(int32_t) * g.bin_num, cudaMemcpyDeviceToHost, e->stream));
+  int32_t ovf = 0;
+  CU_TRY(cudaMemcpyAsync(&ovf, d_ovf, 4, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  if (ovf) return fail(VO_ERR_CAPACITY, "a (bin,class) list is longer than cap_stride=%d (the reference would overflow)", cap_stride);
+  return VO_OK;
+}
+
+vo_status vo_compute_features(vo_engine* e, const uint8_t* image, int32_t pitch_bytes, int32_t* max2,
+                              int32_t* max2_num, int32_t cap_stride) {
+  if (!e || !image) return fail(VO_ERR_INVALID, "null argument");
+  if (pitch_bytes < e->g.W) return fail(VO_ERR_INVALID, "ERROR: Image dimension mismatch!");
+  CU_TRY(cudaSetDevice(e->device));
+  vo_status s = upload_images(e, e->op_slot_a, 1, image, (int64_t)pitch_bytes * e->g.H, pitch_bytes, cudaMemcpyHostToDevice);
+  if (s != VO_OK) return s;
+  s = do_extract(e, e->tmap_slots, e->op_slot_a, e->op_slot_a, 1);
+  if (s != VO_OK) return s;
+  return dump_slot(e, e->op_slot_a, max2, max2_num, cap_stride);
+}
+
+vo_status vo_matching(vo_engine* e, const int32_t* m1p, const int32_t* n1p, const int32_t* m1c, const int32_t* n1c,
+                      int32_t cap_stride, vo_p_match* p_matched, int32_t p_matched_cap, int32_t* p_matched_num) {
+  if (!e || !m1p || !n1p || !m1c || !n1c || !p_matched_num || cap_stride < 1) return fail(VO_ERR_INVALID, "null argument");
+  CU_TRY(cudaSetDevice(e->device));
+  const vo::Geom& g = e->g;
+  const size_t bytes = sizeof(int32_t) * 12 * (size_t)g.bin_num * cap_stride;
+  vo_status s = ensure(&e->d_max2, &e->d_max2_bytes, bytes);
+  if (s != VO_OK) return s;
+  s = ensure(&e->d_max2b, &e->d_max2b_bytes, bytes);
+  if (s != VO_OK) return s;
+  CU_TRY(cudaMemcpyAsync(e->d_max2, m1p, bytes, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_max2b, m1c, bytes, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_num, n1p, sizeof(int32_t) * g.bin_num, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_num + g.bin_num, n1c, sizeof(int32_t) * g.bin_num, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(vo::launch_load(g, e->fa, e->op_slot_a, e->d_max2, e->d_num, cap_stride, e->stream));
+  CU_TRY(vo::launch_load(g, e->fa, e->op_slot_b, e->d_max2b, e->d_num + g.bin_num, cap_stride, e->stream));
+  e->launches += 2;
+  int32_t pv = e->op_slot_a, cu = e->op_slot_b;
+  s = set_pairs(e, e->op_pair, 1, &pv, &cu);
+  if (s != VO_OK) return s;
+  s = do_match(e, e->op_pair, 1, 0, 0.f, 0.f);
+  if (s != VO_OK) return s;
+  CU_TRY(cudaMemcpyAsync(&e->h_counts[0], e->d_n_raw + e->op_pair, 4, cudaMemcpyDeviceToHost, e->stream));
+  s = check_device_status(e);
+  if (s != VO_OK) return s;
+  const int32_t n = e->h_counts[0];
+  *p_matched_num = n;
+  if (n > p_matched_cap) return fail(VO_ERR_CAPACITY, "%d matches > caller capacity %d", n, p_matched_cap);
+  if (n > 0) {
+    CU_TRY(cudaMemcpyAsync(p_matched, e->d_raw + (int64_t)e->op_pair * e->cfg.max_matches, sizeof(vo_p_match) * n,
+                           cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(cudaStreamSynchronize(e->stream));
+  }
+  return VO_OK;
+}
+
+vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, int32_t max_features, float bucket_w,
+                            float bucket_h, vo_p_match* out, int32_t out_cap, int32_t* n_out) {
+  if (!e || (!in && n_in > 0) || !n_out || n_in < 0) return fail(VO_ERR_INVALID, "null argument");
+  if (!(bucket_w > 0.f) || !(bucket_h > 0.f)) return fail(VO_ERR_INVALID, "bucket size must be positive");
+  if (n_in > e->cfg.max_matches) return fail(VO_ERR_CAPACITY, "%d matches > engine capacity %d", n_in, e->cfg.max_matches);
+  CU_TRY(cudaSetDevice(e->device));
+  const int pb = e->op_pair;
+  if (n_in > 0)
+    CU_TRY(cudaMemcpyAsync(e->d_raw + (int64_t)pb * e->cfg.max_matches, in, sizeof(vo_p_match) * n_in, cudaMemcpyHostToDevice, e->stream));
+  e->h_counts[1] = n_in;
+  CU_TRY(cudaMemcpyAsync(e->d_n_raw + pb, &e->h_counts[1], 4, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(vo::launch_k4(e->d_raw + (int64_t)pb * e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + pb, 1, max_features,
+                       bucket_w, bucket_h, e->d_lfsr, kLfsrLen, e->d_scratch + (int64_t)pb * e->scratch_stride,
+                       e->scratch_stride, kNbMax, kQCap, e->d_bucketed + (int64_t)pb * e->cfg.max_matches,
+                       e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + pb, e->d_status, e->stream));
+  e->launches += 1;
+  CU_TRY(cudaMemcpyAsync(&e->h_counts[0], e->d_n_bucketed + pb, 4, cudaMemcpyDeviceToHost, e->stream));
+  vo_status s = check_device_status(e);
+  if (s != VO_OK) return s;
+  const int32_t n = e->h_counts[0];
+  *n_out = n;
+  if (n > out_cap) return fail(VO_ERR_CAPACITY, "%d bucketed matches > caller capacity %d", n, out_cap);
+  if (n > 0) {
+    CU_TRY(cudaMemcpyAsync(out, e->d_bucketed + (int64_t)pb * e->cfg.max_matches, sizeof(vo_p_match) * n,
+                           cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(cudaStreamSynchronize(e->stream));
+  }
+  return VO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Matcher level
+// ---------------------------------------------------------------------------------------------
+
+vo_status vo_push_back(vo_engine* e, const uint8_t* I1, const uint8_t* I2, const int32_t dims[3], int32_t replace) {
+  (void)I2;  // ignored, as in the reference (src/matcher.cpp:51-91 never reads I2)
+  if (!e || !dims) return fail(VO_ERR_INVALID, "null argument");
+  const int32_t width = dims[0], height = dims[1], bpl = dims[2];
+  if (width <= 0 || height <= 0 || bpl < width || I1 == nullptr)
+    return fail(VO_ERR_INVALID, "ERROR: Image dimension mismatch!");  // src/matcher.cpp:59-62
+  if (width != e->g.W || height != e->g.H)
+    return fail(VO_ERR_INVALID, "image %dx%d does not match engine geometry %dx%d", width, height, e->g.W, e->g.H);
+  CU_TRY(cudaSetDevice(e->device));
+  if (!replace) {  // prev <- curr is a slot swap, not a 3.66 MB copy (src/matcher.cpp:68-73)
+    const int t = e->ring_prev; e->ring_prev = e->ring_curr; e->ring_curr = t;
+    e->frames_pushed += 1;
+  } else if (e->frames_pushed == 0) {
+    e->frames_pushed = 1;
+  }
+  vo_status s = upload_images(e, e->ring_curr, 1, I1, (int64_t)bpl * height, bpl, cudaMemcpyHostToDevice);
+  if (s != VO_OK) return s;
+  s = do_extract(e, e->tmap_slots, e->ring_curr, e->ring_curr, 1);
+  if (s != VO_OK) return s;
+  // the caller's image is borrowed only for the duration of the call
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  return VO_OK;
+}
+
+vo_status vo_match_features(vo_engine* e, int32_t method) {
+  (void)method;  // ignored, as in the reference (src/matcher.cpp:93-111)
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  CU_TRY(cudaSetDevice(e->device));
+  e->cur_which = 0;
+  if (e->frames_pushed < 2) {  // frame-0 contract: zero matches
+    CU_TRY(cudaMemsetAsync(e->d_n_raw + 0, 0, 4, e->stream));
+    return VO_OK;
+  }
+  int32_t pv = e->ring_prev, cu = e->ring_curr;
+  vo_status s = set_pairs(e, 0, 1, &pv, &cu);
+  if (s != VO_OK) return s;
+  s = do_match(e, 0, 1, 0, 0.f, 0.f);
+  if (s != VO_OK) return s;
+  return check_device_status(e);
+}
+
+vo_status vo_bucket_features(vo_engine* e, int32_t max_features, float bucket_w, float bucket_h) {
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  if (!(bucket_w > 0.f) || !(bucket_h > 0.f)) return fail(VO_ERR_INVALID, "bucket size must be positive");
+  CU_TRY(cudaSetDevice(e->device));
+  const int64_t M = e->cfg.max_matches;
+  if (e->cur_which == 1) {  // bucketing an already bucketed list: feed it back as the input list
+    CU_TRY(cudaMemcpyAsync(e->d_raw, e->d_bucketed, sizeof(vo_p_match) * M, cudaMemcpyDeviceToDevice, e->stream));
+    CU_TRY(cudaMemcpyAsync(e->d_n_raw, e->d_n_bucketed, 4, cudaMemcpyDeviceToDevice, e->stream));
+  }
+  {
+    Scope sc(e, F_BUCKET);
+    CU_TRY(vo::launch_k4(e->d_raw, M, e->d_n_raw, 1, max_features, bucket_w, bucket_h, e->d_lfsr, kLfsrLen, e->d_scratch,
+                         e->scratch_stride, kNbMax, kQCap, e->d_bucketed, M, (int32_t)M, e->d_n_bucketed, e->d_status,
+                         e->stream));
+    e->launches += 1;
+  }
+  e->cur_which = 1;
+  return check_device_status(e);
+}
+
+vo_status vo_num_matches(vo_engine* e, int32_t* n) {
+  if (!e || !n) return fail(VO_ERR_INVALID, "null argument");
+  CU_TRY(cudaSetDevice(e->device));
+  CU_TRY(cudaMemcpyAsync(&e->h_counts[0], e->cur_which ? e->d_n_bucketed : e->d_n_raw, 4, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  *n = e->h_counts[0];
+  return VO_OK;
+}
+
+vo_status vo_get_matches(vo_engine* e, vo_p_match* out, int32_t cap, int32_t* n) {
+  if (!e || !n) return fail(VO_ERR_INVALID, "null argument");
+  vo_status s = vo_num_matches(e, n);
+  if (s != VO_OK) return s;
+  if (*n > cap) return fail(VO_ERR_CAPACITY, "%d matches > caller capacity %d", *n, cap);
+  if (*n > 0) {
+    if (!out) return fail(VO_ERR_INVALID, "null output");
+    CU_TRY(cudaMemcpyAsync(out, e->cur_which ? e->d_bucketed : e->d_raw, sizeof(vo_p_match) * (size_t)*n, cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(cudaStreamSynchronize(e->stream));
+  }
+  return VO_OK;
+}
+
+vo_status vo_set_matches(vo_engine* e, const vo_p_match* in, int32_t n) {
+  if (!e || n < 0 || (!in && n > 0)) return fail(VO_ERR_INVALID, "bad argument");
+  if (n > e->cfg.max_matches) return fail(VO_ERR_CAPACITY, "%d matches > engine capacity %d", n, e->cfg.max_matches);
+  CU_TRY(cudaSetDevice(e->device));
+  if (n > 0) CU_TRY(cudaMemcpyAsync(e->d_raw, in, sizeof(vo_p_match) * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+  e->h_counts[1] = n;
+  CU_TRY(cudaMemcpyAsync(e->d_n_raw, &e->h_counts[1], 4, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  e->cur_which = 0;
+  return VO_OK;
+}
+
+vo_status vo_dump_features(vo_engine* e, int32_t which, int32_t* max2, int32_t* max2_num, int32_t cap_stride) {
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  CU_TRY(cudaSetDevice(e->device));
+  return dump_slot(e, which ? e->ring_curr : e->ring_prev, max2, max2_num, cap_stride);
+}
+
+// ---------------------------------------------------------------------------------------------
+// batch level
+// ---------------------------------------------------------------------------------------------
+
+vo_status vo_batch_extract_host(vo_engine* e, int32_t first_slot, int32_t n, const uint8_t* images,
+                                int64_t frame_stride_bytes, int32_t pitch_bytes) {
+  if (!e || !images) return fail(VO_ERR_INVALID, "null argument");
+  if (n < 1 || first_slot < 0 || first_slot + n > e->cfg.max_frames) return fail(VO_ERR_INVALID, "slot range [%d,%d) outside [0,%d)", first_slot, first_slot + n, e->cfg.max_frames);
+  if (pitch_bytes < e->g.W || frame_stride_bytes < (int64_t)pitch_bytes * e->g.H) return fail(VO_ERR_INVALID, "ERROR: Image dimension mismatch!");
+  CU_TRY(cudaSetDevice(e->device));
+  vo_status s = upload_images(e, first_slot, n, images, frame_stride_bytes, pitch_bytes, cudaMemcpyHostToDevice);
+  if (s != VO_OK) return s;
+  return do_extract(e, e->tmap_slots, first_slot, first_slot, n);
+}
+
+vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n, const uint8_t* d_images,
+                                  int64_t frame_stride_bytes, int32_t pitch_bytes) {
+  if (!e || !d_images) return fail(VO_ERR_INVALID, "null argument");
+  if (n < 1 || first_slot < 0 || first_slot + n > e->cfg.max_frames) return fail(VO_ERR_INVALID, "slot range [%d,%d) outside [0,%d)", first_slot, first_slot + n, e->cfg.max_frames);
+  if (pitch_bytes < e->g.W || frame_stride_bytes < (int64_t)pitch_bytes * e->g.H) return fail(VO_ERR_INVALID, "ERROR: Image dimension mismatch!");
+  CU_TRY(cudaSetDevice(e->device));
+  const bool tma_ok = ((uintptr_t)d_images % 16 == 0) && (pitch_bytes % 16 == 0) && (frame_stride_bytes % 16 == 0);
+  if (tma_ok) {  // read the caller's HBM-resident frames in place through a tensor map of their own
+    CUtensorMap tm;
+    vo_status s = make_tmap(&tm, d_images, e->g.W, e->g.H, n, pitch_bytes, frame_stride_bytes);
+    if (s != VO_OK) return s;
+    return do_extract(e, tm, first_slot, 0, n);
+  }
+  vo_status s = upload_images(e, first_slot, n, d_images, frame_stride_bytes, pitch_bytes, cudaMemcpyDeviceToDevice);
+  if (s != VO_OK) return s;
+  return do_extract(e, e->tmap_slots, first_slot, first_slot, n);
+}
+
+vo_status vo_batch_match(vo_engine* e, int32_t n_pairs, const int32_t* prev_slot, const int32_t* curr_slot,
+                         int32_t max_features, float bucket_w, float bucket_h) {
+  if (!e || !prev_slot || !curr_slot) return fail(VO_ERR_INVALID, "null argument");
+  if (n_pairs < 1 || n_pairs > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "n_pairs %d outside [1,%d]", n_pairs, e->cfg.max_pairs);
+  if (max_features > 0 && (!(bucket_w > 0.f) || !(bucket_h > 0.f))) return fail(VO_ERR_INVALID, "bucket size must be positive");
+  CU_TRY(cudaSetDevice(e->device));
+  vo_status s = set_pairs(e, 0, n_pairs, prev_slot, curr_slot);
+  if (s != VO_OK) return s;
+  e->last_batch_pairs = n_pairs;
+  e->cur_which = max_features > 0 ? 1 : 0;
+  return do_match(e, 0, n_pairs, max_features, bucket_w, bucket_h);
+}
+
+vo_status vo_batch_counts(vo_engine* e, int32_t n_pairs, int32_t* raw, int32_t* bucketed) {
+  if (!e || n_pairs < 1 || n_pairs > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "bad argument");
+  CU_TRY(cudaSetDevice(e->device));
+  CU_TRY(cudaMemcpyAsync(e->h_counts, e->d_n_raw, 4 * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->h_counts + e->n_pairbuf, e->d_n_bucketed, 4 * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  vo_status s = check_device_status(e);
+  if (s != VO_OK) return s;
+  for (int i = 0; i < n_pairs; i++) {
+    if (raw) raw[i] = e->h_counts[i];
+    if (bucketed) bucketed[i] = e->h_counts[e->n_pairbuf + i];
+  }
+  return VO_OK;
+}
+
+vo_status vo_batch_get_matches(vo_engine* e, int32_t pair, int32_t which, vo_p_match* out, int32_t cap, int32_t* n) {
+  if (!e || !n || pair < 0 || pair >= e->cfg.max_pairs) return fail(VO_ERR_INVALID, "bad argument");
+  CU_TRY(cudaSetDevice(e->device));
+  CU_TRY(cudaMemcpyAsync(&e->h_counts[0], (which ? e->d_n_bucketed : e->d_n_raw) + pair, 4, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  *n = e->h_counts[0];
+  if (*n > cap) return fail(VO_ERR_CAPACITY, "%d matches > caller capacity %d", *n, cap);
+  if (*n > 0) {
+    if (!out) return fail(VO_ERR_INVALID, "null output");
+    CU_TRY(cudaMemcpyAsync(out, (which ? e->d_bucketed : e->d_raw) + (int64_t)pair * e->cfg.max_matches,
+                           sizeof(vo_p_match) * (size_t)*n, cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(cudaStreamSynchronize(e->stream));
+  }
+  return VO_OK;
+}
+
+vo_status vo_batch_download_async(vo_engine* e, int32_t n_pairs, int32_t which, int32_t* counts, vo_p_match* out,
+                                  int64_t stride_matches, int32_t max_per_pair) {
+  if (!e || !counts || n_pairs < 1 || n_pairs > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "bad argument");
+  if (out && (max_per_pair < 1 || max_per_pair > e->cfg.max_matches || stride_matches < max_per_pair))
+    return fail(VO_ERR_INVALID, "bad list geometry");
+  CU_TRY(cudaSetDevice(e->device));
+  CU_TRY(cudaMemcpyAsync(counts, e->d_n_raw, 4 * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaMemcpyAsync(counts + n_pairs, e->d_n_bucketed, 4 * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  if (out) {
+    const vo_p_match* src = which ? e->d_bucketed : e->d_raw;
+    CU_TRY(cudaMemcpy2DAsync(out, sizeof(vo_p_match) * stride_matches, src, sizeof(vo_p_match) * (size_t)e->cfg.max_matches,
+                             sizeof(vo_p_match) * (size_t)max_per_pair, n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  }
+  return VO_OK;
+}
+
+vo_status vo_slot_dump_features(vo_engine* e, int32_t slot, int32_t* max2, int32_t* max2_num, int32_t cap_stride) {
+  if (!e || slot < 0 || slot >= e->cfg.max_frames) return fail(VO_ERR_INVALID, "bad slot");
+  CU_TRY(cudaSetDevice(e->device));
+  return dump_slot(e, slot, max2, max2_num, cap_stride);
+}
+
+vo_status vo_slot_feature_count(vo_engine* e, int32_t slot, int32_t* n) {
+  if (!e || !n || slot < 0 || slot >= e->cfg.max_frames) return fail(VO_ERR_INVALID, "bad slot");
+  CU_TRY(cudaSetDevice(e->device));
+  std::vector<int32_t> c(e->g.bin_num);
+  CU_TRY(cudaMemcpyAsync(c.data(), e->fa.cnt + (int64_t)slot * e->fa.cnt_stride, 4 * (size_t)e->g.bin_num, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  int64_t s = 0;
+  for (int32_t v : c) s += v;
+  *n = (int32_t)s;
+  return VO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// instrumentation
+// ---------------------------------------------------------------------------------------------
+
+vo_status vo_launch_count(const vo_engine* e, int64_t* n) {
+  if (!e || !n) return fail(VO_ERR_INVALID, "null argument");
+  *n = e->launches;
+  return VO_OK;
+}
+
+vo_status vo_profile_enable(vo_engine* e, int32_t on) {
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  drain_events(e);
+  e->profiling = on != 0;
+  return VO_OK;
+}
+
+vo_status vo_profile_read(vo_engine* e, double ms[4], int64_t calls[4], int32_t reset) {
+  if (!e || !ms || !calls) return fail(VO_ERR_INVALID, "null argument");
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  drain_events(e);
+  for (int i = 0; i < 4; i++) { ms[i] = e->prof_ms[i]; calls[i] = e->prof_calls[i]; }
+  if (reset) for (int i = 0; i < 4; i++) { e->prof_ms[i] = 0; e->prof_calls[i] = 0; }
+  return VO_OK;
+}
+
+vo_status vo_host_alloc(void** p, int64_t bytes) {
+  if (!p || bytes <= 0) return fail(VO_ERR_INVALID, "bad argument");
+  CU_TRY(cudaMallocHost(p, (size_t)bytes));
+  return VO_OK;
+}
+
+vo_status vo_host_free(void* p) {
+  if (p) CU_TRY(cudaFreeHost(p));
+  return VO_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,302 @@
+// K1: fused feature extraction for one 60x45-pixel bin tile per CTA (sm_100a).
+//
+// Replaces, bit-exactly, the reference's
+//   mySobel5x5 / myBlob5x5 / myCheckerboard5x5           src/myComputeFeature.cpp:58-151
+//   myNonMaximumSuppression_and_ComputeDescriptors       src/myComputeFeature.cpp:153-350
+//   myComputeDescriptor                                  src/myComputeFeature.cpp:11-55
+// The reference makes four full-frame passes through four full-size planes; here a CTA pulls
+// its 74x59 pixel tile (bin + 7 px halo, inside a 16-byte aligned 96x59 TMA box) into shared memory with one
+// cp.async.bulk.tensor, derives du/dv/f1/f2 there (separably: identical integers, fewer MACs), runs
+// the 3x3-block NMS + 5x5 validity test, and writes the surviving features straight into the
+// per-(v_bin,u_bin,class) lists in block-raster order via warp ballots + an ordered CTA scan --
+// never atomics, so list order equals the reference's sequential append order.
+#include "vo_common.cuh"
+#include <cuda.h>
+
+namespace vo {
+
+constexpr int BW = 60, BH = 45;          // bin size this kernel is specialised for
+constexpr int TW = 96, TH = 59;          // TMA box: 74x59 needed; the box must START on a 16-byte boundary in x
+                                         // (u8 elements: measured, unaligned inner coordinates fault), so up to 15
+                                         // lead-in bytes + 74 -> 96
+constexpr int PW = 72;                   // row stride of the horizontal-pass planes
+constexpr int OW = 70, OH = 55;          // du/dv/f1/f2 region: tile cols 2..71, rows 2..56
+constexpr int NBX = BW / 3, NBY = BH / 3;  // 20 x 15 NMS blocks per tile
+constexpr int K1_THREADS = 320;
+constexpr int K1_WARPS = K1_THREADS / 32;
+
+struct __align__(128) K1Smem {
+  uint8_t img[TH * TW];
+  unsigned long long bar;
+  int16_t hd[TH * PW];    // horizontal [1 2 0 -2 -1]
+  int16_t hg[TH * PW];    // horizontal [1 4 6 4 1]
+  int16_t hc[TH * PW];    // horizontal [-1 -1 0 1 1]
+  int16_t hs5[TH * PW];   // horizontal box-5 sum
+  int16_t ht[TH * PW];    // 2*box3 - box5
+  uint16_t duv[OH * OW];  // du | dv<<8
+  int16_t f1[OH * OW];
+  int16_t f2[OH * OW];
+  int32_t warp_tot[K1_WARPS][4];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ int sobel_u8(int acc) {
+  // C division by 128 truncating toward zero, +128, clamp (src/myComputeFeature.cpp:84-106)
+  int q = ((acc + ((acc >> 31) & 127)) >> 7) + 128;
+  return min(max(q, 0), 255);
+}
+
+__global__ void __launch_bounds__(K1_THREADS)
+k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int first_slot, int z_base) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  K1Smem& s = *reinterpret_cast<K1Smem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int ub = blockIdx.x, r = blockIdx.y, slot = first_slot + blockIdx.z;
+  const int x0 = ub * BW, y0 = r * BH;
+  const int xs = (x0 - 7) & ~15;   // 16-byte aligned box origin (floor, also for the negative halo of ub == 0)
+  const int xoff = x0 - 7 - xs;    // tile column of image x0-7
+
+  // ---- TMA: one 96x59 box at (xs, y0-7, z); out-of-image bytes arrive as zeros -------------
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s.bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s.bar)),
+                 "r"(TW * TH)
+                 : "memory");
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(s.img)),
+        "l"(&tmap), "r"(xs), "r"(y0 - 7), "r"(z_base + (int)blockIdx.z), "r"(smem_u32(&s.bar))
+        : "memory");
+  }
+  {
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(smem_u32(&s.bar))
+          : "memory");
+    }
+  }
+
+  // ---- horizontal 5-tap pass: tile columns 2..71 of all 59 rows ---------------------------
+  for (int idx = tid; idx < TH * OW; idx += K1_THREADS) {
+    const int ty = idx / OW, px = idx - ty * OW;
+    const uint8_t* p = &s.img[ty * TW + xoff + px];
+    const int p0 = p[0], p1 = p[1], p2 = p[2], p3 = p[3], p4 = p[4];
+    const int o = ty * PW + px;
+    const int s3 = p1 + p2 + p3, s5 = s3 + p0 + p4;
+    s.hd[o] = (int16_t)(p0 + 2 * p1 - 2 * p3 - p4);
+    s.hg[o] = (int16_t)(p0 + p4 + 4 * (p1 + p3) + 6 * p2);
+    s.hc[o] = (int16_t)(p3 + p4 - p0 - p1);
+    s.hs5[o] = (int16_t)s5;
+    s.ht[o] = (int16_t)(2 * s3 - s5);
+  }
+  __syncthreads();
+
+  // ---- vertical pass -> du,dv (u8), f1 (blob), f2 (checkerboard) ---------------------------
+  for (int idx = tid; idx < OH * OW; idx += K1_THREADS) {
+    const int oy = idx / OW, ox = idx - oy * OW;
+    const int c0 = (oy + 2) * PW + ox;  // centre row in the planes
+    const int du_acc = s.hd[c0 - 2 * PW] + s.hd[c0 + 2 * PW] + 4 * (s.hd[c0 - PW] + s.hd[c0 + PW]) + 6 * s.hd[c0];
+    const int dv_acc = s.hg[c0 - 2 * PW] + 2 * s.hg[c0 - PW] - 2 * s.hg[c0 + PW] - s.hg[c0 + 2 * PW];
+    const int f2v = s.hc[c0 - 2 * PW] + s.hc[c0 - PW] - s.hc[c0 + PW] - s.hc[c0 + 2 * PW];
+    const int f1v = s.ht[c0 - PW] + s.ht[c0] + s.ht[c0 + PW] - s.hs5[c0 - 2 * PW] - s.hs5[c0 + 2 * PW] +
+                    7 * (int)s.img[(oy + 2) * TW + xoff + ox + 2];
+    s.duv[idx] = (uint16_t)(sobel_u8(du_acc) | (sobel_u8(dv_acc) << 8));
+    s.f1[idx] = (int16_t)f1v;
+    s.f2[idx] = (int16_t)f2v;
+  }
+  __syncthreads();
+
+  // ---- NMS: one thread per 3x3 block, block-raster order == thread order -------------------
+  const int bx = tid % NBX, by = tid / NBX;
+  const int bi = x0 + 3 * bx, bj = y0 + 3 * by;  // block origin (i, j) of the reference loops
+  const bool block_ok = (tid < NBX * NBY) && bi >= 9 && bi < g.W - 9 && bj >= 9 && bj < g.H - 9;
+  bool flag[4] = {false, false, false, false};
+  int pos[4] = {0, 0, 0, 0};  // ox | oy<<8 of the extremum, plane coordinates
+  if (block_ok) {
+    const int ox0 = 3 * bx + 5, oy0 = 3 * by + 5;
+#pragma unroll
+    for (int pl = 0; pl < 2; pl++) {
+      const int16_t* f = pl ? s.f2 : s.f1;
+      int mn = 32767, mx = -32767, pmn = 0, pmx = 0;
+#pragma unroll
+      for (int dy = 0; dy < 3; dy++)
+#pragma unroll
+        for (int dx = 0; dx < 3; dx++) {
+          const int v = f[(oy0 + dy) * OW + ox0 + dx];
+          const int pp = (ox0 + dx) | ((oy0 + dy) << 8);
+          if (v < mn) { mn = v; pmn = pp; }   // strict: first in raster order wins (:199-224)
+          if (v > mx) { mx = v; pmx = pp; }
+        }
+      bool vmn = mn <= -g.tau, vmx = mx >= g.tau;
+      if (vmn) {
+        const int cx = pmn & 255, cy = pmn >> 8;
+#pragma unroll
+        for (int ky = -2; ky <= 2; ky++)
+#pragma unroll
+          for (int kx = -2; kx <= 2; kx++) vmn &= !(f[(cy + ky) * OW + cx + kx] < mn);
+      }
+      if (vmx) {
+        const int cx = pmx & 255, cy = pmx >> 8;
+#pragma unroll
+        for (int ky = -2; ky <= 2; ky++)
+#pragma unroll
+          for (int kx = -2; kx <= 2; kx++) vmx &= !(f[(cy + ky) * OW + cx + kx] > mx);
+      }
+      flag[2 * pl] = vmn; pos[2 * pl] = pmn;
+      flag[2 * pl + 1] = vmx; pos[2 * pl + 1] = pmx;
+    }
+  }
+
+  // ---- ordered compaction: 4 ballots per warp + scan over warps in raster order -----------
+  const int lane = tid & 31, warp = tid >> 5;
+  const uint32_t lt = (1u << lane) - 1u;
+  int rank[4];
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const uint32_t b = __ballot_sync(0xFFFFFFFFu, flag[c]);
+    rank[c] = __popc(b & lt);
+    if (lane == 0) s.warp_tot[warp][c] = __popc(b);
+  }
+  __syncthreads();
+  int total[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int w = 0; w < K1_WARPS; w++)
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      const int t = s.warp_tot[w][c];
+      if (w < warp) rank[c] += t;
+      total[c] += t;
+    }
+
+  const int bj_first = max(y0, 9);
+  if (bj_first >= g.H - 9) return;  // no block row in this tile (grid is sized to avoid it)
+  const int vd = dest_v_bin(g, bj_first);
+  const int bin0 = (vd * g.U + ub) * 4;
+  int32_t* cnt = fa.cnt + (int64_t)slot * fa.cnt_stride;
+  if (tid < 4) cnt[bin0 + tid] = total[tid];
+
+  uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride;
+  uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride;
+  uint4* desc = fa.desc + (int64_t)slot * fa.rec_stride * 2;
+  constexpr int sdx[16] = {-3, -3, -1, -1, 3, 3, 1, 1, -1, -1, 1, 1, -5, -5, 5, 5};
+  constexpr int sdy[16] = {-1, 1, -1, 1, -1, 1, -1, 1, -5, 5, -5, 5, -3, 3, -3, 3};
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    if (!flag[c]) continue;
+    const int ox = pos[c] & 255, oy = pos[c] >> 8;
+    const int64_t rec = (int64_t)(bin0 + c) * g.cap + rank[c];
+    xy[rec] = (uint32_t)(x0 - 5 + ox) | ((uint32_t)(y0 - 5 + oy) << 16);
+    uint32_t tw = kNone;  // lower-class feature sharing this pixel (dedupe key of the reference's M[][])
+    if (c >= 2) {
+      if (flag[0] && pos[0] == pos[c]) tw = (0u << 16) | (uint32_t)rank[0];
+      else if (flag[1] && pos[1] == pos[c]) tw = (1u << 16) | (uint32_t)rank[1];
+    }
+    meta[rec] = tw;
+    uint32_t w[8];
+    const uint16_t* base = &s.duv[oy * OW + ox];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint32_t lo = base[sdy[2 * k] * OW + sdx[2 * k]];
+      const uint32_t hi = base[sdy[2 * k + 1] * OW + sdx[2 * k + 1]];
+      w[k] = lo | (hi << 16);
+    }
+    desc[rec * 2] = make_uint4(w[0], w[1], w[2], w[3]);
+    desc[rec * 2 + 1] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
+}
+
+// Convert a frame slot to the reference's AoS layout (parity dumps, operator-level ABI):
+// max2 int32[bin_num][cap_stride][12] = {u, v, 0, class, 8 descriptor words}; src/size.h:17-20,
+// src/myComputeFeature.cpp:262-270.  Lists longer than cap_stride are truncated and flagged.
+__global__ void k_dump_features(Geom g, FrameArrays fa, int slot, int32_t* __restrict__ max2,
+                                int32_t* __restrict__ max2_num, int cap_stride, int32_t* __restrict__ overflow) {
+  const int bin = blockIdx.x;
+  const int32_t n = fa.cnt[(int64_t)slot * fa.cnt_stride + bin];
+  if (threadIdx.x == 0) {
+    max2_num[bin] = n;
+    if (n > cap_stride) atomicExch(overflow, 1);
+  }
+  const uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
+  const uint4* desc = fa.desc + ((int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap) * 2;
+  for (int k = threadIdx.x; k < min(n, cap_stride); k += blockDim.x) {
+    int32_t* rec = max2 + ((int64_t)bin * cap_stride + k) * 12;
+    const uint32_t p = xy[k];
+    const uint4 a = desc[2 * k], b = desc[2 * k + 1];
+    rec[0] = (int32_t)(p & 0xFFFFu); rec[1] = (int32_t)(p >> 16); rec[2] = 0; rec[3] = bin & 3;
+    rec[4] = (int32_t)a.x; rec[5] = (int32_t)a.y; rec[6] = (int32_t)a.z; rec[7] = (int32_t)a.w;
+    rec[8] = (int32_t)b.x; rec[9] = (int32_t)b.y; rec[10] = (int32_t)b.z; rec[11] = (int32_t)b.w;
+  }
+}
+
+// Inverse of k_dump_features: load reference-layout feature arrays into a frame slot (operator
+// level vo_matching).  The twin links are rebuilt from equal pixels inside a bin.
+__global__ void k_load_features(Geom g, FrameArrays fa, int slot, const int32_t* __restrict__ max2,
+                                const int32_t* __restrict__ max2_num, int cap_stride) {
+  const int bin = blockIdx.x;
+  const int32_t n = min(max2_num[bin], g.cap);
+  if (threadIdx.x == 0) fa.cnt[(int64_t)slot * fa.cnt_stride + bin] = n;
+  uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
+  uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
+  uint4* desc = fa.desc + ((int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap) * 2;
+  const int c = bin & 3;
+  for (int k = threadIdx.x; k < n; k += blockDim.x) {
+    const int32_t* rec = max2 + ((int64_t)bin * cap_stride + k) * 12;
+    xy[k] = (uint32_t)rec[0] | ((uint32_t)rec[1] << 16);
+    desc[2 * k] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+    desc[2 * k + 1] = make_uint4(rec[8], rec[9], rec[10], rec[11]);
+    uint32_t tw = kNone;
+    if (c >= 2) {
+      for (int c2 = 0; c2 < 2 && tw == kNone; c2++) {
+        const int bin2 = (bin & ~3) | c2;
+        const int32_t n2 = min(max2_num[bin2], g.cap);
+        for (int k2 = 0; k2 < n2; k2++) {
+          const int32_t* r2 = max2 + ((int64_t)bin2 * cap_stride + k2) * 12;
+          if (r2[0] == rec[0] && r2[1] == rec[1]) { tw = ((uint32_t)c2 << 16) | (uint32_t)k2; break; }
+        }
+      }
+    }
+    meta[k] = tw;
+  }
+}
+
+size_t k1_smem_bytes() { return sizeof(K1Smem); }
+
+cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
+                      cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k1_extract, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem));
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int rows = g.j_last / BH + 1;  // tile rows that contain at least one block row
+  dim3 grid(g.U, rows, n);
+  k1_extract<<<grid, K1_THREADS, sizeof(K1Smem), st>>>(tmap, g, fa, first_slot, z_base);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t* max2, int32_t* max2_num,
+                        int cap_stride, int32_t* overflow, cudaStream_t st) {
+  k_dump_features<<<g.bin_num, 128, 0, st>>>(g, fa, slot, max2, max2_num, cap_stride, overflow);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
+                        int cap_stride, cudaStream_t st) {
+  k_load_features<<<g.bin_num, 128, 0, st>>>(g, fa, slot, max2, max2_num, cap_stride);
+  return cudaGetLastError();
+}
+
+}  // namespace vo

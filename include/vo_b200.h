@@ -1,0 +1,198 @@
+/* vo_b200.h -- C ABI of the B200-native visual-odometry front end (libvo_b200.so).
+ *
+ * Drop-in boundary for ONE path of Chang-Tun-Yu/HLS-final-Visual-Odometry: feature extraction ->
+ * circular (prev<->curr) descriptor matching -> match bucketing.  Plain pointers and sizes only, no
+ * C++/torch types; every entry point returns a vo_status and never throws.  All device work is
+ * hand-written CUDA for sm_100a; there is NO CPU fallback: if no CUDA device is usable,
+ * vo_engine_create fails with VO_ERR_CUDA and nothing else can be called.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference
+ * checkout).  Three levels, lowest first:
+ *
+ *  1. operator level  == the reference's three `extern "C"` HLS kernels
+ *       vo_compute_features   <- myComputeFeatures   hls_opencl/kernel/myComputeFeature.hpp:19-21
+ *                                                    src/myComputeFeature.cpp:352
+ *       vo_matching           <- myMatching          hls_opencl/kernel/myMatch.hpp:51-57
+ *                                                    src/myMatch.cpp:122
+ *       vo_bucket_matches     <- bucketing half of removeOutliers
+ *                                                    hls_opencl/kernel/remove_outliers.cpp:104-154
+ *                                                    src/matcher.cpp:140-187
+ *  2. Matcher level   == the stateful ring buffer behind Matcher::pushBack / matchFeatures /
+ *       bucketFeatures / getMatches (src/matcher.h:116-143, src/matcher.cpp:51-187)
+ *  3. batch level     == many frames / frame pairs per launch (what the reference's FPGA host
+ *       pipelines by hand, hls_opencl/host/main2.cpp:395-519); this is the throughput path.
+ *
+ * Threading: an engine is not re-entrant; different engines are independent (one CUDA stream
+ * each, or a caller-supplied stream).
+ */
+#ifndef VO_B200_H
+#define VO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum vo_status {
+  VO_OK = 0,
+  VO_ERR_INVALID = 1,      /* bad argument (the reference prints "Image dimension mismatch", src/matcher.cpp:59-62) */
+  VO_ERR_UNSUPPORTED = 2,  /* geometry/parameter outside what the reference path defines */
+  VO_ERR_CUDA = 3,         /* CUDA runtime/driver failure; vo_last_error() has the text */
+  VO_ERR_CAPACITY = 4,     /* an output did not fit the caller's buffer or an engine capacity */
+  VO_ERR_STATE = 5         /* call sequence error (e.g. matching with no previous frame) */
+} vo_status;
+
+/* == Matcher::p_match, src/matcher.h:89-104 (48 bytes, no padding).  The reference's flow matcher
+ * fills u1p,v1p,u1c,v1c with integer-valued floats and every other field with -1
+ * (src/myMatch.cpp:189). */
+typedef struct vo_p_match {
+  float u1p, v1p; int32_t i1p;
+  float u2p, v2p; int32_t i2p;
+  float u1c, v1c; int32_t i1c;
+  float u2c, v2c; int32_t i2c;
+} vo_p_match;
+
+/* Geometry.  The reference hard-wires 1024x284 and these constants in src/size.h:4-22 and
+ * src/myComputeFeature.cpp:157-158; here they are runtime values validated at create time.
+ * Fields left 0 take the reference value. */
+typedef struct vo_config {
+  int32_t width, height;   /* image size in pixels; >= 64 x 64 */
+  int32_t bin_w, bin_h;    /* 60, 45 (must be multiples of 3) */
+  int32_t nms_tau;         /* 50 */
+  int32_t max_frames;      /* frame slots held on the device (>= 2; default 2) */
+  int32_t max_pairs;       /* frame pairs matched per batch call (>= 1; default 1) */
+  int32_t max_matches;     /* capacity of one pair's raw match list (default: generous bound) */
+  int32_t match_rows_per_cta; /* tuning: origin v-bin rows per matching CTA (0 = auto) */
+  int32_t reserved[7];
+} vo_config;
+
+/* Derived geometry (what src/size.h spells as macros). */
+typedef struct vo_geometry {
+  int32_t width, height, pitch;     /* pitch = device row pitch of the frame slots (multiple of 16) */
+  int32_t bin_w, bin_h;
+  int32_t u_bins, v_bins;           /* U_BIN_NUM, V_BIN_NUM */
+  int32_t bin_cap;                  /* MAX_FP_IN_BIN: records per (v_bin,u_bin,class) list = (bin_w/3)*(bin_h/3) */
+  int32_t col_cap;                  /* COL_BIN_FEATURE_MAX = bin_cap * v_bins */
+  int32_t bin_num;                  /* BIN_NUM = u_bins*v_bins*4 */
+  int32_t max_frames, max_pairs, max_matches;
+  int32_t reserved[3];
+} vo_geometry;
+
+typedef struct vo_engine vo_engine;
+
+/* ---------------------------------------------------------------------------------------- */
+/* lifetime                                                                                  */
+/* ---------------------------------------------------------------------------------------- */
+
+/* `stream` is a cudaStream_t passed as void* (NULL: the engine creates its own stream).
+ * Replaces Matcher::Matcher / ~Matcher (src/matcher.cpp:32-49): the engine owns all feature buffers. */
+vo_status vo_engine_create(const vo_config* cfg, int32_t device, void* stream, vo_engine** out);
+void      vo_engine_destroy(vo_engine* e);
+vo_status vo_engine_geometry(const vo_engine* e, vo_geometry* out);
+vo_status vo_engine_synchronize(vo_engine* e);
+const char* vo_last_error(void);            /* thread-local text of the last failure */
+const char* vo_version(void);
+
+/* ---------------------------------------------------------------------------------------- */
+/* 1. operator level (stateless from the caller's point of view; host buffers in, host out)   */
+/* ---------------------------------------------------------------------------------------- */
+
+/* myComputeFeatures(I, max2, max2_num): src/myComputeFeature.cpp:352, layout src/size.h:17-20.
+ *   image     : u8, `pitch_bytes` per row (>= width)
+ *   max2      : int32[bin_num * cap_stride * 12], record {u,v,0,class,8 descriptor words}
+ *   max2_num  : int32[bin_num], bin index (v_bin*u_bins + u_bin)*4 + class
+ *   cap_stride: records per list in the caller's array (MAX_FP_IN_BIN; 160 in the reference).
+ * Returns VO_ERR_CAPACITY (after filling what fits) if a list is longer than cap_stride -- the
+ * reference silently overflows. */
+vo_status vo_compute_features(vo_engine* e, const uint8_t* image, int32_t pitch_bytes,
+                              int32_t* max2, int32_t* max2_num, int32_t cap_stride);
+
+/* myMatching(m1p, m1c, n1p, n1c, p_matched, p_matched_num): src/myMatch.cpp:122.
+ * Feature arrays in the layout above (same cap_stride for both). */
+vo_status vo_matching(vo_engine* e, const int32_t* m1p, const int32_t* n1p, const int32_t* m1c,
+                      const int32_t* n1c, int32_t cap_stride, vo_p_match* p_matched,
+                      int32_t p_matched_cap, int32_t* p_matched_num);
+
+/* Matcher::bucketFeatures on an explicit list (src/matcher.cpp:140-187; FPGA: second half of
+ * removeOutliers, hls_opencl/kernel/remove_outliers.cpp:104-154).  in and out may alias. */
+vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, int32_t max_features,
+                            float bucket_w, float bucket_h, vo_p_match* out, int32_t out_cap,
+                            int32_t* n_out);
+
+/* ---------------------------------------------------------------------------------------- */
+/* 2. Matcher level: a prev/curr ring on frame slots 0/1 of the engine                         */
+/* ---------------------------------------------------------------------------------------- */
+
+/* Matcher::pushBack(I1, I2, dims, replace): src/matcher.cpp:51-91.  dims = {width,height,bytes per
+ * line}; I2 is accepted and ignored exactly as in the reference.  width/height must equal the
+ * engine geometry (the reference ignores dims and uses its compile-time size). */
+vo_status vo_push_back(vo_engine* e, const uint8_t* I1, const uint8_t* I2, const int32_t dims[3],
+                       int32_t replace);
+/* Matcher::matchFeatures(method): src/matcher.cpp:93-111, WITHOUT the host-side Delaunay filter,
+ * which is a separate call (vo_set_matches lets a host removeOutliers stage sit in between).
+ * `method` is accepted and ignored as in the reference.  With fewer than two frames pushed the
+ * result is zero matches (frame-0 contract of hls_opencl/kernel/myMatch.cpp:221-224). */
+vo_status vo_match_features(vo_engine* e, int32_t method);
+/* Matcher::bucketFeatures(max_features, bucket_width, bucket_height): src/matcher.cpp:140-187 */
+vo_status vo_bucket_features(vo_engine* e, int32_t max_features, float bucket_w, float bucket_h);
+/* Matcher::getMatches(): src/matcher.h:138-143 */
+vo_status vo_get_matches(vo_engine* e, vo_p_match* out, int32_t cap, int32_t* n);
+vo_status vo_num_matches(vo_engine* e, int32_t* n);
+/* replace the current match list (e.g. after a host-side removeOutliers, src/remove_outliers.cpp:4) */
+vo_status vo_set_matches(vo_engine* e, const vo_p_match* in, int32_t n);
+/* parity dump of the ring buffer in the reference layout; which: 0 = previous, 1 = current */
+vo_status vo_dump_features(vo_engine* e, int32_t which, int32_t* max2, int32_t* max2_num,
+                           int32_t cap_stride);
+
+/* ---------------------------------------------------------------------------------------- */
+/* 3. batch level                                                                            */
+/* ---------------------------------------------------------------------------------------- */
+
+/* Extract features of `n` frames into frame slots first_slot .. first_slot+n-1 (one launch).
+ * Host variant: frames at images + i*frame_stride_bytes, rows pitch_bytes apart; the H2D copy is
+ * enqueued on the engine stream.  Device variant: same addressing in device memory. */
+vo_status vo_batch_extract_host(vo_engine* e, int32_t first_slot, int32_t n, const uint8_t* images,
+                                int64_t frame_stride_bytes, int32_t pitch_bytes);
+vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n,
+                                  const uint8_t* d_images, int64_t frame_stride_bytes,
+                                  int32_t pitch_bytes);
+/* Match n_pairs pairs (prev_slot[i] -> curr_slot[i]) and, if max_features > 0, bucket each raw
+ * list (bucketing directly follows matching, as in the FPGA operator chain without Delaunay). */
+vo_status vo_batch_match(vo_engine* e, int32_t n_pairs, const int32_t* prev_slot,
+                         const int32_t* curr_slot, int32_t max_features, float bucket_w,
+                         float bucket_h);
+/* Counts of the last vo_batch_match: raw[i], bucketed[i] (either may be NULL). Synchronises. */
+vo_status vo_batch_counts(vo_engine* e, int32_t n_pairs, int32_t* raw, int32_t* bucketed);
+/* Copy pair i's raw (which=0) or bucketed (which=1) list to the host. Synchronises. */
+vo_status vo_batch_get_matches(vo_engine* e, int32_t pair, int32_t which, vo_p_match* out,
+                               int32_t cap, int32_t* n);
+/* Enqueue D2H of all n_pairs count words + lists into caller (ideally pinned) memory without
+ * synchronising: counts int32[2*n_pairs] = {raw, bucketed} per pair; lists laid out
+ * out + i*stride_matches.  which selects raw (0) / bucketed (1) lists. */
+vo_status vo_batch_download_async(vo_engine* e, int32_t n_pairs, int32_t which, int32_t* counts,
+                                  vo_p_match* out, int64_t stride_matches, int32_t max_per_pair);
+/* parity dump of any frame slot in the reference layout */
+vo_status vo_slot_dump_features(vo_engine* e, int32_t slot, int32_t* max2, int32_t* max2_num,
+                                int32_t cap_stride);
+/* number of features in a slot (sum of max2_num) -- for the algorithmic-bytes formula */
+vo_status vo_slot_feature_count(vo_engine* e, int32_t slot, int32_t* n);
+
+/* ---------------------------------------------------------------------------------------- */
+/* instrumentation                                                                           */
+/* ---------------------------------------------------------------------------------------- */
+
+/* Kernels launched by this engine since creation (every launch of one of OUR kernels counts 1). */
+vo_status vo_launch_count(const vo_engine* e, int64_t* n);
+/* Accumulated device time per kernel family, measured with CUDA events on the engine stream while
+ * profiling is enabled: ms[0]=extract ms[1]=match ms[2]=cycle+emit ms[3]=bucket; calls[] likewise. */
+vo_status vo_profile_enable(vo_engine* e, int32_t on);
+vo_status vo_profile_read(vo_engine* e, double ms[4], int64_t calls[4], int32_t reset);
+/* pinned host memory helpers for callers without a CUDA runtime of their own */
+vo_status vo_host_alloc(void** p, int64_t bytes);
+vo_status vo_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VO_B200_H */
