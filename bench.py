@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""bench.py -- frame-pairs/s of the VO front-end hot path (extract -> circular match -> bucket).
+
+Contract (see the task statement):  python bench.py --gpus N --steps K --warmup W  prints ONE JSON
+line from rank 0.  For N > 1 it is launched by torchrun, one rank per GPU; ranks shard INDEPENDENT
+synthetic sequences (no data-path collective, "scaling": "weak").
+
+A step = one batch of B consecutive new frames of a synthetic 1241x376 sequence: B extractions
+(one new frame per pair, the previous frame's features are reused from HBM -- the steady state
+of Matcher::pushBack, /root/reference/src/matcher.cpp:51-91), B circular matchings and B
+bucketings.  `value` times that with the frames already resident in HBM; `e2e` times the same step
+through the C ABI from pinned HOST frames (H2D inside) with the bucketed match lists and counts
+copied back (D2H inside).
+
+--impl reference times the reference's own CPU code for the same path (oracle/_ref, compiled from
+/root/reference/src in place) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+W_DEFAULT, H_DEFAULT = 1241, 376
+METRIC = "frame_pairs_per_s_1241x376"
+UNIT = "frame-pairs/s"
+
+
+# --------------------------------------------------------------------------------------------
+# CPU legs (the only place outside tests/ and smoke() that touches oracle/)
+# --------------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    """Process n consecutive pairs of one synthetic sequence with the reference code; returns
+    (pairs, seconds, kind)."""
+    width, height, seed, n_pairs = args
+    from hls_final_visual_odometry_b200.synth import make_sequence
+    from oracle.oracle_lib import Oracle
+    from oracle.ref_lib import RefLib, have_ref
+
+    seq = make_sequence(width, height, n_pairs + 1, seed=seed)
+    tag = f"{width}x{height}"
+    orc = Oracle(width, height)
+    if have_ref(tag):
+        ref = RefLib(tag)
+        kind = "reference"
+        extract = lambda img: ref.compute_features(img)  # noqa: E731
+        match = lambda a, b: ref.matching(a[0], a[1], b[0], b[1])  # noqa: E731
+    else:
+        kind = "port"
+        extract = lambda img: orc.compute_features(img)[:2]  # noqa: E731
+        match = lambda a, b: orc.matching(a[0], a[1], b[0], b[1])[0]  # noqa: E731
+    prev = extract(seq[0])  # untimed: steady state has the previous frame's features already
+    t0 = time.perf_counter()
+    for i in range(1, n_pairs + 1):
+        cur = extract(seq[i])
+        raw = match(prev, cur)
+        # the reference's bucketFeatures keeps its buckets in a fixed [126][256] stack array
+        # (src/matcher.cpp:154-155) that overflows at this image size, so the (sub-millisecond)
+        # bucketing stage of the CPU leg runs through the oracle port
+        orc.bucket_features(raw, 2, 50.0, 50.0)
+        prev = cur
+    return n_pairs, time.perf_counter() - t0, kind
+
+
+def cpu_throughput(width, height, pairs_per_worker, workers):
+    """Aggregate pairs/s of `workers` independent single-threaded reference processes."""
+    import multiprocessing as mp
+    ctx = mp.get_context("fork")
+    jobs = [(width, height, 100 + i, pairs_per_worker) for i in range(workers)]
+    t0 = time.perf_counter()
+    with ctx.Pool(workers) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    slowest = max(r[1] for r in res)
+    total = sum(r[0] for r in res)
+    return total / slowest, res[0][2], wall, total
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    workers = max(1, min(cores, 64))
+    pairs_per_worker = 2
+    vals = []
+    kind = "reference"
+    for s in range(args.warmup + args.steps):
+        v, kind, _, total = cpu_throughput(args.width, args.height, pairs_per_worker, workers)
+        if s >= args.warmup:
+            vals.append(v)
+    value = float(np.mean(vals)) if vals else 0.0
+    sample = (f"{workers} single-threaded processes x {pairs_per_worker} consecutive pairs per step of the "
+              f"{args.width}x{args.height} synthetic sequence: myComputeFeatures + myMatching "
+              f"({'oracle/_ref, reference sources compiled in place' if kind == 'reference' else 'oracle port'})"
+              f" + bucketing (oracle port)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * workers * pairs_per_worker / value if value else None,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": f"configs[1]: {args.width}x{args.height} frame pairs, extract+match+bucket",
+                   "pairs_per_step": workers * pairs_per_worker},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+
+    from hls_final_visual_odometry_b200 import Engine, pinned_empty
+    from hls_final_visual_odometry_b200.api import P_MATCH_DTYPE
+    from hls_final_visual_odometry_b200.synth import frame_from_canvas, make_canvas
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+
+    W, H, B = args.width, args.height, args.batch
+    pitch = (W + 15) & ~15
+    pool_frames = max(args.pool, 2 * B)
+    pool_frames = (pool_frames + B - 1) // B * B       # whole steps
+    # ---- synthetic sequence of this rank (independent sequences: seed 1 + rank) ------------
+    canvas = make_canvas(W, H, seed=1 + rank)
+    host_pool = pinned_empty((pool_frames, H, pitch), np.uint8)
+    host_pool[:] = 0
+    for f in range(pool_frames):
+        host_pool[f, :, :W] = frame_from_canvas(canvas, W, H, f)
+    dev_pool = torch.from_numpy(host_pool).cuda()        # HBM-resident copy, TMA-friendly pitch
+    stream = torch.cuda.current_stream()
+    eng = Engine(W, H, max_frames=2 * B, max_pairs=B, device=local_rank, stream=stream.cuda_stream,
+                 match_rows_per_cta=args.rows)
+    max_keep = 512
+    counts = pinned_empty((2 * B,), np.int32)
+    out_lists = pinned_empty((B, max_keep), P_MATCH_DTYPE)
+
+    def slots_of(step):
+        base = (step % 2) * B
+        curr = (base + np.arange(B)) % (2 * B)
+        prev = (curr - 1) % (2 * B)
+        return base, prev.astype(np.int32), curr.astype(np.int32)
+
+    def step_device(step):
+        base, prev, curr = slots_of(step)
+        f0 = (step * B) % pool_frames
+        eng.batch_extract_device(base, dev_pool.data_ptr() + f0 * H * pitch, B, H * pitch, pitch)
+        eng.batch_match(prev, curr, 2, 50.0, 50.0)
+
+    def step_e2e(step):
+        base, prev, curr = slots_of(step)
+        f0 = (step * B) % pool_frames
+        eng.batch_extract_host(base, host_pool[f0:f0 + B])
+        eng.batch_match(prev, curr, 2, 50.0, 50.0)
+        eng.batch_download_async(B, 1, counts, out_lists, max_keep, max_keep)
+        eng.synchronize()                                  # the step's result is on the host
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, first_step):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for s in range(args.steps):
+            fn(first_step + s)
+        e1.record(stream)
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms, wall * 1e3], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1]) / 1e3
+        return ms, wall
+
+    # ---- warm-up (fills the ring so every timed pair has a real previous frame) ------------
+    for s in range(max(args.warmup, 3)):
+        step_device(s)
+    step0 = max(args.warmup, 3)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches0 = eng.launch_count()
+    eng.profile_enable(True)
+    eng.profile_read(reset=True)
+    dev_ms, _ = timed(step_device, step0)
+    prof = eng.profile_read(reset=True)
+    eng.profile_enable(False)
+    launches = eng.launch_count() - launches0
+    raw_n, bk_n = eng.batch_counts(B)
+    n_feat = [eng.slot_feature_count(s) for s in range(0, 2 * B, max(1, (2 * B) // 8))]
+    for s in range(3):
+        step_e2e(step0 + args.steps + s)
+    e2e_ms, e2e_wall = timed(step_e2e, step0 + args.steps + 3)
+    e2e_ms = max(e2e_ms, e2e_wall * 1e3)                  # host-visible completion is what counts
+    clocks = sampler.stop() if sampler else None
+
+    pairs_per_step = B * world
+    value = pairs_per_step * args.steps / (dev_ms / 1e3)
+    e2e_value = pairs_per_step * args.steps / (e2e_ms / 1e3)
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (k2_match) ----------------------------------------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    if os.path.exists(peaks_path):
+        try:
+            peak = float(json.load(open(peaks_path))["hbm_gbs"]); peak_src = "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    n_c = float(np.mean(n_feat)); n_m = float(np.mean(raw_n)); n_b = float(np.mean(bk_n))
+    # algorithmic bytes per pair
+    b_pair = W * H + 48 * n_c + 48 * (2 * n_c) + 48 * n_m + 48 * n_m + 48 * n_b
+    b_match = 48 * (2 * n_c) + 4 * (2 * n_c)              # k2: both feature lists in, one best-id per origin out
+    k2_ms, k2_calls = prof["match"]
+    k2_avg_s = k2_ms / max(k2_calls, 1) / 1e3
+    achieved = b_match * B / k2_avg_s / 1e9 if k2_avg_s > 0 else 0.0
+    step_ms = dev_ms / args.steps
+    fam = {k: (v[0] / max(v[1], 1)) for k, v in prof.items()}
+    roofline = {
+        "kernel": "k2_match", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": b_match * B, "avg_launch_ms": k2_avg_s * 1e3,
+        "share_of_step": (k2_avg_s * 1e3) / step_ms if step_ms else None,
+        "kernel_ms_per_step": fam,
+        "path": {"bytes_per_pair": b_pair, "achieved": b_pair * value / world / 1e9, "frac": b_pair * value / world / 1e9 / peak},
+        "note": "SAD matching is integer-pipe bound (about 100 int ops per algorithmic byte, SURVEY.md row D3); "
+                "the HBM fraction is reported because BASELINE.json's metric asks for it",
+    }
+
+    # ---- CPU baseline on this box's host cores (bounded sample) ----------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cores = max(1, min(os.cpu_count() or 1, 64))
+        v, kind, wall, total = cpu_throughput(W, H, 2, cores)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": f"{cores} single-threaded processes x 2 consecutive pairs ({total} pairs, {wall:.1f} s wall) of "
+                         f"the same {W}x{H} synthetic sequence type: myComputeFeatures+myMatching from oracle/_ref, "
+                         f"bucketing via the oracle port"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": f"configs[1]: {W}x{H} frame pairs, extract+match+bucket, batch of {B} consecutive frames per step per GPU",
+                   "pairs_per_step": pairs_per_step, "batch_per_gpu": B, "bucket": "2 per 50x50",
+                   "l2": f"inputs larger than L2: pool of {pool_frames} frames ({pool_frames * H * pitch / 1e6:.0f} MB) cycled",
+                   "features_per_frame": n_c, "raw_matches_per_pair": n_m, "bucketed_per_pair": n_b,
+                   "sharding": "independent sequences per GPU, no collective"},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * H * W) * world,
+                "d2h_bytes_per_step": int(counts.nbytes + B * max_keep * 48) * world,
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(launches) * world,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=W_DEFAULT)
+    ap.add_argument("--height", type=int, default=H_DEFAULT)
+    ap.add_argument("--batch", type=int, default=64, help="frame pairs per step per GPU")
+    ap.add_argument("--pool", type=int, default=320, help="distinct frames cycled (keeps inputs larger than L2)")
+    ap.add_argument("--rows", type=int, default=0, help="match_rows_per_cta tuning knob (0 = library default)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus != world and world == 1 and args.gpus > 1:
+        # convenience: re-launch under torchrun when called directly with --gpus N
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -21,7 +21,7 @@ cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t*
 cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
                         int cap_stride, cudaStream_t st);
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
-                      int rows_per_group, int cand_cap, cudaStream_t st);
+                      int rows_per_group, int prune, cudaStream_t st);
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
                       uint8_t* flags, int32_t* list_cnt, void* out, int64_t out_stride_matches, int32_t max_matches,
                       int32_t* n_raw, int32_t* status, cudaStream_t st);
@@ -68,7 +68,7 @@ struct vo_engine {
   bool own_stream = false;
   int n_slots = 0, n_pairbuf = 0;       // incl. the operator-level scratch slots / pair
   int op_slot_a = 0, op_slot_b = 0, op_pair = 0;
-  int rows_per_group = 0, cand_cap = 0;
+  int rows_per_group = 0, prune = 1;
   vo::FrameArrays fa{};
   CUtensorMap tmap_slots;
   // pair buffers
@@ -218,7 +218,7 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
   {
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
-                         e->rows_per_group, e->cand_cap, e->stream));
+                         e->rows_per_group, e->prune, e->stream));
     e->launches += 1;
   }
   {
@@ -317,9 +317,8 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   e->cfg = cfg;
   e->n_slots = cfg.max_frames + 2; e->op_slot_a = cfg.max_frames; e->op_slot_b = cfg.max_frames + 1;
   e->n_pairbuf = cfg.max_pairs + 1; e->op_pair = cfg.max_pairs;
-  e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : 3;
-  e->cand_cap = 2560;  // >= 6*cap (one full row of the window always fits)
-  if (e->cand_cap < 6 * g.cap) e->cand_cap = 6 * g.cap;
+  e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : g.V;
+  e->prune = cfg.match_exhaustive ? 0 : 1;
 
   if (stream) { e->stream = (cudaStream_t)stream; e->own_stream = false; }
   else {
@@ -342,6 +341,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   ALLOC(e->fa.xy, sizeof(uint32_t) * S * e->fa.rec_stride);
   ALLOC(e->fa.meta, sizeof(uint32_t) * S * e->fa.rec_stride);
   ALLOC(e->fa.desc, sizeof(uint4) * 2 * S * e->fa.rec_stride);
+  ALLOC(e->fa.q, sizeof(uint2) * S * e->fa.rec_stride);
   cudaMemsetAsync(e->fa.cnt, 0, sizeof(int32_t) * S * e->fa.cnt_stride, e->stream);
   cudaMemsetAsync(e->fa.img, 0, (size_t)(S * e->fa.img_stride + 256), e->stream);
   const int64_t lists = (int64_t)g.U * 4 * g.col_cap;
@@ -388,7 +388,7 @@ void vo_engine_destroy(vo_engine* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
-  cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc);
+  cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc); cudaFree(e->fa.q);
   cudaFree(e->d_pairs); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
   cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);

@@ -190,6 +190,7 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
   uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride;
   uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride;
   uint4* desc = fa.desc + (int64_t)slot * fa.rec_stride * 2;
+  uint2* qsig = fa.q + (int64_t)slot * fa.rec_stride;
   constexpr int sdx[16] = {-3, -3, -1, -1, 3, 3, 1, 1, -1, -1, 1, 1, -5, -5, 5, 5};
   constexpr int sdy[16] = {-1, 1, -1, 1, -1, 1, -1, 1, -5, 5, -5, 5, -3, 3, -3, 3};
 #pragma unroll
@@ -212,8 +213,10 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
       const uint32_t hi = base[sdy[2 * k + 1] * OW + sdx[2 * k + 1]];
       w[k] = lo | (hi << 16);
     }
-    desc[rec * 2] = make_uint4(w[0], w[1], w[2], w[3]);
-    desc[rec * 2 + 1] = make_uint4(w[4], w[5], w[6], w[7]);
+    const uint4 d0 = make_uint4(w[0], w[1], w[2], w[3]), d1 = make_uint4(w[4], w[5], w[6], w[7]);
+    desc[rec * 2] = d0;
+    desc[rec * 2 + 1] = d1;
+    qsig[rec] = desc_q(d0, d1);
   }
 }
 
@@ -250,12 +253,15 @@ __global__ void k_load_features(Geom g, FrameArrays fa, int slot, const int32_t*
   uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
   uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
   uint4* desc = fa.desc + ((int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap) * 2;
+  uint2* qsig = fa.q + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
   const int c = bin & 3;
   for (int k = threadIdx.x; k < n; k += blockDim.x) {
     const int32_t* rec = max2 + ((int64_t)bin * cap_stride + k) * 12;
     xy[k] = (uint32_t)rec[0] | ((uint32_t)rec[1] << 16);
-    desc[2 * k] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
-    desc[2 * k + 1] = make_uint4(rec[8], rec[9], rec[10], rec[11]);
+    const uint4 d0 = make_uint4(rec[4], rec[5], rec[6], rec[7]), d1 = make_uint4(rec[8], rec[9], rec[10], rec[11]);
+    desc[2 * k] = d0;
+    desc[2 * k + 1] = d1;
+    qsig[k] = desc_q(d0, d1);
     uint32_t tw = kNone;
     if (c >= 2) {
       for (int c2 = 0; c2 < 2 && tw == kNone; c2++) {

@@ -13,6 +13,8 @@
 // the range, each candidate costing 8 VABSDIFF4.U8.ACC (packed-byte SAD) + a packed window test,
 // and keeps min(SAD<<19 | u_rel<<16 | col_idx), which is exactly the reference's "strict <,
 // first candidate in (u_bin asc, col_idx asc) order wins".  One REDUX.MIN per origin.
+// Optional exact pruning (PRUNE): a 2-instruction lower bound of the SAD (see desc_q) skips the
+// 8-instruction exact SAD for candidates that provably cannot win or tie; results are identical.
 // SAD is not a contraction: no tensor cores here by design.
 //
 // K3 (k3_flags, k3_emit): closed-cycle test, same-pixel dedupe (lowest class wins, via the twin
@@ -23,8 +25,9 @@ namespace vo {
 
 constexpr int K2_THREADS = 512;
 constexpr int K2_WARPS = K2_THREADS / 32;
-constexpr int kMaxV = 64;     // v-bin rows supported by the shared-memory tables
-constexpr int kMaxCols = 6;   // target u-bin columns: [ub-3, ub+3) clipped
+constexpr int kMaxV = 64;       // v-bin rows supported by the shared-memory tables
+constexpr int kMaxCols = 6;     // target u-bin columns: [ub-3, ub+3) clipped
+constexpr int kCandCap = 2176;  // staged candidates per chunk; >= 6*300 so one window row always fits
 
 struct K2Tables {
   int32_t cntT[kMaxV][kMaxCols];      // target counts (row, rel. column)
@@ -33,17 +36,35 @@ struct K2Tables {
   int32_t stageOff[kMaxV + 1];        // staged position of the first candidate of a row (chunk-relative)
   int32_t cntO[kMaxV];
   int32_t prefO[kMaxV + 1];
+  int32_t lagEnd[kMaxV];              // origins o < lagEnd[v] of row v may carry a lagging v_bin (slow path)
+  int32_t posLo[kMaxV], posHi[kMaxV]; // staged candidate range of a non-lagging origin of row v (this chunk)
 };
 
-__host__ __device__ inline size_t k2_smem_bytes(int cand_cap) {
-  return sizeof(K2Tables) + 128 + (size_t)cand_cap * (16 + 16 + 8);
-}
+template <bool PRUNE>
+struct __align__(128) K2Smem {
+  K2Tables t;
+  __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
+  uint4 hi[kCandCap];                 // descriptor bytes 16..31
+  uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
+  uint2 q[PRUNE ? kCandCap : 1];      // 8 quantised group sums (lower-bound filter)
+};
 
 // acc + sum of |a_i - b_i| over the four packed bytes: one VABSDIFF4.U8.ACC
 __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) {
   uint32_t d;
   asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
   return d;
+}
+
+__device__ __forceinline__ uint32_t sad32(const uint4& a, const uint4& b, const uint4& x, const uint4& y) {
+  uint32_t s = sad4(a.x, x.x, 0u);
+  s = sad4(a.y, x.y, s);
+  s = sad4(a.z, x.z, s);
+  s = sad4(a.w, x.w, s);
+  s = sad4(b.x, y.x, s);
+  s = sad4(b.y, y.y, s);
+  s = sad4(b.z, y.z, s);
+  return sad4(b.w, y.w, s);
 }
 
 // v_buffer_idx of the reference (src/myMatch.cpp:153-158): starts at 0, bumped at most once per
@@ -55,15 +76,13 @@ __device__ __forceinline__ int origin_vb(const K2Tables& t, int col_idx, int v) 
   return vb;
 }
 
+template <bool PRUNE>
 __global__ void __launch_bounds__(K2_THREADS, 2)
 k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __restrict__ best, int rows_per_group,
-         int ngroups, int cand_cap) {
+         int ngroups) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
-  K2Tables& t = *reinterpret_cast<K2Tables*>(smem_raw);
-  uint8_t* p = smem_raw + ((sizeof(K2Tables) + 127) & ~size_t(127));
-  uint4* sLo = reinterpret_cast<uint4*>(p);
-  uint4* sHi = sLo + cand_cap;
-  uint2* sXR = reinterpret_cast<uint2*>(sHi + cand_cap);  // {xy + 0x80008000, u_rel<<16 | col_idx}
+  K2Smem<PRUNE>& S = *reinterpret_cast<K2Smem<PRUNE>*>(smem_raw);
+  K2Tables& t = S.t;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ub = blockIdx.x / ngroups, grp = blockIdx.x - ub * ngroups;
@@ -98,6 +117,12 @@ k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __res
     t.rowTot[v] = acc;
   }
   __syncthreads();
+  if (tid < V) {  // first origin index of row v whose v_bin is the nominal v+1 (see origin_vb)
+    int le = tid;
+    for (int b = 0; b < tid; b++)
+      if (t.cntO[b] > 0) le = max(le, t.prefO[b + 1] + tid - 1 - b);
+    t.lagEnd[tid] = le;
+  }
 
   const int r0 = grp * rows_per_group, r1 = min(r0 + rows_per_group, V);
   const int o_begin = t.prefO[r0], o_end = t.prefO[r1];
@@ -114,21 +139,29 @@ k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __res
   const uint4* desc_from = fa.desc + (int64_t)from_slot * fa.rec_stride * 2;
   const uint32_t* xy_to = fa.xy + (int64_t)to_slot * fa.rec_stride;
   const uint4* desc_to = fa.desc + (int64_t)to_slot * fa.rec_stride * 2;
+  const uint2* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
+  const uint2* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
   uint32_t* best_out = best + ((int64_t)(blockIdx.z * 2 + dir) * U * 4 + (ub * 4 + c)) * g.col_cap;
+  const int rec_row_stride = U * 4 * g.cap;              // records between consecutive rows of one (u,c)
+  const int rec_col0 = (ub * 4 + c) * g.cap;             // record index of row 0 of the origin column
 
   bool first_chunk = true;
-  for (int ra = row_lo; ra < row_hi || first_chunk;) {
+  for (int ra = row_lo;;) {
     // ---- chunk = as many whole rows as fit the staging buffer ------------------------------
     int rb = ra, staged = 0;
-    while (rb < row_hi && staged + t.rowTot[rb] <= cand_cap) { staged += t.rowTot[rb]; rb++; }
-    if (rb == ra && ra < row_hi) rb = ra + 1;  // cannot happen: launch guarantees cand_cap >= 6*cap
-    __syncthreads();  // previous chunk fully consumed
+    while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
+    __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
     if (tid == 0) {
       int acc = 0;
       for (int v = ra; v < rb; v++) { t.stageOff[v] = acc; acc += t.rowTot[v]; }
       t.stageOff[rb] = acc;
     }
     __syncthreads();
+    if (tid < V) {  // nominal window of row tid: v-bins [v-2, v+4) clipped (vb = v+1)
+      const int vlo = max(max(tid - 2, 0), ra), vhi = min(min(tid + 4, V - 1), rb);
+      t.posLo[tid] = (vlo < vhi) ? t.stageOff[vlo] : 0;
+      t.posHi[tid] = (vlo < vhi) ? t.stageOff[vhi] : 0;
+    }
     // ---- stage: warp per (row, column) bin list, coalesced 16-byte copies ------------------
     for (int b = warp; b < (rb - ra) * ncol; b += K2_WARPS) {
       const int v = ra + b / ncol, j = b % ncol;
@@ -138,46 +171,108 @@ k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __res
       const int64_t src = (int64_t)((v * U + ulo + j) * 4 + c) * g.cap;
       const uint32_t rank0 = ((uint32_t)j << 16) | (uint32_t)t.colT[j][v];
       for (int k = lane; k < n; k += 32) {
-        sLo[dst + k] = desc_to[(src + k) * 2];
-        sHi[dst + k] = desc_to[(src + k) * 2 + 1];
-        sXR[dst + k] = make_uint2(xy_to[src + k] + 0x80008000u, rank0 + (uint32_t)k);
+        const uint4 d0 = desc_to[(src + k) * 2], d1 = desc_to[(src + k) * 2 + 1];
+        S.lo[dst + k] = d0;
+        S.hi[dst + k] = d1;
+        S.xr[dst + k] = make_uint2(xy_to[src + k] + 0x80008000u, rank0 + (uint32_t)k);
+        if (PRUNE) S.q[dst + k] = q_to[src + k];
       }
     }
     __syncthreads();
 
-    // ---- origins: one warp each ------------------------------------------------------------
-    int v = v_first;
-    for (int o = o_begin + warp; o < o_end; o += K2_WARPS) {
-      while (t.prefO[v + 1] <= o) v++;
-      const int k = o - t.prefO[v];
-      const int vb = origin_vb(t, o, v);
-      const int vlo = max(max(vb - 3, 0), ra), vhi = min(min(vb + 3, V - 1), rb);
+    // ---- origins: one warp each, next origin's record prefetched while this one is matched ---
+    int o = o_begin + warp, vl = v_first;
+    uint32_t n_xy = 0;
+    uint4 n_a = make_uint4(0, 0, 0, 0), n_b = n_a;
+    uint2 n_q = make_uint2(0, 0);
+    if (o < o_end) {
+      while (t.prefO[vl + 1] <= o) vl++;
+      const int rec = rec_col0 + vl * rec_row_stride + (o - t.prefO[vl]);
+      n_xy = __ldg(&xy_from[rec]); n_a = __ldg(&desc_from[2 * rec]); n_b = __ldg(&desc_from[2 * rec + 1]);
+      if (PRUNE) n_q = __ldg(&q_from[rec]);
+    }
+    while (o < o_end) {
+      const uint32_t oxy = n_xy;
+      const uint4 a = n_a, b = n_b;
+      const uint2 qa = n_q;
+      const int v = vl;  // row of origin o (found when it was prefetched)
+      const int on = o + K2_WARPS;
+      if (on < o_end) {
+        while (t.prefO[vl + 1] <= on) vl++;
+        const int rec = rec_col0 + vl * rec_row_stride + (on - t.prefO[vl]);
+        n_xy = __ldg(&xy_from[rec]); n_a = __ldg(&desc_from[2 * rec]); n_b = __ldg(&desc_from[2 * rec + 1]);
+        if (PRUNE) n_q = __ldg(&q_from[rec]);
+      }
+      int lo, hi;
+      if (o >= t.lagEnd[v]) {
+        lo = t.posLo[v]; hi = t.posHi[v];
+      } else {  // rare: the first origins after empty bins carry a lagging v_bin
+        const int vb = origin_vb(t, o, v);
+        const int vlo = max(max(vb - 3, 0), ra), vhi = min(min(vb + 3, V - 1), rb);
+        lo = (vlo < vhi) ? t.stageOff[vlo] : 0;
+        hi = (vlo < vhi) ? t.stageOff[vhi] : 0;
+      }
+      const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
+      // packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
+      const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);
+      const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
       uint32_t bestk = kNone;
-      if (vlo < vhi) {
-        const int64_t orec = (int64_t)((v * U + ub) * 4 + c) * g.cap + k;
-        const uint32_t oxy = __ldg(&xy_from[orec]);
-        const uint4 a = __ldg(&desc_from[orec * 2]), b = __ldg(&desc_from[orec * 2 + 1]);
-        const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
-        // packed window test: fields carry a guard bit (bit 15); see DESIGN.md "window test"
-        const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);
-        const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
-        const int pos_end = t.stageOff[vhi];
-#pragma unroll 2
-        for (int pos = t.stageOff[vlo] + lane; pos < pos_end; pos += 32) {
-          const uint4 x = sLo[pos], y = sHi[pos];
-          const uint2 xr = sXR[pos];
-          uint32_t sad = sad4(a.x, x.x, 0u);
-          sad = sad4(a.y, x.y, sad);
-          sad = sad4(a.z, x.z, sad);
-          sad = sad4(a.w, x.w, sad);
-          sad = sad4(b.x, y.x, sad);
-          sad = sad4(b.y, y.y, sad);
-          sad = sad4(b.z, y.z, sad);
-          sad = sad4(b.w, y.w, sad);
+      if (!PRUNE) {
+#pragma unroll 4
+        for (int pos = lo + lane; pos < hi; pos += 32) {
+          const uint2 xr = S.xr[pos];
+          const uint32_t sad = sad32(a, b, S.lo[pos], S.hi[pos]);
           const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
-          const bool ok = ((t1 & ~t2) & 0x80008000u) == 0x80008000u;
-          const uint32_t key = ok ? ((sad << 19) | xr.y) : kNone;
-          bestk = min(bestk, key);
+          const uint32_t key = sad * 0x80000u + xr.y;
+          if (((t1 & ~t2) & 0x80008000u) == 0x80008000u) bestk = min(bestk, key);
+        }
+      } else {
+        // pass 1: the candidate with the smallest lower bound, per lane
+        uint32_t k1 = kNone;
+#pragma unroll 4
+        for (int pos = lo + lane; pos < hi; pos += 32) {
+          const uint2 q = S.q[pos];
+          const uint32_t Q = sad4(qa.y, q.y, sad4(qa.x, q.x, 0u));
+          k1 = min(k1, Q * 0x100000u + (uint32_t)(pos - lo));
+        }
+        uint32_t tq = 0;
+        // exact SAD + window test of one staged candidate; tightens this lane's bound
+        auto exact = [&](int pos) {
+          const uint2 xr = S.xr[pos];
+          const uint32_t sad = sad32(a, b, S.lo[pos], S.hi[pos]);
+          const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
+          const uint32_t key = sad * 0x80000u + xr.y;
+          if (((t1 & ~t2) & 0x80008000u) == 0x80008000u && key < bestk) {
+            bestk = key;
+            tq = min(tq, (sad + 24u) >> 2);
+          }
+        };
+        tq = kNone;
+        if (k1 != kNone) exact(lo + (int)(k1 & 0xFFFFFu));
+        // any candidate that can still win (or tie) has 4Q-24 <= best SAD so far
+        uint32_t tsad = __reduce_min_sync(0xFFFFFFFFu, bestk) >> 19;
+        if (!first_chunk) tsad = min(tsad, best_out[o] >> 19);
+        tq = (tsad + 24u) >> 2;
+        // pass 2: exact SAD only where the bound allows; four candidates share one branch
+        int pos = lo + lane;
+        for (; pos + 96 < hi; pos += 128) {
+          const uint2 q0 = S.q[pos], q1 = S.q[pos + 32], q2 = S.q[pos + 64], q3 = S.q[pos + 96];
+          const uint32_t Q0 = sad4(qa.y, q0.y, sad4(qa.x, q0.x, 0u));
+          const uint32_t Q1 = sad4(qa.y, q1.y, sad4(qa.x, q1.x, 0u));
+          const uint32_t Q2 = sad4(qa.y, q2.y, sad4(qa.x, q2.x, 0u));
+          const uint32_t Q3 = sad4(qa.y, q3.y, sad4(qa.x, q3.x, 0u));
+          if (min(min(Q0, Q1), min(Q2, Q3)) <= tq) {
+            if (Q0 <= tq) exact(pos);
+            if (Q1 <= tq) exact(pos + 32);
+            if (Q2 <= tq) exact(pos + 64);
+            if (Q3 <= tq) exact(pos + 96);
+          }
+        }
+#pragma unroll 1
+        for (; pos < hi; pos += 32) {
+          const uint2 q = S.q[pos];
+          const uint32_t Q = sad4(qa.y, q.y, sad4(qa.x, q.x, 0u));
+          if (Q <= tq) exact(pos);
         }
       }
       bestk = __reduce_min_sync(0xFFFFFFFFu, bestk);
@@ -185,6 +280,7 @@ k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __res
         if (!first_chunk) bestk = min(bestk, best_out[o]);
         best_out[o] = bestk;
       }
+      o = on;
     }
     first_chunk = false;
     ra = rb;
@@ -353,19 +449,26 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
   }
 }
 
-cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
-                      int rows_per_group, int cand_cap, cudaStream_t st) {
-  static int attr_bytes = 0;
-  const int bytes = (int)k2_smem_bytes(cand_cap);
-  if (bytes > attr_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(k2_match, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+template <bool PRUNE>
+static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
+                               int rows_per_group, cudaStream_t st) {
+  static bool attr_set = false;
+  const int bytes = (int)sizeof(K2Smem<PRUNE>);
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k2_match<PRUNE>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
-    attr_bytes = bytes;
+    attr_set = true;
   }
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   dim3 grid((g.U - 1) * ngroups, 8, n_pairs);
-  k2_match<<<grid, K2_THREADS, bytes, st>>>(g, fa, pairs, best, rows_per_group, ngroups, cand_cap);
+  k2_match<PRUNE><<<grid, K2_THREADS, bytes, st>>>(g, fa, pairs, best, rows_per_group, ngroups);
   return cudaGetLastError();
+}
+
+cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
+                      int rows_per_group, int prune, cudaStream_t st) {
+  return prune ? launch_k2_t<true>(g, fa, pairs, n_pairs, best, rows_per_group, st)
+               : launch_k2_t<false>(g, fa, pairs, n_pairs, best, rows_per_group, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,

@@ -63,8 +63,10 @@ typedef struct vo_config {
   int32_t max_frames;      /* frame slots held on the device (>= 2; default 2) */
   int32_t max_pairs;       /* frame pairs matched per batch call (>= 1; default 1) */
   int32_t max_matches;     /* capacity of one pair's raw match list (default: generous bound) */
-  int32_t match_rows_per_cta; /* tuning: origin v-bin rows per matching CTA (0 = auto) */
-  int32_t reserved[7];
+  int32_t match_rows_per_cta; /* tuning: origin v-bin rows per matching CTA (0 = auto: whole column) */
+  int32_t match_exhaustive;   /* 0: exact lower-bound pruning in the SAD search (default); 1: evaluate every SAD.
+                                 Results are bit-identical either way. */
+  int32_t reserved[6];
 } vo_config;
 
 /* Derived geometry (what src/size.h spells as macros). */

@@ -34,12 +34,15 @@ def assert_matches_equal(got, want, tag=""):
                 raise AssertionError(f"{tag}: match {i} differs\n got {got[i]}\nwant {want[i]}")
 
 
-@pytest.fixture(scope="module", params=SIZES, ids=lambda s: f"{s[0]}x{s[1]}")
+CASES = [(w, h, ex) for (w, h) in SIZES for ex in (False, True)]
+
+
+@pytest.fixture(scope="module", params=CASES, ids=lambda s: f"{s[0]}x{s[1]}-{'exhaustive' if s[2] else 'pruned'}")
 def setup(request):
-    w, h = request.param
+    w, h, exhaustive = request.param
     seq = make_sequence(w, h, 3, seed=0)
     orc = Oracle(w, h)
-    eng = Engine(w, h, max_frames=4, max_pairs=2)
+    eng = Engine(w, h, max_frames=4, max_pairs=2, match_exhaustive=exhaustive)
     yield w, h, seq, orc, eng
     eng.close()
 
