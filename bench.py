@@ -203,7 +203,11 @@ def run_ours(args):
     for f in range(pool_frames):
         host_pool[f, :, :W] = frame_from_canvas(canvas, W, H, f)
     dev_pool = torch.from_numpy(host_pool).cuda()        # HBM-resident copy, TMA-friendly pitch
-    stream = torch.cuda.current_stream()
+    torch.cuda.synchronize()
+    # the engine launches on THIS torch stream, so torch.cuda.Event timing brackets our kernels
+    # (torch's default stream has handle 0, which the C ABI reads as "create your own stream")
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     eng = Engine(W, H, max_frames=2 * B, max_pairs=B, device=local_rank, stream=stream.cuda_stream,
                  match_rows_per_cta=args.rows)
     max_keep = 512

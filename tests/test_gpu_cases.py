@@ -1,0 +1,171 @@
+"""GPU: adversarial inputs, reference-golden digests, capacity/err behaviour, device-resident inputs."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import cases
+from hls_final_visual_odometry_b200 import Engine, VoError
+from hls_final_visual_odometry_b200 import api
+from hls_final_visual_odometry_b200.synth import make_sequence
+from oracle.oracle_lib import Oracle, features_digest, matches_digest
+from test_gpu_parity import assert_features_equal, assert_matches_equal
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = json.load(open(os.path.join(HERE, "golden", "golden.json")))
+
+
+@pytest.mark.parametrize("size", [(1024, 284), (500, 150)], ids=lambda s: f"{s[0]}x{s[1]}")
+@pytest.mark.parametrize("name", sorted(cases.CASES))
+def test_adversarial_vs_oracle(name, size):
+    w, h = size
+    prev, curr = cases.CASES[name](w, h, 0)
+    orc = Oracle(w, h)
+    eng = Engine(w, h, max_frames=2, max_pairs=1)
+    try:
+        fp = orc.compute_features(prev)[:2]
+        fc = orc.compute_features(curr)[:2]
+        eng.batch_extract_host(0, np.stack([prev, curr]))
+        assert_features_equal(eng.slot_dump_features(0), fp, f"{name} prev")
+        assert_features_equal(eng.slot_dump_features(1), fc, f"{name} curr")
+        eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+        want, _ = orc.matching(fp[0], fp[1], fc[0], fc[1], cap=1 << 18)
+        assert_matches_equal(eng.batch_get_matches(0, 0), want, name)
+        assert_matches_equal(eng.batch_get_matches(0, 1), orc.bucket_features(want, 2, 50.0, 50.0), name + " bucketed")
+    finally:
+        eng.close()
+
+
+GOLD_IDS = [(tag, name) for tag, g in GOLD["geometries"].items() if tag != "native" for name in g["cases"]]
+
+
+@pytest.mark.parametrize("tag,name", GOLD_IDS, ids=[f"{t}-{n}" for t, n in GOLD_IDS])
+def test_cuda_matches_reference_golden(tag, name):
+    """the CUDA path against digests the REFERENCE produced (no oracle in between)"""
+    from test_oracle_golden import _inputs
+    geom = GOLD["geometries"][tag]
+    rec = geom["cases"][name]
+    prev, curr = _inputs(geom, name)
+    eng = Engine(geom["W"], geom["H"], max_frames=2, max_pairs=1)
+    try:
+        eng.batch_extract_host(0, np.stack([prev, curr]))
+        assert features_digest(*eng.slot_dump_features(0)) == rec["features_prev"]
+        assert features_digest(*eng.slot_dump_features(1)) == rec["features_curr"]
+        eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+        raw = eng.batch_get_matches(0, 0)
+        assert len(raw) == rec["n_raw"] and matches_digest(raw) == rec["raw_matches"]
+        if "bucketed_raw_2_50_50" in rec and rec.get("n_after_outliers") == rec["n_raw"]:
+            assert matches_digest(eng.batch_get_matches(0, 1)) == rec["bucketed_2_50_50"]
+    finally:
+        eng.close()
+
+
+def test_reference_array_stride_160():
+    """the reference's own MAX_FP_IN_BIN = 160 layout (src/size.h:18) round-trips"""
+    w, h = 1024, 284
+    seq = make_sequence(w, h, 2, seed=0)
+    orc = Oracle(w, h)
+    eng = Engine(w, h)
+    try:
+        m, n = eng.compute_features(seq[0], cap_stride=160)
+        wm, wn, _ = orc.compute_features(seq[0])
+        assert m.shape[3] == 160
+        assert_features_equal((m, n), (wm, wn), "stride 160")
+        m1, n1 = eng.compute_features(seq[1], cap_stride=160)
+        got = eng.matching(m, n, m1, n1)
+        wm1, wn1, _ = orc.compute_features(seq[1])
+        want, _ = orc.matching(wm, wn, wm1, wn1)
+        assert_matches_equal(got, want, "stride 160 matching")
+    finally:
+        eng.close()
+
+
+def test_capacity_errors_are_reported():
+    w, h = 500, 150
+    seq = make_sequence(w, h, 2, seed=0)
+    eng = Engine(w, h, max_matches=100)
+    try:
+        with pytest.raises(VoError) as ei:
+            eng.compute_features(seq[0], cap_stride=8)   # lists are longer than 8: the reference would overflow
+        assert ei.value.status == api.VO_ERR_CAPACITY
+        eng.push_back(seq[0]); eng.push_back(seq[1])
+        with pytest.raises(VoError) as ei:
+            eng.match_features(0)                        # 2324 raw matches do not fit max_matches=100
+        assert ei.value.status == api.VO_ERR_CAPACITY
+    finally:
+        eng.close()
+
+
+def test_push_back_error_behaviour():
+    eng = Engine(500, 150)
+    try:
+        img = np.zeros((150, 500), np.uint8)
+        import ctypes as C
+        dims = (C.c_int32 * 3)(500, 150, 400)  # bytes per line < width: src/matcher.cpp:59-62
+        st = eng.lib.vo_push_back(eng.h, img.ctypes.data_as(C.c_void_p), None, dims, 0)
+        assert st == api.VO_ERR_INVALID and b"Image dimension mismatch" in eng.lib.vo_last_error()
+        dims = (C.c_int32 * 3)(500, 150, 500)
+        assert eng.lib.vo_push_back(eng.h, None, None, dims, 0) == api.VO_ERR_INVALID
+        dims = (C.c_int32 * 3)(640, 150, 640)
+        assert eng.lib.vo_push_back(eng.h, img.ctypes.data_as(C.c_void_p), None, dims, 0) == api.VO_ERR_INVALID
+        # replace=True overwrites the current frame only
+        seq = make_sequence(500, 150, 3, seed=0)
+        orc = Oracle(500, 150)
+        eng.push_back(seq[0]); eng.push_back(seq[1]); eng.push_back(seq[2], replace=True)
+        assert_features_equal(eng.dump_features(0), orc.compute_features(seq[0])[:2], "prev after replace")
+        assert_features_equal(eng.dump_features(1), orc.compute_features(seq[2])[:2], "curr after replace")
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("pitch_pad", [0, 7, 12], ids=["tight", "odd-pitch", "tma-aligned"])
+def test_device_resident_input(pitch_pad):
+    """HBM-resident frames: read in place through a caller tensor map when 16-byte aligned,
+    otherwise staged device-to-device; both give identical features"""
+    import torch
+    w, h = 500, 150
+    pitch = w + pitch_pad                     # 500, 507, 512
+    seq = make_sequence(w, h, 3, seed=4)
+    buf = np.zeros((3, h, pitch), np.uint8)
+    buf[:, :, :w] = seq
+    d = torch.from_numpy(buf).cuda()
+    orc = Oracle(w, h)
+    eng = Engine(w, h, max_frames=3, max_pairs=2)
+    try:
+        eng.batch_extract_device(0, d.data_ptr(), 3, h * pitch, pitch)
+        for f in range(3):
+            assert_features_equal(eng.slot_dump_features(f), orc.compute_features(seq[f])[:2], f"slot {f}")
+    finally:
+        eng.close()
+
+
+def test_full_size_properties():
+    """BASELINE sizes through size-independent properties (2048x1024 and 1241x376)"""
+    for w, h in [(2048, 1024), (1241, 376)]:
+        seq = make_sequence(w, h, 2, seed=9)
+        eng = Engine(w, h, max_frames=2, max_pairs=1)
+        try:
+            eng.batch_extract_host(0, seq)
+            eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+            raw = eng.batch_get_matches(0, 0)
+            b = eng.batch_get_matches(0, 1)
+            assert len(raw) > 10000
+            cur = raw["u1c"].astype(np.int64) * 65536 + raw["v1c"].astype(np.int64)
+            assert len(np.unique(cur)) == len(cur)
+            assert (np.abs(raw["u1c"] - raw["u1p"]) <= 180).all() and (np.abs(raw["v1c"] - raw["v1p"]) <= 135).all()
+            assert (raw["u1c"] < 60 * (eng.U - 1)).all()
+            flow = np.stack([raw["u1c"] - raw["u1p"], raw["v1c"] - raw["v1p"]], 1)
+            assert (flow == [-3, -1]).all(axis=1).mean() > 0.99
+            cols = int(raw["u1c"].max() // 50) + 1
+            ids = (b["v1c"] // 50).astype(int) * cols + (b["u1c"] // 50).astype(int)
+            assert (np.diff(ids) >= 0).all() and np.bincount(ids).max() <= 2
+            # swapping the roles of the two frames reverses every match (circular consistency)
+            eng.batch_match([1], [0], max_features=0)
+            rev = eng.batch_get_matches(0, 0)
+            fwd = set(zip(raw["u1p"].tolist(), raw["v1p"].tolist(), raw["u1c"].tolist(), raw["v1c"].tolist()))
+            bwd = set(zip(rev["u1c"].tolist(), rev["v1c"].tolist(), rev["u1p"].tolist(), rev["v1p"].tolist()))
+            assert len(fwd & bwd) > 0.98 * len(fwd)
+        finally:
+            eng.close()
