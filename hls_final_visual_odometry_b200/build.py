@@ -16,6 +16,7 @@ CSRC = os.path.join(_PKG, "csrc")
 HOST = os.path.join(_PKG, "host")
 LIB = os.path.join(_PKG, "libvo_b200.so")
 HOST_LIB = os.path.join(_PKG, "libvo_host.so")
+DEMO = os.path.join(_PKG, "vo_demo")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -56,14 +57,21 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 def build_host(force: bool = False) -> str | None:
     if not os.path.isdir(HOST):
         return None
-    srcs = _sources(HOST, (".cpp",))
+    srcs = [s for s in _sources(HOST, (".cpp",)) if not s.endswith("demo_main.cpp")]
     if not srcs:
         return None
     deps = srcs + _sources(HOST, (".h",)) + [LIB]
+    inc = ["-I", os.path.join(_ROOT, "include"), "-I", HOST]
     if force or _stale(HOST_LIB, deps):
         subprocess.check_call([
-            "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-I", os.path.join(_ROOT, "include"),
+            "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", *inc,
             "-o", HOST_LIB, *srcs, "-L", _PKG, "-lvo_b200", "-Wl,-rpath,$ORIGIN",
+        ])
+    demo_src = os.path.join(HOST, "demo_main.cpp")
+    if os.path.exists(demo_src) and (force or _stale(DEMO, deps + [demo_src, HOST_LIB])):
+        subprocess.check_call([
+            "g++", "-O2", "-std=c++17", "-Wall", *inc, "-o", DEMO, demo_src, "-L", _PKG, "-lvo_host", "-lvo_b200",
+            "-Wl,-rpath,$ORIGIN",
         ])
     return HOST_LIB
 

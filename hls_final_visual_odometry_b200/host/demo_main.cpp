@@ -1,0 +1,42 @@
+// vo_demo: the reference's src/demo.cpp loop (read raw I1_%06d.dat frames, process(), print the
+// number of matches per frame) on the C++ shim.  Usage: vo_demo <dir> <width> <height> <n_frames>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "viso_mono.h"
+
+int main(int argc, char** argv) {
+  if (argc < 5) {
+    std::cerr << "Usage: vo_demo path/to/sequence width height n_frames" << std::endl;
+    return 1;
+  }
+  const std::string dir = argv[1];
+  const int32_t width = atoi(argv[2]), height = atoi(argv[3]), n = atoi(argv[4]);
+  VisualOdometryMono::parameters param;
+  VisualOdometryMono viso(param);
+  std::vector<uint8_t> img((size_t)width * height);
+  for (int32_t i = 0; i < n; i++) {
+    char name[256];
+    snprintf(name, sizeof(name), "/I1_%06d.dat", i);
+    std::ifstream ifs((dir + name).c_str(), std::ifstream::binary | std::ifstream::in);
+    if (!ifs.read((char*)img.data(), img.size())) {
+      std::cerr << "ERROR: Couldn't read input files!" << std::endl;
+      return 1;
+    }
+    int32_t dims[] = {width, height, width};
+    viso.process(img.data(), dims);
+    if (viso.getMatcher()->lastStatus() != 0) return 2;
+    std::vector<Matcher::p_match> m = viso.getMatches();
+    double su = 0, sv = 0;
+    for (size_t k = 0; k < m.size(); k++) { su += m[k].u1c - m[k].u1p; sv += m[k].v1c - m[k].v1p; }
+    std::cout << "Processing: Frame: " << i << ", Matches: " << m.size();
+    if (!m.empty()) std::cout << ", mean flow: " << su / m.size() << " " << sv / m.size();
+    std::cout << std::endl;
+  }
+  std::cout << "Demo complete! Exiting ..." << std::endl;
+  return 0;
+}

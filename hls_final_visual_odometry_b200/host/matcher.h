@@ -1,0 +1,99 @@
+// Drop-in C++ host shim: the reference's Matcher class surface (src/matcher.h:40-143) on top of the
+// C ABI of libvo_b200.so.  Same class name, nested types, method names, argument meaning and error
+// behaviour, so a caller of the reference (src/viso_mono.cpp:33-39, src/demo.cpp:117) recompiles
+// against this header unchanged.  No algorithm lives here: every method is one or two C-ABI calls.
+//
+// Differences that are visible on purpose:
+//  * the image size is taken from `dims` at the first pushBack (the reference hard-wires
+//    1024x284 in src/size.h and ignores dims);
+//  * matchFeatures() runs the GPU circular matcher; the reference additionally runs its host-side
+//    Delaunay filter (removeOutliers, src/remove_outliers.cpp:4) inside matchFeatures -- here that
+//    stage is a plug-in (setOutlierFilter) until row F1 of SURVEY.md section 8 lands;
+//  * frame 0 yields zero matches instead of matching against uninitialised counts.
+#ifndef VO_B200_HOST_MATCHER_H
+#define VO_B200_HOST_MATCHER_H
+
+#include <stdint.h>
+
+#include <functional>
+#include <vector>
+
+struct vo_engine;
+class Matrix;  // only ever passed through as an ignored pointer, as in the reference
+
+class Matcher {
+ public:
+  // parameter settings (src/matcher.h:45-72) -- dead on the reference's executed path, kept for API parity
+  struct parameters {
+    int32_t nms_n;
+    int32_t nms_tau;
+    int32_t match_binsize;
+    int32_t match_radius;
+    int32_t match_disp_tolerance;
+    int32_t outlier_disp_tolerance;
+    int32_t outlier_flow_tolerance;
+    int32_t multi_stage;
+    int32_t half_resolution;
+    int32_t refinement;
+    double f, cu, cv, base;
+    parameters() {
+      nms_n = 2; nms_tau = 50; match_binsize = 50; match_radius = 200; match_disp_tolerance = 2;
+      outlier_disp_tolerance = 5; outlier_flow_tolerance = 5; multi_stage = 0; half_resolution = 0;
+      refinement = 0; f = cu = cv = base = 0;
+    }
+  };
+
+  // structure for storing matches (src/matcher.h:89-104): 48 bytes, identical to vo_p_match
+  class p_match {
+   public:
+    float u1p, v1p; int32_t i1p;
+    float u2p, v2p; int32_t i2p;
+    float u1c, v1c; int32_t i1c;
+    float u2c, v2c; int32_t i2c;
+    p_match() {}
+    p_match(float u1p, float v1p, int32_t i1p, float u2p, float v2p, int32_t i2p, float u1c, float v1c,
+            int32_t i1c, float u2c, float v2c, int32_t i2c)
+        : u1p(u1p), v1p(v1p), i1p(i1p), u2p(u2p), v2p(v2p), i2p(i2p), u1c(u1c), v1c(v1c), i1c(i1c),
+          u2c(u2c), v2c(v2c), i2c(i2c) {}
+  };
+
+  explicit Matcher(parameters param, int device = 0);
+  ~Matcher();
+  Matcher(const Matcher&) = delete;
+  Matcher& operator=(const Matcher&) = delete;
+
+  void setIntrinsics(double f, double cu, double cv, double base) {
+    param.f = f; param.cu = cu; param.cv = cv; param.base = base;
+  }
+
+  // src/matcher.cpp:51-91.  dims = {width, height, bytes per line}; I2 is ignored as in the reference.
+  void pushBack(uint8_t* I1, uint8_t* I2, int32_t* dims, const bool replace);
+  void pushBack(uint8_t* I1, int32_t* dims, const bool replace) { pushBack(I1, 0, dims, replace); }
+
+  // src/matcher.cpp:93-111.  method and Tr_delta are accepted and ignored, as in the reference.
+  void matchFeatures(int32_t method, Matrix* Tr_delta = 0);
+
+  // src/matcher.cpp:140-187
+  void bucketFeatures(int32_t max_features, float bucket_width, float bucket_height);
+
+  // src/matcher.h:138-143: returns a copy
+  std::vector<Matcher::p_match> getMatches();
+
+  // host stage between matching and bucketing (the reference's removeOutliers); in/out list
+  void setOutlierFilter(std::function<void(std::vector<Matcher::p_match>&)> f) { outlier_filter = f; }
+
+  // last C-ABI status (0 = ok) and message, for callers that want more than the reference's cerr line
+  int lastStatus() const { return last_status; }
+  const char* lastError() const;
+  vo_engine* engine() { return eng; }
+
+ private:
+  bool ensureEngine(int32_t width, int32_t height);
+  parameters param;
+  int device;
+  vo_engine* eng;
+  int last_status;
+  std::function<void(std::vector<Matcher::p_match>&)> outlier_filter;
+};
+
+#endif

@@ -169,3 +169,26 @@ def test_full_size_properties():
             assert len(fwd & bwd) > 0.98 * len(fwd)
         finally:
             eng.close()
+
+
+def test_cpp_shim_demo(tmp_path):
+    """the C++ drop-in (Matcher / VisualOdometryMono::process, reference class surface) driven by the
+    reference's demo loop over raw I1_%06d.dat frames"""
+    import subprocess
+    from hls_final_visual_odometry_b200 import build
+    build.build_all()
+    w, h, n = 500, 150, 4
+    seq = make_sequence(w, h, n, seed=6)
+    for f in range(n):
+        seq[f].tofile(str(tmp_path / f"I1_{f:06d}.dat"))
+    out = subprocess.run([build.DEMO, str(tmp_path), str(w), str(h), str(n)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    counts = [int(l.split("Matches:")[1].split(",")[0]) for l in out.stdout.splitlines() if "Matches:" in l]
+    orc = Oracle(w, h)
+    feats = [orc.compute_features(seq[f])[:2] for f in range(n)]
+    want = [0]
+    for f in range(1, n):
+        raw, _ = orc.matching(feats[f - 1][0], feats[f - 1][1], feats[f][0], feats[f][1])
+        want.append(len(orc.bucket_features(raw, 2, 50.0, 50.0)))
+    assert counts == want
+    assert "mean flow: -3 -1" in out.stdout
