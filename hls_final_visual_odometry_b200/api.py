@@ -33,7 +33,7 @@ class VoConfig(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bin_w", C.c_int32), ("bin_h", C.c_int32),
                 ("nms_tau", C.c_int32), ("max_frames", C.c_int32), ("max_pairs", C.c_int32),
                 ("max_matches", C.c_int32), ("match_rows_per_cta", C.c_int32), ("match_exhaustive", C.c_int32),
-                ("reserved", C.c_int32 * 6)]
+                ("match_threads", C.c_int32), ("reserved", C.c_int32 * 5)]
 
 
 class VoGeometry(C.Structure):
@@ -123,11 +123,12 @@ class Engine:
 
     def __init__(self, width: int, height: int, max_frames: int = 2, max_pairs: int = 1, device: int = 0,
                  stream: int | None = None, max_matches: int = 0, match_rows_per_cta: int = 0, nms_tau: int = 0,
-                 bin_w: int = 0, bin_h: int = 0, match_exhaustive: bool = False):
+                 bin_w: int = 0, bin_h: int = 0, match_exhaustive: bool = False, match_threads: int = 0):
         self.lib = load_library()
         cfg = VoConfig(width=width, height=height, bin_w=bin_w, bin_h=bin_h, nms_tau=nms_tau,
                        max_frames=max_frames, max_pairs=max_pairs, max_matches=max_matches,
-                       match_rows_per_cta=match_rows_per_cta, match_exhaustive=int(match_exhaustive))
+                       match_rows_per_cta=match_rows_per_cta, match_exhaustive=int(match_exhaustive),
+                       match_threads=match_threads)
         h = C.c_void_p()
         self.h = None
         self._check(self.lib.vo_engine_create(C.byref(cfg), device, C.c_void_p(stream or 0), C.byref(h)))

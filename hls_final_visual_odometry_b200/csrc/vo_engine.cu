@@ -21,7 +21,7 @@ cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t*
 cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
                         int cap_stride, cudaStream_t st);
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
-                      int rows_per_group, int prune, cudaStream_t st);
+                      int rows_per_group, int prune, int threads, cudaStream_t st);
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
                       uint8_t* flags, int32_t* list_cnt, void* out, int64_t out_stride_matches, int32_t max_matches,
                       int32_t* n_raw, int32_t* status, cudaStream_t st);
@@ -68,7 +68,7 @@ struct vo_engine {
   bool own_stream = false;
   int n_slots = 0, n_pairbuf = 0;       // incl. the operator-level scratch slots / pair
   int op_slot_a = 0, op_slot_b = 0, op_pair = 0;
-  int rows_per_group = 0, prune = 1;
+  int rows_per_group = 0, prune = 1, match_threads = 0;
   vo::FrameArrays fa{};
   CUtensorMap tmap_slots;
   // pair buffers
@@ -218,7 +218,7 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
   {
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
-                         e->rows_per_group, e->prune, e->stream));
+                         e->rows_per_group, e->prune, e->match_threads, e->stream));
     e->launches += 1;
   }
   {
@@ -319,6 +319,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   e->n_pairbuf = cfg.max_pairs + 1; e->op_pair = cfg.max_pairs;
   e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : g.V;
   e->prune = cfg.match_exhaustive ? 0 : 1;
+  e->match_threads = cfg.match_threads;
 
   if (stream) { e->stream = (cudaStream_t)stream; e->own_stream = false; }
   else {

@@ -6,15 +6,18 @@
 //   myMatching      src/myMatch.cpp:122-204   (both directions, cycle check, pixel dedupe, emit)
 // in the ring-buffer-free formulation of SURVEY.md appendix A.
 //
-// K2 (k2_match): one CTA per (origin u-bin column, group of origin v-bin rows, class, direction,
-// frame pair).  The CTA stages the target window of the OTHER frame -- up to 6 u-bin columns x
-// the v-bin rows its origins can see -- into shared memory ordered (v_bin, u_bin, slot), so that
-// every origin's candidate set is ONE contiguous range.  A warp owns an origin; its lanes stride
-// the range, each candidate costing 8 VABSDIFF4.U8.ACC (packed-byte SAD) + a packed window test,
-// and keeps min(SAD<<19 | u_rel<<16 | col_idx), which is exactly the reference's "strict <,
-// first candidate in (u_bin asc, col_idx asc) order wins".  One REDUX.MIN per origin.
-// Optional exact pruning (PRUNE): a 2-instruction lower bound of the SAD (see desc_q) skips the
-// 8-instruction exact SAD for candidates that provably cannot win or tie; results are identical.
+// K2 (k2_match): one CTA per (pair of origin u-bin columns, group of origin v-bin rows, class,
+// direction, frame pair).  The CTA stages the target window of the OTHER frame -- up to 7 u-bin
+// columns x the v-bin rows its origins can see -- into shared memory ordered (v_bin, u_bin, slot),
+// every bin list padded to a multiple of 4.  A LANE owns an origin: the 32 lanes of a warp hold 32
+// consecutive origins of one column list and walk the same candidates, so every shared-memory
+// read is a broadcast and no per-origin work is replicated across lanes.  Per candidate and lane:
+// a 2-instruction lower bound Q of the SAD (see desc_q) against the lane's running threshold;
+// only candidates that could still win or tie pay the exact SAD (8 VABSDIFF4.U8.ACC) + packed
+// window test, and the key min(SAD<<19 | u_rel<<16 | col_idx) is exactly the reference's
+// "strict <, first candidate in (u_bin asc, col_idx asc) order wins".  The threshold is seeded
+// from the bins the origins themselves sit in (zero-flow prior).  Pruning is conservative, so the
+// result is identical to evaluating every SAD (PRUNE=false does that, for the tests).
 // SAD is not a contraction: no tensor cores here by design.
 //
 // K3 (k3_flags, k3_emit): closed-cycle test, same-pixel dedupe (lowest class wins, via the twin
@@ -23,30 +26,34 @@
 
 namespace vo {
 
-constexpr int K2_THREADS = 512;
-constexpr int K2_WARPS = K2_THREADS / 32;
 constexpr int kMaxV = 64;       // v-bin rows supported by the shared-memory tables
-constexpr int kMaxCols = 6;     // target u-bin columns: [ub-3, ub+3) clipped
-constexpr int kCandCap = 2176;  // staged candidates per chunk; >= 6*300 so one window row always fits
+constexpr int kOC = 2;          // origin u-bin columns per CTA (they share the staged window)
+constexpr int kMaxCols = kOC + 5;  // staged target columns: [ub0-3, ub_last+3) clipped
+constexpr int kSegW = kMaxCols + 1;
+constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
+constexpr int kMaxWarps = 16;
+constexpr int kQueue = 64;      // deferred exact evaluations per warp
+constexpr int kBig = 1 << 20;
 
 struct K2Tables {
-  int32_t cntT[kMaxV][kMaxCols];      // target counts (row, rel. column)
+  int32_t cntT[kMaxV][kSegW];         // target counts (row, staged column)
+  int32_t segOff[kMaxV][kSegW];       // this chunk: staged position of bin (row, column); [ncol] = end of the row
   int32_t colT[kMaxCols][kMaxV + 1];  // col_idx prefix of each target column
-  int32_t rowTot[kMaxV];              // candidates per staged row
-  int32_t stageOff[kMaxV + 1];        // staged position of the first candidate of a row (chunk-relative)
-  int32_t cntO[kMaxV];
-  int32_t prefO[kMaxV + 1];
-  int32_t lagEnd[kMaxV];              // origins o < lagEnd[v] of row v may carry a lagging v_bin (slow path)
-  int32_t posLo[kMaxV], posHi[kMaxV]; // staged candidate range of a non-lagging origin of row v (this chunk)
+  int32_t rowTot[kMaxV];              // staged (padded) candidates per row
+  int32_t rowStart[kMaxV + 1];        // this chunk: staged position of the first candidate of a row
+  int32_t cntO[kOC][kMaxV];
+  int32_t prefO[kOC][kMaxV + 1];
+  int32_t lagEnd[kOC][kMaxV];         // origins o < lagEnd[v] of row v may carry a lagging v_bin
 };
 
-template <bool PRUNE>
 struct __align__(128) K2Smem {
   K2Tables t;
+  uint32_t sbest[kMaxWarps][32];      // running best key of the 32 origins of a warp's task
+  uint32_t queue[kMaxWarps][kQueue];  // deferred exact evaluations: owner lane << 16 | candidate group
   __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
   uint4 hi[kCandCap];                 // descriptor bytes 16..31
   uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
-  uint2 q[PRUNE ? kCandCap : 1];      // 8 quantised group sums (lower-bound filter)
+  __align__(16) uint2 q[kCandCap];    // 8 quantised group sums (lower-bound filter); read two at a time
 };
 
 // acc + sum of |a_i - b_i| over the four packed bytes: one VABSDIFF4.U8.ACC
@@ -67,83 +74,114 @@ __device__ __forceinline__ uint32_t sad32(const uint4& a, const uint4& b, const 
   return sad4(b.w, y.w, s);
 }
 
+__device__ __forceinline__ int sadq(const uint2& a, uint32_t x, uint32_t y) {
+  return (int)sad4(a.y, y, sad4(a.x, x, 0u));
+}
+
+// key of one staged candidate for an origin (a, b, window lo_p/hi_p), kNone if outside the window.
+// packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
+__device__ __forceinline__ uint32_t cand_key(const K2Smem& S, int p, const uint4& a, const uint4& b, uint32_t lo_p,
+                                             uint32_t hi_p) {
+  const uint2 xr = S.xr[p];
+  const uint32_t sad = sad32(a, b, S.lo[p], S.hi[p]);
+  const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
+  const uint32_t key = sad * 0x80000u + xr.y;
+  return (((t1 & ~t2) & 0x80008000u) == 0x80008000u) ? key : kNone;
+}
+
 // v_buffer_idx of the reference (src/myMatch.cpp:153-158): starts at 0, bumped at most once per
 // origin => vb(k) = min(k+1, v+1, min over non-empty rows b<v of b+2+k-prefix[b+1]).
-__device__ __forceinline__ int origin_vb(const K2Tables& t, int col_idx, int v) {
+__device__ __forceinline__ int origin_vb(const K2Tables& t, int cc, int col_idx, int v) {
   int vb = min(col_idx + 1, v + 1);
   for (int b = 0; b < v; b++)
-    if (t.cntO[b] > 0) vb = min(vb, b + 2 + col_idx - t.prefO[b + 1]);
+    if (t.cntO[cc][b] > 0) vb = min(vb, b + 2 + col_idx - t.prefO[cc][b + 1]);
   return vb;
 }
 
-template <bool PRUNE>
-__global__ void __launch_bounds__(K2_THREADS, 2)
-k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __restrict__ best, int rows_per_group,
-         int ngroups) {
-  extern __shared__ __align__(128) uint8_t smem_raw[];
-  K2Smem<PRUNE>& S = *reinterpret_cast<K2Smem<PRUNE>*>(smem_raw);
-  K2Tables& t = S.t;
+__device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 
+// Matches the origins of columns [ub0, ub0+noc) x rows of group `grp`.  Returns false (having
+// written nothing) when a row of the shared (noc+5)-column window does not fit the staging buffer;
+// the caller then runs the columns one at a time (a 6-column row always fits).
+template <bool PRUNE, int THREADS>
+__device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
+                                           uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
+                                           int rows_per_group) {
+  constexpr int NW = THREADS / 32;
+  constexpr uint32_t FULL = 0xFFFFFFFFu;
+  K2Tables& t = S.t;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int ub = blockIdx.x / ngroups, grp = blockIdx.x - ub * ngroups;
-  const int c = blockIdx.y >> 1, dir = blockIdx.y & 1;
-  const int2 pr = pairs[blockIdx.z];  // x = prev slot, y = curr slot
-  const int from_slot = dir ? pr.x : pr.y, to_slot = dir ? pr.y : pr.x;
   const int U = g.U, V = g.V;
-  const int ulo = max(ub - 3, 0), uhi = min(ub + 3, U - 1);  // [ulo, uhi): src/myMatch.cpp:90-91,97
+  const int ulo = max(ub0 - 3, 0), uhi = min(ub0 + noc - 1 + 3, U - 1);  // staged target columns [ulo, uhi)
   const int ncol = uhi - ulo;
 
   const int32_t* cnt_to = fa.cnt + (int64_t)to_slot * fa.cnt_stride;
   const int32_t* cnt_from = fa.cnt + (int64_t)from_slot * fa.cnt_stride;
-  for (int idx = tid; idx < V * kMaxCols; idx += K2_THREADS) {
-    const int v = idx / kMaxCols, j = idx - v * kMaxCols;
+  __syncthreads();  // tables may still be in use by a previous call
+  for (int idx = tid; idx < V * kSegW; idx += THREADS) {
+    const int v = idx / kSegW, j = idx - v * kSegW;
     t.cntT[v][j] = (j < ncol) ? cnt_to[(v * U + ulo + j) * 4 + c] : 0;
   }
-  for (int v = tid; v < V; v += K2_THREADS) t.cntO[v] = cnt_from[(v * U + ub) * 4 + c];
+  for (int idx = tid; idx < V * kOC; idx += THREADS) {
+    const int cc = idx / V, v = idx - cc * V;
+    t.cntO[cc][v] = (cc < noc) ? cnt_from[(v * U + ub0 + cc) * 4 + c] : 0;
+  }
   __syncthreads();
   if (tid < kMaxCols) {
     int acc = 0;
     t.colT[tid][0] = 0;
     for (int v = 0; v < V; v++) { acc += t.cntT[v][tid]; t.colT[tid][v + 1] = acc; }
-  } else if (tid == 32) {
+  } else if (tid >= 32 && tid < 32 + kOC) {
+    const int cc = tid - 32;
     int acc = 0;
-    t.prefO[0] = 0;
-    for (int v = 0; v < V; v++) { acc += t.cntO[v]; t.prefO[v + 1] = acc; }
+    t.prefO[cc][0] = 0;
+    for (int v = 0; v < V; v++) { acc += t.cntO[cc][v]; t.prefO[cc][v + 1] = acc; }
   } else if (tid >= 64 && tid < 64 + V) {
     const int v = tid - 64;
     int acc = 0;
 #pragma unroll
-    for (int j = 0; j < kMaxCols; j++) acc += t.cntT[v][j];
+    for (int j = 0; j < kMaxCols; j++) acc += pad4(t.cntT[v][j]);
     t.rowTot[v] = acc;
   }
   __syncthreads();
-  if (tid < V) {  // first origin index of row v whose v_bin is the nominal v+1 (see origin_vb)
-    int le = tid;
-    for (int b = 0; b < tid; b++)
-      if (t.cntO[b] > 0) le = max(le, t.prefO[b + 1] + tid - 1 - b);
-    t.lagEnd[tid] = le;
+  for (int idx = tid; idx < V * kOC; idx += THREADS) {  // first origin of row v whose v_bin is the nominal v+1
+    const int cc = idx / V, v = idx - cc * V;
+    int le = v;
+    for (int b = 0; b < v; b++)
+      if (t.cntO[cc][b] > 0) le = max(le, t.prefO[cc][b + 1] + v - 1 - b);
+    t.lagEnd[cc][v] = le;
   }
 
   const int r0 = grp * rows_per_group, r1 = min(r0 + rows_per_group, V);
-  const int o_begin = t.prefO[r0], o_end = t.prefO[r1];
-  if (o_begin >= o_end) return;
-
-  // rows any origin of this group can see: vb is non-decreasing along the column list
-  int v_first = r0;
-  while (t.prefO[v_first + 1] <= o_begin) v_first++;
-  const int vb_first = origin_vb(t, o_begin, v_first);
-  const int row_lo = max(vb_first - 3, 0);
+  int oB0 = 0, nT0 = 0, ntasks = 0, row_lo = V;
+#pragma unroll
+  for (int cc = 0; cc < kOC; cc++) {
+    const int ob = t.prefO[cc][r0];
+    const int n = t.prefO[cc][r1] - ob;
+    if (cc == 0) { oB0 = ob; nT0 = (n + 31) >> 5; }
+    ntasks += (n + 31) >> 5;
+    if (n > 0) {  // rows any origin of this group can see: vb is non-decreasing along the column list
+      int v_first = r0;
+      while (t.prefO[cc][v_first + 1] <= ob) v_first++;
+      row_lo = min(row_lo, max(origin_vb(t, cc, ob, v_first) - 3, 0));
+    }
+  }
+  if (ntasks == 0) return true;
   const int row_hi = min(r1 + 3, V - 1);  // exclusive: src/myMatch.cpp:93,99
+  if (noc > 1)
+    for (int v = row_lo; v < row_hi; v++)
+      if (t.rowTot[v] > kCandCap) return false;
 
   const uint32_t* xy_from = fa.xy + (int64_t)from_slot * fa.rec_stride;
   const uint4* desc_from = fa.desc + (int64_t)from_slot * fa.rec_stride * 2;
+  const uint2* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
   const uint32_t* xy_to = fa.xy + (int64_t)to_slot * fa.rec_stride;
   const uint4* desc_to = fa.desc + (int64_t)to_slot * fa.rec_stride * 2;
-  const uint2* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
   const uint2* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
-  uint32_t* best_out = best + ((int64_t)(blockIdx.z * 2 + dir) * U * 4 + (ub * 4 + c)) * g.col_cap;
-  const int rec_row_stride = U * 4 * g.cap;              // records between consecutive rows of one (u,c)
-  const int rec_col0 = (ub * 4 + c) * g.cap;             // record index of row 0 of the origin column
+  const uint4* Q4 = reinterpret_cast<const uint4*>(S.q);
+  uint32_t* sbest = S.sbest[warp];
+  uint32_t* queue = S.queue[warp];
+  const uint32_t lt_mask = (1u << lane) - 1u;
 
   bool first_chunk = true;
   for (int ra = row_lo;;) {
@@ -151,140 +189,188 @@ k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __res
     int rb = ra, staged = 0;
     while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
     __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
-    if (tid == 0) {
+    if (tid <= rb - ra) {
+      const int v = ra + tid;
       int acc = 0;
-      for (int v = ra; v < rb; v++) { t.stageOff[v] = acc; acc += t.rowTot[v]; }
-      t.stageOff[rb] = acc;
+      for (int x = ra; x < v; x++) acc += t.rowTot[x];
+      t.rowStart[v] = acc;
+      if (v < rb) {
+#pragma unroll
+        for (int j = 0; j < kSegW; j++) { t.segOff[v][j] = acc; acc += pad4(t.cntT[v][j]); }
+      }
     }
     __syncthreads();
-    if (tid < V) {  // nominal window of row tid: v-bins [v-2, v+4) clipped (vb = v+1)
-      const int vlo = max(max(tid - 2, 0), ra), vhi = min(min(tid + 4, V - 1), rb);
-      t.posLo[tid] = (vlo < vhi) ? t.stageOff[vlo] : 0;
-      t.posHi[tid] = (vlo < vhi) ? t.stageOff[vhi] : 0;
-    }
-    // ---- stage: warp per (row, column) bin list, coalesced 16-byte copies ------------------
-    for (int b = warp; b < (rb - ra) * ncol; b += K2_WARPS) {
+    // ---- stage: warp per (row, column) bin list, coalesced 16-byte copies; every list is padded
+    //      to a multiple of 4 with dummies that can never pass the window test -------------------
+    for (int b = warp; b < (rb - ra) * ncol; b += NW) {
       const int v = ra + b / ncol, j = b % ncol;
-      const int n = t.cntT[v][j];
-      int dst = t.stageOff[v];
-      for (int jj = 0; jj < j; jj++) dst += t.cntT[v][jj];
+      const int n = t.cntT[v][j], npad = pad4(n);
+      const int dst = t.segOff[v][j];
       const int64_t src = (int64_t)((v * U + ulo + j) * 4 + c) * g.cap;
       const uint32_t rank0 = ((uint32_t)j << 16) | (uint32_t)t.colT[j][v];
-      for (int k = lane; k < n; k += 32) {
-        const uint4 d0 = desc_to[(src + k) * 2], d1 = desc_to[(src + k) * 2 + 1];
-        S.lo[dst + k] = d0;
-        S.hi[dst + k] = d1;
-        S.xr[dst + k] = make_uint2(xy_to[src + k] + 0x80008000u, rank0 + (uint32_t)k);
-        if (PRUNE) S.q[dst + k] = q_to[src + k];
+      for (int k = lane; k < npad; k += 32) {
+        if (k < n) {
+          const uint4 d0 = desc_to[(src + k) * 2], d1 = desc_to[(src + k) * 2 + 1];
+          S.lo[dst + k] = d0;
+          S.hi[dst + k] = d1;
+          S.xr[dst + k] = make_uint2(xy_to[src + k] + 0x80008000u, rank0 + (uint32_t)k);
+          S.q[dst + k] = q_to[src + k];
+        } else {
+          S.lo[dst + k] = make_uint4(0, 0, 0, 0);
+          S.hi[dst + k] = make_uint4(0, 0, 0, 0);
+          S.xr[dst + k] = make_uint2(kNone, kNone);
+          S.q[dst + k] = make_uint2(kNone, kNone);
+        }
       }
     }
     __syncthreads();
 
-    // ---- origins: one warp each, next origin's record prefetched while this one is matched ---
-    int o = o_begin + warp, vl = v_first;
-    uint32_t n_xy = 0;
-    uint4 n_a = make_uint4(0, 0, 0, 0), n_b = n_a;
-    uint2 n_q = make_uint2(0, 0);
-    if (o < o_end) {
-      while (t.prefO[vl + 1] <= o) vl++;
-      const int rec = rec_col0 + vl * rec_row_stride + (o - t.prefO[vl]);
-      n_xy = __ldg(&xy_from[rec]); n_a = __ldg(&desc_from[2 * rec]); n_b = __ldg(&desc_from[2 * rec + 1]);
-      if (PRUNE) n_q = __ldg(&q_from[rec]);
-    }
-    while (o < o_end) {
-      const uint32_t oxy = n_xy;
-      const uint4 a = n_a, b = n_b;
-      const uint2 qa = n_q;
-      const int v = vl;  // row of origin o (found when it was prefetched)
-      const int on = o + K2_WARPS;
-      if (on < o_end) {
-        while (t.prefO[vl + 1] <= on) vl++;
-        const int rec = rec_col0 + vl * rec_row_stride + (on - t.prefO[vl]);
-        n_xy = __ldg(&xy_from[rec]); n_a = __ldg(&desc_from[2 * rec]); n_b = __ldg(&desc_from[2 * rec + 1]);
-        if (PRUNE) n_q = __ldg(&q_from[rec]);
-      }
-      int lo, hi;
-      if (o >= t.lagEnd[v]) {
-        lo = t.posLo[v]; hi = t.posHi[v];
-      } else {  // rare: the first origins after empty bins carry a lagging v_bin
-        const int vb = origin_vb(t, o, v);
-        const int vlo = max(max(vb - 3, 0), ra), vhi = min(min(vb + 3, V - 1), rb);
-        lo = (vlo < vhi) ? t.stageOff[vlo] : 0;
-        hi = (vlo < vhi) ? t.stageOff[vhi] : 0;
-      }
-      const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
-      // packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
-      const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);
-      const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
+    // ---- tasks: 32 consecutive origins of one column list, one per lane.  Every lane walks the
+    //      same candidates (shared-memory broadcast); its own search rows are [vlo, vhi). ----------
+    for (int task = warp; task < ntasks; task += NW) {
+      const int cc = (kOC > 1 && task >= nT0) ? 1 : 0;
+      const int tb = task - (cc ? nT0 : 0);
+      const int ub = ub0 + cc;
+      const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo, jown = ub - ulo;  // src/myMatch.cpp:90-91,97
+      const int o = (cc ? t.prefO[cc][r0] : oB0) + tb * 32 + lane;
+      const bool valid = o < t.prefO[cc][r1];
+      uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
+
+      int v = r0, vlo = kBig, vhi = 0;
+      uint32_t oxy = 0;
+      uint4 a = make_uint4(0, 0, 0, 0), b = a;
+      uint2 qa = make_uint2(0, 0);
       uint32_t bestk = kNone;
-      if (!PRUNE) {
-#pragma unroll 4
-        for (int pos = lo + lane; pos < hi; pos += 32) {
-          const uint2 xr = S.xr[pos];
-          const uint32_t sad = sad32(a, b, S.lo[pos], S.hi[pos]);
-          const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
-          const uint32_t key = sad * 0x80000u + xr.y;
-          if (((t1 & ~t2) & 0x80008000u) == 0x80008000u) bestk = min(bestk, key);
+      if (valid) {
+        while (t.prefO[cc][v + 1] <= o) v++;
+        const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
+        oxy = __ldg(&xy_from[rec]);
+        a = __ldg(&desc_from[2 * rec]);
+        b = __ldg(&desc_from[2 * rec + 1]);
+        qa = __ldg(&q_from[rec]);
+        // lagging v_bin (src/myMatch.cpp:153-158): only the first origins after empty bins
+        const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
+        const int lo_r = max(max(vb - 3, 0), ra), hi_r = min(min(vb + 3, V - 1), rb);  // src/myMatch.cpp:92-93,99
+        if (lo_r < hi_r) { vlo = lo_r; vhi = hi_r; }
+        if (!first_chunk) {
+          bestk = bo[o];
+          if (bestk != kNone) bestk += (uint32_t)j0 << 16;
         }
-      } else {
-        // pass 1: the candidate with the smallest lower bound, per lane
+      }
+      const int rlo = __reduce_min_sync(FULL, vlo), rhi = __reduce_max_sync(FULL, vhi);
+      const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
+      const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
+      const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
+
+      if (PRUNE) {
+        // seed: the candidate with the smallest lower bound among the bins the origins themselves
+        // sit in (zero-flow prior); any legal candidate gives a valid bound
+        const int smin = max(__reduce_min_sync(FULL, valid ? v : kBig), ra);
+        const int smax = min(__reduce_max_sync(FULL, valid ? v : -1), rb - 1);
         uint32_t k1 = kNone;
-#pragma unroll 4
-        for (int pos = lo + lane; pos < hi; pos += 32) {
-          const uint2 q = S.q[pos];
-          const uint32_t Q = sad4(qa.y, q.y, sad4(qa.x, q.x, 0u));
-          k1 = min(k1, Q * 0x100000u + (uint32_t)(pos - lo));
-        }
-        uint32_t tq = 0;
-        // exact SAD + window test of one staged candidate; tightens this lane's bound
-        auto exact = [&](int pos) {
-          const uint2 xr = S.xr[pos];
-          const uint32_t sad = sad32(a, b, S.lo[pos], S.hi[pos]);
-          const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
-          const uint32_t key = sad * 0x80000u + xr.y;
-          if (((t1 & ~t2) & 0x80008000u) == 0x80008000u && key < bestk) {
-            bestk = key;
-            tq = min(tq, (sad + 24u) >> 2);
-          }
-        };
-        tq = kNone;
-        if (k1 != kNone) exact(lo + (int)(k1 & 0xFFFFFu));
-        // any candidate that can still win (or tie) has 4Q-24 <= best SAD so far
-        uint32_t tsad = __reduce_min_sync(0xFFFFFFFFu, bestk) >> 19;
-        if (!first_chunk) tsad = min(tsad, best_out[o] >> 19);
-        tq = (tsad + 24u) >> 2;
-        // pass 2: exact SAD only where the bound allows; four candidates share one branch
-        int pos = lo + lane;
-        for (; pos + 96 < hi; pos += 128) {
-          const uint2 q0 = S.q[pos], q1 = S.q[pos + 32], q2 = S.q[pos + 64], q3 = S.q[pos + 96];
-          const uint32_t Q0 = sad4(qa.y, q0.y, sad4(qa.x, q0.x, 0u));
-          const uint32_t Q1 = sad4(qa.y, q1.y, sad4(qa.x, q1.x, 0u));
-          const uint32_t Q2 = sad4(qa.y, q2.y, sad4(qa.x, q2.x, 0u));
-          const uint32_t Q3 = sad4(qa.y, q3.y, sad4(qa.x, q3.x, 0u));
-          if (min(min(Q0, Q1), min(Q2, Q3)) <= tq) {
-            if (Q0 <= tq) exact(pos);
-            if (Q1 <= tq) exact(pos + 32);
-            if (Q2 <= tq) exact(pos + 64);
-            if (Q3 <= tq) exact(pos + 96);
+        for (int r = smin; r <= smax; r++) {
+          const int p1 = t.segOff[r][jown + 1];
+          for (int p = t.segOff[r][jown]; p < p1; p += 2) {
+            const uint4 qq = Q4[p >> 1];
+            const uint32_t ka = (uint32_t)sadq(qa, qq.x, qq.y) * 0x100000u + (uint32_t)p;
+            const uint32_t kb = (uint32_t)sadq(qa, qq.z, qq.w) * 0x100000u + (uint32_t)(p + 1);
+            k1 = min(k1, min(ka, kb));
           }
         }
-#pragma unroll 1
-        for (; pos < hi; pos += 32) {
-          const uint2 q = S.q[pos];
-          const uint32_t Q = sad4(qa.y, q.y, sad4(qa.x, q.x, 0u));
-          if (Q <= tq) exact(pos);
+        if (k1 != kNone && vlo < vhi) {
+          const int p = (int)(k1 & 0xFFFFFu);
+          if (p >= t.rowStart[vlo] && p < t.rowStart[vhi]) bestk = min(bestk, cand_key(S, p, a, b, lo_p, hi_p));
         }
       }
-      bestk = __reduce_min_sync(0xFFFFFFFFu, bestk);
-      if (lane == 0) {
-        if (!first_chunk) bestk = min(bestk, best_out[o]);
-        best_out[o] = bestk;
+      sbest[lane] = bestk;
+      __syncwarp();
+      // tq: a candidate can still win (or tie) only if its lower bound 4Q-24 <= best SAD so far
+      int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(((bestk >> 19) + 24u) >> 2);
+      int qn = 0;  // queued groups (warp-uniform)
+
+      // exact SAD + window test of up to 32 queued (origin, group of 4 candidates) entries, one per
+      // lane; the origin's record comes from its owner lane by shuffle, the result goes back
+      // through a shared-memory atomicMin.  Every lane then refreshes its bound.
+      auto flush = [&]() {
+        const int n = min(qn, 32);
+        qn -= n;
+        const bool on = lane < n;
+        const uint32_t e = on ? queue[qn + lane] : 0u;
+        const int owner = (int)(e >> 16), p = (int)(e & 0xFFFFu) << 2;
+        uint4 oa, ob;
+        oa.x = __shfl_sync(FULL, a.x, owner); oa.y = __shfl_sync(FULL, a.y, owner);
+        oa.z = __shfl_sync(FULL, a.z, owner); oa.w = __shfl_sync(FULL, a.w, owner);
+        ob.x = __shfl_sync(FULL, b.x, owner); ob.y = __shfl_sync(FULL, b.y, owner);
+        ob.z = __shfl_sync(FULL, b.z, owner); ob.w = __shfl_sync(FULL, b.w, owner);
+        const uint32_t olo = __shfl_sync(FULL, lo_p, owner), ohi = __shfl_sync(FULL, hi_p, owner);
+        if (on) {
+          uint32_t k = cand_key(S, p, oa, ob, olo, ohi);
+          k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
+          k = min(k, cand_key(S, p + 2, oa, ob, olo, ohi));
+          k = min(k, cand_key(S, p + 3, oa, ob, olo, ohi));
+          if (k != kNone) atomicMin(&sbest[owner], k);
+        }
+        __syncwarp();
+        bestk = sbest[lane];
+        tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(((bestk >> 19) + 24u) >> 2);
+      };
+
+      for (int r = rlo; r < rhi; r++) {
+        const bool act = (r >= vlo) && (r < vhi);
+        int tqe = act ? tq : -1;  // tq while this lane searches the current row, else -1 (never passes)
+        const int p0 = t.segOff[r][j0], p1 = t.segOff[r][j1];
+#pragma unroll 2
+        for (int p = p0; p < p1; p += 4) {
+          bool hit = act;
+          if (PRUNE) {
+            const uint4 qx = Q4[p >> 1], qy = Q4[(p >> 1) + 1];
+            const int Q0 = sadq(qa, qx.x, qx.y), Q1 = sadq(qa, qx.z, qx.w);
+            const int Q2 = sadq(qa, qy.x, qy.y), Q3 = sadq(qa, qy.z, qy.w);
+            hit = min(min(Q0, Q1), min(Q2, Q3)) <= tqe;
+          }
+          const uint32_t bal = __ballot_sync(FULL, hit);
+          if (bal) {  // warp-uniform: queue the groups that may still hold a winner
+            if (hit) queue[qn + __popc(bal & lt_mask)] = ((uint32_t)lane << 16) | (uint32_t)(p >> 2);
+            qn += __popc(bal);
+            if (qn >= 32) {
+              __syncwarp();
+              flush();
+              tqe = act ? tq : -1;
+            }
+          }
+        }
       }
-      o = on;
+      __syncwarp();
+      while (qn > 0) flush();
+      if (valid) bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
+      __syncwarp();  // sbest/queue are reused by this warp's next task
     }
     first_chunk = false;
     ra = rb;
     if (ra >= row_hi) break;
+  }
+  return true;
+}
+
+template <bool PRUNE, int THREADS>
+__global__ void __launch_bounds__(THREADS, 2)
+k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __restrict__ best, int rows_per_group,
+         int ngroups) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  K2Smem& S = *reinterpret_cast<K2Smem*>(smem_raw);
+  const int cg = blockIdx.x / ngroups, grp = blockIdx.x - cg * ngroups;
+  const int c = blockIdx.y >> 1, dir = blockIdx.y & 1;
+  const int2 pr = pairs[blockIdx.z];  // x = prev slot, y = curr slot
+  const int from_slot = dir ? pr.x : pr.y, to_slot = dir ? pr.y : pr.x;
+  const int ub0 = cg * kOC;
+  const int noc = min(kOC, (g.U - 1) - ub0);  // origin columns 0..U-2 only (src/myMatch.cpp:141-146)
+  uint32_t* best_dir = best + (int64_t)(blockIdx.z * 2 + dir) * g.U * 4 * g.col_cap;
+  // joint pass over both columns; if a row of the shared window does not fit, one pass per column
+  for (int it = -1;;) {
+    const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
+                                               it < 0 ? noc : 1, grp, rows_per_group);
+    if (it < 0 && ok) break;
+    if (++it >= noc) break;
   }
 }
 
@@ -449,26 +535,29 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
   }
 }
 
-template <bool PRUNE>
+template <bool PRUNE, int THREADS>
 static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
                                int rows_per_group, cudaStream_t st) {
   static bool attr_set = false;
-  const int bytes = (int)sizeof(K2Smem<PRUNE>);
+  const int bytes = (int)sizeof(K2Smem);
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k2_match<PRUNE>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    cudaError_t e = cudaFuncSetAttribute(k2_match<PRUNE, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
-  dim3 grid((g.U - 1) * ngroups, 8, n_pairs);
-  k2_match<PRUNE><<<grid, K2_THREADS, bytes, st>>>(g, fa, pairs, best, rows_per_group, ngroups);
+  const int cgroups = (g.U - 1 + kOC - 1) / kOC;
+  dim3 grid(cgroups * ngroups, 8, n_pairs);
+  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, pairs, best, rows_per_group, ngroups);
   return cudaGetLastError();
 }
 
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
-                      int rows_per_group, int prune, cudaStream_t st) {
-  return prune ? launch_k2_t<true>(g, fa, pairs, n_pairs, best, rows_per_group, st)
-               : launch_k2_t<false>(g, fa, pairs, n_pairs, best, rows_per_group, st);
+                      int rows_per_group, int prune, int threads, cudaStream_t st) {
+  if (!prune) return launch_k2_t<false, 256>(g, fa, pairs, n_pairs, best, rows_per_group, st);
+  if (threads == 256) return launch_k2_t<true, 256>(g, fa, pairs, n_pairs, best, rows_per_group, st);
+  if (threads == 384) return launch_k2_t<true, 384>(g, fa, pairs, n_pairs, best, rows_per_group, st);
+  return launch_k2_t<true, 512>(g, fa, pairs, n_pairs, best, rows_per_group, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,

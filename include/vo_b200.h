@@ -66,7 +66,8 @@ typedef struct vo_config {
   int32_t match_rows_per_cta; /* tuning: origin v-bin rows per matching CTA (0 = auto: whole column) */
   int32_t match_exhaustive;   /* 0: exact lower-bound pruning in the SAD search (default); 1: evaluate every SAD.
                                  Results are bit-identical either way. */
-  int32_t reserved[6];
+  int32_t match_threads;      /* tuning: threads per matching CTA (256, 384 or 512; 0 = library default) */
+  int32_t reserved[5];
 } vo_config;
 
 /* Derived geometry (what src/size.h spells as macros). */
