@@ -49,7 +49,7 @@ struct K2Tables {
 struct __align__(128) K2Smem {
   K2Tables t;
   uint32_t sbest[kMaxWarps][32];      // running best key of the 32 origins of a warp's task
-  uint32_t queue[kMaxWarps][kQueue];  // deferred exact evaluations: owner lane << 16 | candidate group
+  uint32_t queue[kMaxWarps][kQueue + 32];  // deferred exact evaluations: owner lane << 16 | candidate group (+32 dump slots)
   __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
   uint4 hi[kCandCap];                 // descriptor bytes 16..31
   uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
@@ -181,7 +181,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
   const uint4* Q4 = reinterpret_cast<const uint4*>(S.q);
   uint32_t* sbest = S.sbest[warp];
   uint32_t* queue = S.queue[warp];
-  const uint32_t lt_mask = (1u << lane) - 1u;
+  uint32_t* qdump = queue + kQueue + lane;
+  const uint32_t lt_mask = (1u << lane) - 1u, lane16 = (uint32_t)lane << 16;
 
   bool first_chunk = true;
   for (int ra = row_lo;;) {
@@ -318,26 +319,46 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       for (int r = rlo; r < rhi; r++) {
         const bool act = (r >= vlo) && (r < vhi);
         int tqe = act ? tq : -1;  // tq while this lane searches the current row, else -1 (never passes)
-        const int p0 = t.segOff[r][j0], p1 = t.segOff[r][j1];
+        int pg = t.segOff[r][j0] >> 2;            // candidate groups of 4 (every bin list is padded to 4)
+        const int pg1 = t.segOff[r][j1] >> 2;
+        const uint4* qp = Q4 + 2 * pg;
+        // queue the groups of this lane that may still hold a winner (warp-uniform control flow)
+        auto enqueue = [&](bool hit, int grp4) {
+          const uint32_t bal = __ballot_sync(FULL, hit);
+          uint32_t* dst = hit ? queue + qn + __popc(bal & lt_mask) : qdump;  // branch-free: misses hit a dump slot
+          *dst = lane16 | (uint32_t)grp4;
+          qn += __popc(bal);
+          if (qn >= 32) {
+            __syncwarp();
+            flush();
+            tqe = act ? tq : -1;
+          }
+        };
+        if (PRUNE) {
+          // two groups (8 candidates) per vote: independent loads and SAD chains in flight
 #pragma unroll 2
-        for (int p = p0; p < p1; p += 4) {
-          bool hit = act;
-          if (PRUNE) {
-            const uint4 qx = Q4[p >> 1], qy = Q4[(p >> 1) + 1];
+          for (; pg + 1 < pg1; pg += 2, qp += 4) {
+            const uint4 qx = qp[0], qy = qp[1], qz = qp[2], qw = qp[3];
             const int Q0 = sadq(qa, qx.x, qx.y), Q1 = sadq(qa, qx.z, qx.w);
             const int Q2 = sadq(qa, qy.x, qy.y), Q3 = sadq(qa, qy.z, qy.w);
-            hit = min(min(Q0, Q1), min(Q2, Q3)) <= tqe;
-          }
-          const uint32_t bal = __ballot_sync(FULL, hit);
-          if (bal) {  // warp-uniform: queue the groups that may still hold a winner
-            if (hit) queue[qn + __popc(bal & lt_mask)] = ((uint32_t)lane << 16) | (uint32_t)(p >> 2);
-            qn += __popc(bal);
-            if (qn >= 32) {
-              __syncwarp();
-              flush();
-              tqe = act ? tq : -1;
+            const int Q4_ = sadq(qa, qz.x, qz.y), Q5 = sadq(qa, qz.z, qz.w);
+            const int Q6 = sadq(qa, qw.x, qw.y), Q7 = sadq(qa, qw.z, qw.w);
+            const int ma = min(min(Q0, Q1), min(Q2, Q3)), mb = min(min(Q4_, Q5), min(Q6, Q7));
+            if (__any_sync(FULL, min(ma, mb) <= tqe)) {
+              enqueue(ma <= tqe, pg);
+              enqueue(mb <= tqe, pg + 1);
             }
           }
+          if (pg < pg1) {
+            const uint4 qx = qp[0], qy = qp[1];
+            const int Q0 = sadq(qa, qx.x, qx.y), Q1 = sadq(qa, qx.z, qx.w);
+            const int Q2 = sadq(qa, qy.x, qy.y), Q3 = sadq(qa, qy.z, qy.w);
+            const bool hit = min(min(Q0, Q1), min(Q2, Q3)) <= tqe;
+            if (__any_sync(FULL, hit)) enqueue(hit, pg);
+          }
+        } else {
+          for (; pg < pg1; pg++)
+            if (__any_sync(FULL, act)) enqueue(act, pg);
         }
       }
       __syncwarp();
