@@ -123,51 +123,85 @@ def run_reference(args):
 # clocks
 # --------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed region: NVML polled from a thread every
+    few ms (nvidia-smi's own loop is too coarse for a sub-second region), nvidia-smi as fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index: int):
-        self.index = index
-        self.proc = None
-        self.lines = []
+    def __init__(self, index: int, period_s: float = 0.004):
+        self.index, self.period = index, period_s
+        self.sm, self.reasons, self.mx = [], set(), None
+        self.stop_flag = threading.Event()
+        self.thread = None
+        self.how = None
 
-    def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
-                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._pump, daemon=True)
-            self.thread.start()
-        except Exception:
-            self.proc = None
+    def _nvml_loop(self, nv, h):
+        bits = {}
+        for nm, attr in (("hw_slowdown", "nvmlClocksEventReasonHwSlowdown"), ("hw_thermal_slowdown", "nvmlClocksEventReasonHwThermalSlowdown"),
+                         ("sw_thermal_slowdown", "nvmlClocksEventReasonSwThermalSlowdown"), ("sw_power_cap", "nvmlClocksEventReasonSwPowerCap")):
+            alt = attr.replace("ClocksEventReason", "ClocksThrottleReason")
+            bits[nm] = getattr(nv, attr, getattr(nv, alt, 0))
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = get_reasons(h)
+                for nm, b in bits.items():
+                    if b and (r & b):
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(self.period)
 
-    def _pump(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
-
-    def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
+    def _smi_loop(self):
+        proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20", "-i",
+                                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        import select
+        while not self.stop_flag.is_set():
+            if not select.select([proc.stdout], [], [], 0.05)[0]:
+                continue
+            ln = proc.stdout.readline()
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 6:
                 continue
             try:
-                sm.append(float(parts[0])); mx.append(float(parts[1]))
+                self.sm.append(float(parts[0])); self.mx = max(self.mx or 0.0, float(parts[1]))
             except ValueError:
                 continue
             for nm, val in zip(names, parts[2:6]):
                 if val.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                    self.reasons.add(nm)
+        proc.terminate()
+
+    def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            idx = self.index
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis:
+                try:
+                    idx = int(vis.split(",")[self.index])
+                except (ValueError, IndexError):
+                    pass
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.how = "nvml"
+            self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+        except Exception:
+            self.how = "nvidia-smi"
+            self.thread = threading.Thread(target=self._smi_loop, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        self.stop_flag.set()
+        if self.thread:
+            self.thread.join(timeout=5)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["no clock samples"], "samples": 0, "how": self.how}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": self.mx, "reasons": sorted(self.reasons),
+                "samples": len(self.sm), "how": self.how}
 
 
 # --------------------------------------------------------------------------------------------
@@ -211,8 +245,10 @@ def run_ours(args):
     eng = Engine(W, H, max_frames=2 * B, max_pairs=B, device=local_rank, stream=stream.cuda_stream,
                  match_rows_per_cta=args.rows)
     max_keep = 512
-    counts = pinned_empty((2 * B,), np.int32)
-    out_lists = pinned_empty((B, max_keep), P_MATCH_DTYPE)
+    # double-buffered host results: the download of step s overlaps the kernels of step s+1
+    counts = [pinned_empty((2 * B,), np.int32) for _ in range(2)]
+    out_lists = [pinned_empty((B, max_keep), P_MATCH_DTYPE) for _ in range(2)]
+    consumed = [0]
 
     def slots_of(step):
         base = (step % 2) * B
@@ -226,26 +262,39 @@ def run_ours(args):
         eng.batch_extract_device(base, dev_pool.data_ptr() + f0 * H * pitch, B, H * pitch, pitch)
         eng.batch_match(prev, curr, 2, 50.0, 50.0)
 
-    def step_e2e(step):
+    def consume(buf):
+        eng.fence_wait(buf)                                # step's counts + bucketed lists are on the host
+        consumed[0] += int(counts[buf][B:].sum())
+
+    def step_e2e(step, first):
+        # software pipeline, depth 2 (the reference's FPGA host does the same, hls_opencl/host/main2.cpp:449-518):
+        # H2D of this step runs on the upload stream while the previous step's kernels run; its D2H runs on
+        # the download stream; the host blocks only on the PREVIOUS step's result.
         base, prev, curr = slots_of(step)
         f0 = (step * B) % pool_frames
+        buf = step % 2
         eng.batch_extract_host(base, host_pool[f0:f0 + B])
         eng.batch_match(prev, curr, 2, 50.0, 50.0)
-        eng.batch_download_async(B, 1, counts, out_lists, max_keep, max_keep)
-        eng.synchronize()                                  # the step's result is on the host
+        eng.batch_download_async(B, 1, counts[buf], out_lists[buf], max_keep, max_keep)
+        eng.fence_record(buf)
+        if step > first:
+            consume(1 - buf)
 
     def barrier():
         if dist is not None:
             dist.barrier()
+        eng.synchronize()
         torch.cuda.synchronize()
 
-    def timed(fn, first_step):
+    def timed(fn, first_step, drain=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record(stream)
         for s in range(args.steps):
             fn(first_step + s)
+        if drain:
+            drain()
         e1.record(stream)
         barrier()
         wall = time.perf_counter() - t0
@@ -272,9 +321,13 @@ def run_ours(args):
     launches = eng.launch_count() - launches0
     raw_n, bk_n = eng.batch_counts(B)
     n_feat = [eng.slot_feature_count(s) for s in range(0, 2 * B, max(1, (2 * B) // 8))]
-    for s in range(3):
-        step_e2e(step0 + args.steps + s)
-    e2e_ms, e2e_wall = timed(step_e2e, step0 + args.steps + 3)
+    e2e_first = step0 + args.steps
+    for s in range(3):                                     # e2e warm-up (pinned pages, copy engines)
+        step_e2e(e2e_first + s, e2e_first)
+    consume((e2e_first + 2) % 2)
+    e2e_first += 3
+    last = e2e_first + args.steps - 1
+    e2e_ms, e2e_wall = timed(lambda st: step_e2e(st, e2e_first), e2e_first, drain=lambda: consume(last % 2))
     e2e_ms = max(e2e_ms, e2e_wall * 1e3)                  # host-visible completion is what counts
     clocks = sampler.stop() if sampler else None
 
@@ -318,9 +371,10 @@ def run_ours(args):
     cpu = None
     if world == 1 and not args.no_cpu:
         cores = max(1, min(os.cpu_count() or 1, 64))
-        v, kind, wall, total = cpu_throughput(W, H, 2, cores)
+        ppw = 12
+        v, kind, wall, total = cpu_throughput(W, H, ppw, cores)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
-               "sample": f"{cores} single-threaded processes x 2 consecutive pairs ({total} pairs, {wall:.1f} s wall) of "
+               "sample": f"{cores} single-threaded processes x {ppw} consecutive pairs ({total} pairs, {wall:.1f} s wall) of "
                          f"the same {W}x{H} synthetic sequence type: myComputeFeatures+myMatching from oracle/_ref, "
                          f"bucketing via the oracle port"}
 
@@ -334,9 +388,11 @@ def run_ours(args):
                    "features_per_frame": n_c, "raw_matches_per_pair": n_m, "bucketed_per_pair": n_b,
                    "sharding": "independent sequences per GPU, no collective"},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * H * W) * world,
-                "d2h_bytes_per_step": int(counts.nbytes + B * max_keep * 48) * world,
-                "ms_per_step": e2e_ms / args.steps},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * H * pitch) * world,
+                "d2h_bytes_per_step": int(counts[0].nbytes + B * max_keep * 48) * world,
+                "ms_per_step": e2e_ms / args.steps, "pipeline": "depth 2: H2D(s+1) | kernels(s) | D2H(s-1) on three streams; "
+                "every step's frames go host->device and its counts+bucketed lists come back inside the timed region",
+                "bucketed_matches_read_back": consumed[0]},
         "gpu_launches": int(launches) * world,
         "roofline": roofline,
         "cpu_baseline": cpu,
@@ -350,13 +406,13 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=W_DEFAULT)
     ap.add_argument("--height", type=int, default=H_DEFAULT)
-    ap.add_argument("--batch", type=int, default=64, help="frame pairs per step per GPU")
-    ap.add_argument("--pool", type=int, default=320, help="distinct frames cycled (keeps inputs larger than L2)")
+    ap.add_argument("--batch", type=int, default=128, help="frame pairs per step per GPU")
+    ap.add_argument("--pool", type=int, default=384, help="distinct frames cycled (keeps inputs larger than L2)")
     ap.add_argument("--rows", type=int, default=0, help="match_rows_per_cta tuning knob (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     args = ap.parse_args()

@@ -45,8 +45,8 @@ class VoGeometry(C.Structure):
 
 # every symbol include/vo_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = [
-    "vo_engine_create", "vo_engine_destroy", "vo_engine_geometry", "vo_engine_synchronize", "vo_last_error",
-    "vo_version", "vo_compute_features", "vo_matching", "vo_bucket_matches", "vo_push_back", "vo_match_features",
+    "vo_engine_create", "vo_engine_destroy", "vo_engine_geometry", "vo_engine_synchronize", "vo_fence_record",
+    "vo_fence_wait", "vo_last_error", "vo_version", "vo_compute_features", "vo_matching", "vo_bucket_matches", "vo_push_back", "vo_match_features",
     "vo_bucket_features", "vo_get_matches", "vo_num_matches", "vo_set_matches", "vo_dump_features",
     "vo_batch_extract_host", "vo_batch_extract_device", "vo_batch_match", "vo_batch_counts",
     "vo_batch_get_matches", "vo_batch_download_async", "vo_slot_dump_features", "vo_slot_feature_count",
@@ -98,6 +98,8 @@ def load_library() -> C.CDLL:
         "vo_launch_count": [vp, C.POINTER(i64)],
         "vo_profile_enable": [vp, i32],
         "vo_profile_read": [vp, C.POINTER(C.c_double), C.POINTER(i64), i32],
+        "vo_fence_record": [vp, i32],
+        "vo_fence_wait": [vp, i32],
         "vo_host_alloc": [C.POINTER(vp), i64],
         "vo_host_free": [vp],
     }
@@ -156,6 +158,13 @@ class Engine:
 
     def synchronize(self):
         self._check(self.lib.vo_engine_synchronize(self.h))
+
+    def fence_record(self, idx: int):
+        """Mark 'everything enqueued so far, downloads included' (pipeline fence idx in [0,8))."""
+        self._check(self.lib.vo_fence_record(self.h, idx))
+
+    def fence_wait(self, idx: int):
+        self._check(self.lib.vo_fence_wait(self.h, idx))
 
     # ---- operator level ------------------------------------------------------------------
     def new_feature_arrays(self, cap_stride: int | None = None):

@@ -64,8 +64,14 @@ struct vo_engine {
   vo_config cfg{};
   vo::Geom g{};
   int device = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;       // compute (and every synchronous entry point)
   bool own_stream = false;
+  // batch-level software pipeline: uploads and downloads run on their own streams so that the
+  // H2D copy of batch s+1 and the D2H copy of batch s-1 overlap the kernels of batch s
+  cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+  cudaEvent_t ev_h2d_done = nullptr, ev_k1_done = nullptr, ev_compute_done = nullptr, ev_d2h_done = nullptr;
+  bool d2h_pending = false;
+  cudaEvent_t fences[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   int n_slots = 0, n_pairbuf = 0;       // incl. the operator-level scratch slots / pair
   int op_slot_a = 0, op_slot_b = 0, op_pair = 0;
   int rows_per_group = 0, prune = 1, match_threads = 0;
@@ -196,25 +202,35 @@ vo_status do_extract(vo_engine* e, const CUtensorMap& tm, int first_slot, int z_
     CU_TRY(vo::launch_k1(tm, g, e->fa, first_slot, z_base, n, e->stream));
     e->launches += 1;
   }
+  CU_TRY(cudaEventRecord(e->ev_k1_done, e->stream));  // the image slots may be overwritten from here on
   return VO_OK;
 }
 
 vo_status upload_images(vo_engine* e, int first_slot, int n, const uint8_t* images, int64_t frame_stride, int pitch,
-                        cudaMemcpyKind kind) {
+                        cudaMemcpyKind kind, cudaStream_t st = nullptr) {
+  if (!st) st = e->stream;
   const vo::Geom& g = e->g;
   uint8_t* dst = e->fa.img + (int64_t)first_slot * e->fa.img_stride;
-  if (frame_stride == (int64_t)pitch * g.H) {
-    CU_TRY(cudaMemcpy2DAsync(dst, g.pitch, images, pitch, g.W, (size_t)g.H * n, kind, e->stream));
+  if (pitch == g.pitch && frame_stride == e->fa.img_stride) {
+    // caller's layout == slot layout (16-byte row pitch): one linear copy at full link speed; the
+    // pad bytes beyond W travel too but TMA never reads past the tensor's W
+    CU_TRY(cudaMemcpyAsync(dst, images, (size_t)e->fa.img_stride * n, kind, st));
+  } else if (frame_stride == (int64_t)pitch * g.H) {
+    CU_TRY(cudaMemcpy2DAsync(dst, g.pitch, images, pitch, g.W, (size_t)g.H * n, kind, st));
   } else {
     for (int i = 0; i < n; i++)
       CU_TRY(cudaMemcpy2DAsync(dst + (int64_t)i * e->fa.img_stride, g.pitch, images + (int64_t)i * frame_stride, pitch,
-                               g.W, g.H, kind, e->stream));
+                               g.W, g.H, kind, st));
   }
   return VO_OK;
 }
 
 vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float bw, float bh) {
   const vo::Geom& g = e->g;
+  if (e->d2h_pending) {  // the pair buffers are still being downloaded by the previous batch
+    CU_TRY(cudaStreamWaitEvent(e->stream, e->ev_d2h_done, 0));
+    e->d2h_pending = false;
+  }
   {
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
@@ -327,6 +343,15 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
     e->own_stream = true;
   }
 
+  {
+    bool ok = cudaStreamCreateWithFlags(&e->h2d_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking) == cudaSuccess;
+    cudaEvent_t* evs[4] = {&e->ev_h2d_done, &e->ev_k1_done, &e->ev_compute_done, &e->ev_d2h_done};
+    for (auto ev : evs) ok = ok && cudaEventCreateWithFlags(ev, cudaEventDisableTiming) == cudaSuccess;
+    for (auto& f : e->fences) ok = ok && cudaEventCreateWithFlags(&f, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "pipeline stream/event create"); }
+  }
+
 #define ALLOC(ptr, bytes)                                                                        \
   do {                                                                                           \
     cudaError_t _e = cudaMalloc((void**)&(ptr), (bytes));                                        \
@@ -389,6 +414,10 @@ void vo_engine_destroy(vo_engine* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  if (e->h2d_stream) { cudaStreamSynchronize(e->h2d_stream); cudaStreamDestroy(e->h2d_stream); }
+  if (e->d2h_stream) { cudaStreamSynchronize(e->d2h_stream); cudaStreamDestroy(e->d2h_stream); }
+  for (cudaEvent_t ev : {e->ev_h2d_done, e->ev_k1_done, e->ev_compute_done, e->ev_d2h_done}) if (ev) cudaEventDestroy(ev);
+  for (auto& f : e->fences) if (f) cudaEventDestroy(f);
   cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc); cudaFree(e->fa.q);
   cudaFree(e->d_pairs); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
@@ -413,7 +442,25 @@ vo_status vo_engine_geometry(const vo_engine* e, vo_geometry* out) {
 
 vo_status vo_engine_synchronize(vo_engine* e) {
   if (!e) return fail(VO_ERR_INVALID, "null engine");
+  CU_TRY(cudaStreamSynchronize(e->h2d_stream));
   CU_TRY(cudaStreamSynchronize(e->stream));
+  CU_TRY(cudaStreamSynchronize(e->d2h_stream));
+  return VO_OK;
+}
+
+vo_status vo_fence_record(vo_engine* e, int32_t idx) {
+  if (!e || idx < 0 || idx >= 8) return fail(VO_ERR_INVALID, "fence index outside [0,8)");
+  CU_TRY(cudaSetDevice(e->device));
+  // everything enqueued so far: the compute stream's tail, then the download stream's tail
+  CU_TRY(cudaEventRecord(e->ev_compute_done, e->stream));
+  CU_TRY(cudaStreamWaitEvent(e->d2h_stream, e->ev_compute_done, 0));
+  CU_TRY(cudaEventRecord(e->fences[idx], e->d2h_stream));
+  return VO_OK;
+}
+
+vo_status vo_fence_wait(vo_engine* e, int32_t idx) {
+  if (!e || idx < 0 || idx >= 8) return fail(VO_ERR_INVALID, "fence index outside [0,8)");
+  CU_TRY(cudaEventSynchronize(e->fences[idx]));
   return VO_OK;
 }
 
@@ -634,8 +681,14 @@ vo_status vo_batch_extract_host(vo_engine* e, int32_t first_slot, int32_t n, con
   if (n < 1 || first_slot < 0 || first_slot + n > e->cfg.max_frames) return fail(VO_ERR_INVALID, "slot range [%d,%d) outside [0,%d)", first_slot, first_slot + n, e->cfg.max_frames);
   if (pitch_bytes < e->g.W || frame_stride_bytes < (int64_t)pitch_bytes * e->g.H) return fail(VO_ERR_INVALID, "ERROR: Image dimension mismatch!");
   CU_TRY(cudaSetDevice(e->device));
-  vo_status s = upload_images(e, first_slot, n, images, frame_stride_bytes, pitch_bytes, cudaMemcpyHostToDevice);
+  // upload on the copy stream: it only has to wait for the last extraction that read the image
+  // slots, so it overlaps the matching kernels of the previous batch
+  CU_TRY(cudaStreamWaitEvent(e->h2d_stream, e->ev_k1_done, 0));
+  vo_status s = upload_images(e, first_slot, n, images, frame_stride_bytes, pitch_bytes, cudaMemcpyHostToDevice,
+                              e->h2d_stream);
   if (s != VO_OK) return s;
+  CU_TRY(cudaEventRecord(e->ev_h2d_done, e->h2d_stream));
+  CU_TRY(cudaStreamWaitEvent(e->stream, e->ev_h2d_done, 0));
   return do_extract(e, e->tmap_slots, first_slot, first_slot, n);
 }
 
@@ -706,13 +759,17 @@ vo_status vo_batch_download_async(vo_engine* e, int32_t n_pairs, int32_t which, 
   if (out && (max_per_pair < 1 || max_per_pair > e->cfg.max_matches || stride_matches < max_per_pair))
     return fail(VO_ERR_INVALID, "bad list geometry");
   CU_TRY(cudaSetDevice(e->device));
-  CU_TRY(cudaMemcpyAsync(counts, e->d_n_raw, 4 * n_pairs, cudaMemcpyDeviceToHost, e->stream));
-  CU_TRY(cudaMemcpyAsync(counts + n_pairs, e->d_n_bucketed, 4 * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaEventRecord(e->ev_compute_done, e->stream));
+  CU_TRY(cudaStreamWaitEvent(e->d2h_stream, e->ev_compute_done, 0));
+  CU_TRY(cudaMemcpyAsync(counts, e->d_n_raw, 4 * n_pairs, cudaMemcpyDeviceToHost, e->d2h_stream));
+  CU_TRY(cudaMemcpyAsync(counts + n_pairs, e->d_n_bucketed, 4 * n_pairs, cudaMemcpyDeviceToHost, e->d2h_stream));
   if (out) {
     const vo_p_match* src = which ? e->d_bucketed : e->d_raw;
     CU_TRY(cudaMemcpy2DAsync(out, sizeof(vo_p_match) * stride_matches, src, sizeof(vo_p_match) * (size_t)e->cfg.max_matches,
-                             sizeof(vo_p_match) * (size_t)max_per_pair, n_pairs, cudaMemcpyDeviceToHost, e->stream));
+                             sizeof(vo_p_match) * (size_t)max_per_pair, n_pairs, cudaMemcpyDeviceToHost, e->d2h_stream));
   }
+  CU_TRY(cudaEventRecord(e->ev_d2h_done, e->d2h_stream));
+  e->d2h_pending = true;
   return VO_OK;
 }
 

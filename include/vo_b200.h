@@ -94,6 +94,11 @@ vo_status vo_engine_create(const vo_config* cfg, int32_t device, void* stream, v
 void      vo_engine_destroy(vo_engine* e);
 vo_status vo_engine_geometry(const vo_engine* e, vo_geometry* out);
 vo_status vo_engine_synchronize(vo_engine* e);
+/* Fences for the batch-level software pipeline (the double-buffered event graph of the reference's
+ * FPGA host, hls_opencl/host/main2.cpp:449-518).  vo_fence_record(idx) marks "everything enqueued
+ * so far, downloads included"; vo_fence_wait(idx) blocks the host until that point.  idx in [0,8). */
+vo_status vo_fence_record(vo_engine* e, int32_t idx);
+vo_status vo_fence_wait(vo_engine* e, int32_t idx);
 const char* vo_last_error(void);            /* thread-local text of the last failure */
 const char* vo_version(void);
 
@@ -154,7 +159,8 @@ vo_status vo_dump_features(vo_engine* e, int32_t which, int32_t* max2, int32_t* 
 
 /* Extract features of `n` frames into frame slots first_slot .. first_slot+n-1 (one launch).
  * Host variant: frames at images + i*frame_stride_bytes, rows pitch_bytes apart; the H2D copy is
- * enqueued on the engine stream.  Device variant: same addressing in device memory. */
+ * enqueued on the engine's upload stream (it overlaps the kernels of the previous batch; the host
+ * buffer must stay valid until a later fence / synchronize).  Device variant: same addressing in device memory. */
 vo_status vo_batch_extract_host(vo_engine* e, int32_t first_slot, int32_t n, const uint8_t* images,
                                 int64_t frame_stride_bytes, int32_t pitch_bytes);
 vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n,
@@ -170,8 +176,8 @@ vo_status vo_batch_counts(vo_engine* e, int32_t n_pairs, int32_t* raw, int32_t* 
 /* Copy pair i's raw (which=0) or bucketed (which=1) list to the host. Synchronises. */
 vo_status vo_batch_get_matches(vo_engine* e, int32_t pair, int32_t which, vo_p_match* out,
                                int32_t cap, int32_t* n);
-/* Enqueue D2H of all n_pairs count words + lists into caller (ideally pinned) memory without
- * synchronising: counts int32[2*n_pairs] = {raw, bucketed} per pair; lists laid out
+/* Enqueue D2H (on the engine's download stream, after the kernels enqueued so far) of all n_pairs
+ * count words + lists into caller (ideally pinned) memory without synchronising: counts int32[2*n_pairs] = {raw, bucketed} per pair; lists laid out
  * out + i*stride_matches.  which selects raw (0) / bucketed (1) lists. */
 vo_status vo_batch_download_async(vo_engine* e, int32_t n_pairs, int32_t which, int32_t* counts,
                                   vo_p_match* out, int64_t stride_matches, int32_t max_per_pair);
