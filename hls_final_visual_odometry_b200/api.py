@@ -45,7 +45,8 @@ class VoGeometry(C.Structure):
 
 # every symbol include/vo_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = [
-    "vo_engine_create", "vo_engine_destroy", "vo_engine_geometry", "vo_engine_synchronize", "vo_fence_record",
+    "vo_engine_create", "vo_engine_destroy", "vo_engine_geometry", "vo_engine_synchronize", "vo_remove_outliers_host",
+    "vo_remove_outliers", "vo_fence_record",
     "vo_fence_wait", "vo_last_error", "vo_version", "vo_compute_features", "vo_matching", "vo_bucket_matches", "vo_push_back", "vo_match_features",
     "vo_bucket_features", "vo_get_matches", "vo_num_matches", "vo_set_matches", "vo_dump_features",
     "vo_batch_extract_host", "vo_batch_extract_device", "vo_batch_match", "vo_batch_counts",
@@ -98,6 +99,8 @@ def load_library() -> C.CDLL:
         "vo_launch_count": [vp, C.POINTER(i64)],
         "vo_profile_enable": [vp, i32],
         "vo_profile_read": [vp, C.POINTER(C.c_double), C.POINTER(i64), i32],
+        "vo_remove_outliers_host": [vp, C.POINTER(i32)],
+        "vo_remove_outliers": [vp],
         "vo_fence_record": [vp, i32],
         "vo_fence_wait": [vp, i32],
         "vo_host_alloc": [C.POINTER(vp), i64],
@@ -204,6 +207,10 @@ class Engine:
     def match_features(self, method: int = 0):
         self._check(self.lib.vo_match_features(self.h, method))
 
+    def remove_outliers(self):
+        """The removeOutliers call of Matcher::matchFeatures (src/matcher.cpp:108) on the current raw list."""
+        self._check(self.lib.vo_remove_outliers(self.h))
+
     def bucket_features(self, max_features=2, bw=50.0, bh=50.0):
         self._check(self.lib.vo_bucket_features(self.h, max_features, bw, bh))
 
@@ -287,6 +294,17 @@ class Engine:
         return {k: (ms[i], calls[i]) for i, k in enumerate(names)}
 
 
+def remove_outliers_host(matches: np.ndarray) -> np.ndarray:
+    """removeOutliers (src/remove_outliers.cpp:4) on a host list; needs no GPU (host stage of the path)."""
+    lib = load_library()
+    buf = np.array(matches, dtype=P_MATCH_DTYPE, copy=True)
+    n = C.c_int32(len(buf))
+    st = lib.vo_remove_outliers_host(_ptr(buf) if len(buf) else None, C.byref(n))
+    if st != VO_OK:
+        raise VoError(st, "vo_remove_outliers_host")
+    return buf[: n.value].copy()
+
+
 def pinned_empty(shape, dtype) -> np.ndarray:
     """numpy array backed by page-locked host memory from vo_host_alloc (never freed: bench lifetime)."""
     lib = load_library()
@@ -334,7 +352,9 @@ class Matcher:
         self.engine.push_back(I1, replace)
 
     def matchFeatures(self, method=0, Tr_delta=None):
+        # src/matcher.cpp:93-111: myMatching, then the host-side removeOutliers
         self.engine.match_features(method)
+        self.engine.remove_outliers()
 
     def bucketFeatures(self, max_features, bucket_width, bucket_height):
         self.engine.bucket_features(max_features, bucket_width, bucket_height)

@@ -21,6 +21,8 @@ DEMO = os.path.join(_PKG, "vo_demo")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall",
+    # the host Delaunay stage (vo_outliers.cpp) must round exactly like the reference's x86 build
+    "-Xcompiler", "-ffp-contract=off",
 ]
 
 
@@ -43,7 +45,7 @@ def _stale(target: str, deps: list[str]) -> bool:
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
-    srcs = _sources(CSRC, (".cu",))
+    srcs = _sources(CSRC, (".cu", ".cpp"))
     deps = srcs + _sources(CSRC, (".cuh",)) + [os.path.join(_ROOT, "include", "vo_b200.h")]
     if force or _stale(LIB, deps):
         cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", LIB, *srcs]

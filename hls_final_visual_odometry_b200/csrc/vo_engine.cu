@@ -665,6 +665,22 @@ vo_status vo_set_matches(vo_engine* e, const vo_p_match* in, int32_t n) {
   return VO_OK;
 }
 
+vo_status vo_remove_outliers(vo_engine* e) {
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  if (e->cur_which != 0) return fail(VO_ERR_STATE, "removeOutliers runs on the raw match list, before bucketing");
+  CU_TRY(cudaSetDevice(e->device));
+  int32_t n = 0;
+  vo_status s = vo_num_matches(e, &n);
+  if (s != VO_OK) return s;
+  if (n <= 3) return VO_OK;  // src/remove_outliers.cpp:6-7
+  std::vector<vo_p_match> host((size_t)n);
+  CU_TRY(cudaMemcpyAsync(host.data(), e->d_raw, sizeof(vo_p_match) * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  s = vo_remove_outliers_host(host.data(), &n);
+  if (s != VO_OK) return fail(s, "removeOutliers failed");
+  return vo_set_matches(e, host.data(), n);
+}
+
 vo_status vo_dump_features(vo_engine* e, int32_t which, int32_t* max2, int32_t* max2_num, int32_t cap_stride) {
   if (!e) return fail(VO_ERR_INVALID, "null engine");
   CU_TRY(cudaSetDevice(e->device));

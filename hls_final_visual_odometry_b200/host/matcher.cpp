@@ -47,11 +47,14 @@ void Matcher::matchFeatures(int32_t method, Matrix* /*Tr_delta*/) {
     std::cerr << "ERROR: " << vo_last_error() << std::endl;
     return;
   }
-  if (outlier_filter) {
+  if (outlier_filter) {  // caller-supplied replacement of the host stage
     std::vector<p_match> m = getMatches();
     outlier_filter(m);
     last_status = vo_set_matches(eng, reinterpret_cast<const vo_p_match*>(m.data()), (int32_t)m.size());
+  } else {
+    last_status = vo_remove_outliers(eng);  // removeOutliers(p_matched_2, p_matched_2_cnt), src/matcher.cpp:108
   }
+  if (last_status != VO_OK) std::cerr << "ERROR: " << vo_last_error() << std::endl;
 }
 
 void Matcher::bucketFeatures(int32_t max_features, float bucket_width, float bucket_height) {

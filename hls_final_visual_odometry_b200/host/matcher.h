@@ -6,9 +6,9 @@
 // Differences that are visible on purpose:
 //  * the image size is taken from `dims` at the first pushBack (the reference hard-wires
 //    1024x284 in src/size.h and ignores dims);
-//  * matchFeatures() runs the GPU circular matcher; the reference additionally runs its host-side
-//    Delaunay filter (removeOutliers, src/remove_outliers.cpp:4) inside matchFeatures -- here that
-//    stage is a plug-in (setOutlierFilter) until row F1 of SURVEY.md section 8 lands;
+//  * matchFeatures() runs the GPU circular matcher and then, as the reference does inside
+//    matchFeatures (src/matcher.cpp:108), the host-side Delaunay support filter
+//    (vo_remove_outliers, csrc/vo_outliers.cpp); setOutlierFilter() can replace that stage;
 //  * frame 0 yields zero matches instead of matching against uninitialised counts.
 #ifndef VO_B200_HOST_MATCHER_H
 #define VO_B200_HOST_MATCHER_H
@@ -79,7 +79,8 @@ class Matcher {
   // src/matcher.h:138-143: returns a copy
   std::vector<Matcher::p_match> getMatches();
 
-  // host stage between matching and bucketing (the reference's removeOutliers); in/out list
+  // optional replacement of the host stage between matching and bucketing (default: the
+  // reference's removeOutliers, src/remove_outliers.cpp:4); in/out list
   void setOutlierFilter(std::function<void(std::vector<Matcher::p_match>&)> f) { outlier_filter = f; }
 
   // last C-ABI status (0 = ok) and message, for callers that want more than the reference's cerr line

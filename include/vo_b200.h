@@ -122,6 +122,12 @@ vo_status vo_matching(vo_engine* e, const int32_t* m1p, const int32_t* n1p, cons
                       const int32_t* n1c, int32_t cap_stride, vo_p_match* p_matched,
                       int32_t p_matched_cap, int32_t* p_matched_num);
 
+/* removeOutliers(p_matched, p_matched_cnt): src/remove_outliers.cpp:4-94 (Delaunay triangulation of
+ * the current-frame coordinates, flow-consistency votes per triangle, keep support >= 4).  A HOST
+ * stage by design (sequential sweep-hull); single precision and visiting order
+ * follow src/delaunator.cpp so the kept set is the reference's.  In place; no engine needed. */
+vo_status vo_remove_outliers_host(vo_p_match* matches, int32_t* n);
+
 /* Matcher::bucketFeatures on an explicit list (src/matcher.cpp:140-187; FPGA: second half of
  * removeOutliers, hls_opencl/kernel/remove_outliers.cpp:104-154).  in and out may alias. */
 vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, int32_t max_features,
@@ -142,6 +148,10 @@ vo_status vo_push_back(vo_engine* e, const uint8_t* I1, const uint8_t* I2, const
  * `method` is accepted and ignored as in the reference.  With fewer than two frames pushed the
  * result is zero matches (frame-0 contract of hls_opencl/kernel/myMatch.cpp:221-224). */
 vo_status vo_match_features(vo_engine* e, int32_t method);
+/* the removeOutliers call inside Matcher::matchFeatures (src/matcher.cpp:108) on the engine's current
+ * raw list: download, vo_remove_outliers_host, upload.  vo_match_features + vo_remove_outliers ==
+ * the reference's matchFeatures. */
+vo_status vo_remove_outliers(vo_engine* e);
 /* Matcher::bucketFeatures(max_features, bucket_width, bucket_height): src/matcher.cpp:140-187 */
 vo_status vo_bucket_features(vo_engine* e, int32_t max_features, float bucket_w, float bucket_h);
 /* Matcher::getMatches(): src/matcher.h:138-143 */

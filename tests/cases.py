@@ -99,3 +99,54 @@ CASES = {
     "dead_zone_only": dead_zone_only, "tiny_patch": tiny_patch, "periodic": periodic,
     "big_motion": big_motion, "out_of_window": out_of_window,
 }
+
+
+# ---------------------------------------------------------------------------------------------
+# match lists for the removeOutliers (Delaunay support filter) parity tests, SURVEY.md row A17.
+# Integer-lattice current-frame points (as the matcher emits), unique per list, with a smooth flow
+# field plus a fraction of gross outliers.  Pure integer numpy, deterministic.
+# ---------------------------------------------------------------------------------------------
+def _match_list(dtype, uc, vc, du, dv):
+    m = np.zeros(len(uc), dtype)
+    for k in m.dtype.names:
+        m[k] = -1
+    m["u1c"], m["v1c"] = uc, vc
+    m["u1p"], m["v1p"] = uc - du, vc - dv
+    return m
+
+
+def _lattice_points(rng, n, w, h, step=1):
+    cells = rng.permutation((w // step) * (h // step))[:n]
+    cells.sort()  # the matcher emits in a spatial order; keep lists ordered but irregular
+    return (cells % (w // step)) * step + 9, (cells // (w // step)) * step + 9
+
+
+def outlier_lists(dtype, seed=0):
+    """name -> p_match array.  Sizes stay below the reference's POINT_L = 14002."""
+    rng = np.random.default_rng(1000 + seed)
+    out = {}
+
+    def add(name, uc, vc, frac=0.1, spread=12):
+        n = len(uc)
+        du = -3 + (uc // 200) + rng.integers(-1, 2, n)      # smooth flow + 1 px jitter
+        dv = -1 + (vc // 150) + rng.integers(-1, 2, n)
+        bad = rng.permutation(n)[: int(n * frac)]
+        du[bad] += rng.integers(-spread, spread + 1, len(bad))
+        dv[bad] += rng.integers(-spread, spread + 1, len(bad))
+        out[name] = _match_list(dtype, uc, vc, du, dv)
+
+    add("three", *_lattice_points(rng, 3, 100, 80))                       # <= 3: returned unchanged
+    add("four", *_lattice_points(rng, 4, 100, 80))
+    add("small", *_lattice_points(rng, 60, 100, 80))
+    add("mid", *_lattice_points(rng, 2500, 500, 150))
+    add("kitti_10k", *_lattice_points(rng, 10000, 1220, 356))
+    add("near_cap", *_lattice_points(rng, 13500, 1220, 356), frac=0.2)  # 3*(2n-5) stays below TRIANGLE_L = 83598
+    add("coarse_lattice", *_lattice_points(rng, 5000, 1220, 356, step=3))  # 3-px lattice: many co-circular quadruples
+    gu, gv = np.meshgrid(np.arange(60) * 3 + 9, np.arange(40) * 3 + 9)     # full regular grid: every quad is co-circular
+    add("regular_grid", gu.ravel(), gv.ravel(), frac=0.15)
+    cu = np.concatenate([rng.integers(0, 80, 700) + c for c in (50, 500, 1000)])
+    cv = np.concatenate([rng.integers(0, 60, 700) + c for c in (30, 200, 120)])
+    key = np.unique(cv * 4096 + cu)                                         # unique pixels, raster order
+    add("clustered", key % 4096, key // 4096, frac=0.3, spread=30)
+    add("all_outliers", *_lattice_points(rng, 800, 400, 300), frac=1.0, spread=40)
+    return out

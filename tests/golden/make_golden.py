@@ -63,7 +63,7 @@ def pair_record(ref: RefLib, prev, curr, with_post=False):
 
 def main():
     out = {"about": "sha256 digests of outputs of the reference sources compiled in place (oracle/_ref)",
-           "geometries": {}, "lfsr": {}, "filters": {}, "matcher_flow": {}}
+           "geometries": {}, "lfsr": {}, "filters": {}, "matcher_flow": {}, "outliers": {}}
     for tag in ["native", "1024x284", "500x150", "1241x376", "2048x1024"]:
         ref = RefLib(tag)
         g = {"W": ref.W, "H": ref.H, "U": ref.U, "V": ref.V, "cases": {}}
@@ -107,6 +107,16 @@ def main():
                      "n_bucketed": int(len(b)), "bucketed": matches_digest(b)})
     m.close()
     out["matcher_flow"] = {"geometry": "native", "seed": 0, "frames": flow}
+
+    # removeOutliers on explicit match lists with real outliers (tests/cases.py outlier_lists)
+    from oracle.ref_lib import P_MATCH_DTYPE
+    out["outliers"] = {}
+    for seed in (0, 1):
+        for name, lst in cases.outlier_lists(P_MATCH_DTYPE, seed).items():
+            post = ref.remove_outliers(lst)
+            out["outliers"][f"{name}_seed{seed}"] = {"n_in": int(len(lst)), "n_out": int(len(post)),
+                                                     "in": matches_digest(lst), "out": matches_digest(post)}
+    print("outliers done", flush=True)
 
     with open(os.path.join(HERE, "golden.json"), "w") as f:
         json.dump(out, f, indent=1, sort_keys=True)

@@ -192,3 +192,43 @@ def test_cpp_shim_demo(tmp_path):
         want.append(len(orc.bucket_features(raw, 2, 50.0, 50.0)))
     assert counts == want
     assert "mean flow: -3 -1" in out.stdout
+
+
+def test_matcher_facade_matches_reference_golden():
+    """pushBack -> matchFeatures (GPU matching + host removeOutliers) -> bucketFeatures -> getMatches over 4
+    frames, against digests the reference's own Matcher produced (golden 'matcher_flow')."""
+    flow = GOLD["matcher_flow"]
+    assert flow["geometry"] == "native"
+    W, H = 1024, 284
+    seq = make_sequence(W, H, 4, seed=flow["seed"])
+    m = api.Matcher(W, H)
+    try:
+        for f, rec in enumerate(flow["frames"]):
+            m.pushBack(seq[f], [W, H, W])
+            m.matchFeatures(0)
+            after = m.getMatches()
+            assert len(after) == rec["n_after_outliers"], f"frame {f}"
+            assert matches_digest(after) == rec["after_outliers"], f"frame {f}"
+            m.bucketFeatures(2, 50.0, 50.0)
+            b = m.getMatches()
+            assert len(b) == rec["n_bucketed"] and matches_digest(b) == rec["bucketed"], f"frame {f} bucketed"
+    finally:
+        m.engine.close()
+
+
+def test_engine_remove_outliers_with_real_outliers():
+    """vo_set_matches -> vo_remove_outliers -> vo_bucket_features on a list with gross outliers, against
+    the reference-made golden of the host stage and the oracle's bucketing of that result"""
+    lst = cases.outlier_lists(api.P_MATCH_DTYPE, 0)["kitti_10k"]
+    rec = GOLD["outliers"]["kitti_10k_seed0"]
+    eng = Engine(1241, 376)
+    try:
+        eng.set_matches(lst)
+        eng.remove_outliers()
+        kept = eng.get_matches()
+        assert len(kept) == rec["n_out"] and matches_digest(kept) == rec["out"]
+        eng.bucket_features(2, 50.0, 50.0)
+        want = Oracle(1241, 376).bucket_features(kept, 2, 50.0, 50.0)
+        assert_matches_equal(eng.get_matches(), want, "bucketed after removeOutliers")
+    finally:
+        eng.close()
