@@ -357,10 +357,16 @@ def run_ours(args):
     k2_avg_s = k2_ms / max(k2_calls, 1) / 1e3
     achieved = b_match * B / k2_avg_s / 1e9 if k2_avg_s > 0 else 0.0
     step_ms = dev_ms / args.steps
+    traffic = None                                        # measured DRAM bytes per K2 launch (ncu --set full capture)
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k2_match"]
+        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["pairs_per_launch"] * B
+    except Exception:
+        pass
     fam = {k: (v[0] / max(v[1], 1)) for k, v in prof.items()}
     roofline = {
         "kernel": "k2_match", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": b_match * B, "avg_launch_ms": k2_avg_s * 1e3,
         "share_of_step": (k2_avg_s * 1e3) / step_ms if step_ms else None,
         "kernel_ms_per_step": fam,

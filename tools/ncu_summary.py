@@ -4,6 +4,7 @@
   python tools/ncu_summary.py launches gpurun_out/launches.csv > profiles/rN_launches.txt
   python tools/ncu_summary.py kernel   gpurun_out/k2_full.ncu-rep > profiles/rN_k2_full.txt
   python tools/ncu_summary.py sass     gpurun_out/k2_full.ncu-rep [min_share] > hot SASS lines
+  python tools/ncu_summary.py lines    gpurun_out/k2_full.ncu-rep [min_share] > executed instructions per CUDA source line
 """
 import collections
 import csv
@@ -88,9 +89,29 @@ def sass(path, min_share=0.002):
             print(f"{o[0]} {o[2] / 1e6:8.2f}M s={o[3]:5d} thr={o[4]:>3s} {o[1]}")
 
 
+def lines(path, min_share=0.004):
+    """Executed warp instructions and stall samples aggregated per CUDA source line (needs -lineinfo + --import-source on)."""
+    raw = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr = next(r for r in rows if r and r[0] == "Line No")
+    ii, si = hdr.index("Instructions Executed"), hdr.index("# Samples")
+    out = []
+    for r in rows:
+        if r and r[0].isdigit():
+            try:
+                out.append((int(r[0]), int(r[ii]), int(r[si]), r[1].strip()))
+            except (ValueError, IndexError):
+                pass
+    tot, ts = sum(o[1] for o in out) or 1, sum(o[2] for o in out) or 1
+    print(f"# {path}: {tot} warp instructions with line info; lines with >= {min_share:.2%} of instructions or samples (line, Minst, share, stall-sample share)")
+    for ln, n, smp, src in sorted(out):
+        if n >= tot * min_share or smp >= ts * min_share:
+            print(f"L{ln:4d} {n / 1e6:8.1f}M {n / tot:6.1%} samp {smp / ts:6.1%}  {src[:110]}")
+
+
 if __name__ == "__main__":
-    fn = {"launches": launches, "kernel": kernel, "sass": sass}[sys.argv[1]]
-    if sys.argv[1] == "sass" and len(sys.argv) > 3:
+    fn = {"launches": launches, "kernel": kernel, "sass": sass, "lines": lines}[sys.argv[1]]
+    if sys.argv[1] in ("sass", "lines") and len(sys.argv) > 3:
         fn(sys.argv[2], float(sys.argv[3]))
     else:
         fn(sys.argv[2])
