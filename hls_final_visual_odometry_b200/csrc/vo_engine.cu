@@ -367,7 +367,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   ALLOC(e->fa.xy, sizeof(uint32_t) * S * e->fa.rec_stride);
   ALLOC(e->fa.meta, sizeof(uint32_t) * S * e->fa.rec_stride);
   ALLOC(e->fa.desc, sizeof(uint4) * 2 * S * e->fa.rec_stride);
-  ALLOC(e->fa.q, sizeof(uint2) * S * e->fa.rec_stride);
+  ALLOC(e->fa.q, sizeof(uint32_t) * S * e->fa.rec_stride);
   cudaMemsetAsync(e->fa.cnt, 0, sizeof(int32_t) * S * e->fa.cnt_stride, e->stream);
   cudaMemsetAsync(e->fa.img, 0, (size_t)(S * e->fa.img_stride + 256), e->stream);
   const int64_t lists = (int64_t)g.U * 4 * g.col_cap;

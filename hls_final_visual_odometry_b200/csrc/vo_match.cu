@@ -23,8 +23,15 @@
 // K3 (k3_flags, k3_emit): closed-cycle test, same-pixel dedupe (lowest class wins, via the twin
 // links written by K1), ordered emit of p_match records in (u_bin, class, col_idx) order.
 #include "vo_common.cuh"
+#include <cstdio>
 
 namespace vo {
+#ifdef VO_K2_STATS
+__device__ unsigned long long g_k2_stats[8];
+#define K2STAT(i, n) atomicAdd(&g_k2_stats[i], (unsigned long long)(n))
+#else
+#define K2STAT(i, n)
+#endif
 
 constexpr int kMaxV = 64;       // v-bin rows supported by the shared-memory tables
 constexpr int kOC = 2;          // origin u-bin columns per CTA (they share the staged window)
@@ -34,6 +41,9 @@ constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a ro
 constexpr int kMaxWarps = 16;
 constexpr int kQueue = 64;      // deferred exact evaluations per warp
 constexpr int kBig = 1 << 20;
+static_assert(kCandCap <= 2048, "k2 hard pass packs the staged position into 11 bits");
+constexpr int kHardCap = 2048;  // origins per chunk handed to the warp-per-origin pass
+constexpr int kHitBudget = 4;   // filter hits (groups of 4) a lane may queue before its origin is handed over
 
 struct K2Tables {
   int32_t cntT[kMaxV][kSegW];         // target counts (row, staged column)
@@ -50,10 +60,12 @@ struct __align__(128) K2Smem {
   K2Tables t;
   uint32_t sbest[kMaxWarps][32];      // running best key of the 32 origins of a warp's task
   uint32_t queue[kMaxWarps][kQueue + 32];  // deferred exact evaluations: owner lane << 16 | candidate group (+32 dump slots)
+  int32_t hard_n;                     // origins handed to the warp-per-origin pass in this chunk
+  uint16_t hard[kHardCap];            // origin column (bit 15) | col_idx
   __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
   uint4 hi[kCandCap];                 // descriptor bytes 16..31
   uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
-  __align__(16) uint2 q[kCandCap];    // 8 quantised group sums (lower-bound filter); read two at a time
+  __align__(16) uint32_t q[kCandCap]; // 4 coded group sums (lower-bound filter); read four at a time
 };
 
 // acc + sum of |a_i - b_i| over the four packed bytes: one VABSDIFF4.U8.ACC
@@ -74,9 +86,7 @@ __device__ __forceinline__ uint32_t sad32(const uint4& a, const uint4& b, const 
   return sad4(b.w, y.w, s);
 }
 
-__device__ __forceinline__ int sadq(const uint2& a, uint32_t x, uint32_t y) {
-  return (int)sad4(a.y, y, sad4(a.x, x, 0u));
-}
+__device__ __forceinline__ int sadq(uint32_t a, uint32_t x) { return (int)sad4(a, x, 0u); }
 
 // key of one staged candidate for an origin (a, b, window lo_p/hi_p), kNone if outside the window.
 // packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
@@ -174,14 +184,13 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 
   const uint32_t* xy_from = fa.xy + (int64_t)from_slot * fa.rec_stride;
   const uint4* desc_from = fa.desc + (int64_t)from_slot * fa.rec_stride * 2;
-  const uint2* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
+  const uint32_t* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
   const uint32_t* xy_to = fa.xy + (int64_t)to_slot * fa.rec_stride;
   const uint4* desc_to = fa.desc + (int64_t)to_slot * fa.rec_stride * 2;
-  const uint2* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
+  const uint32_t* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
   const uint4* Q4 = reinterpret_cast<const uint4*>(S.q);
   uint32_t* sbest = S.sbest[warp];
   uint32_t* queue = S.queue[warp];
-  uint32_t* qdump = queue + kQueue + lane;
   const uint32_t lt_mask = (1u << lane) - 1u, lane16 = (uint32_t)lane << 16;
 
   bool first_chunk = true;
@@ -190,6 +199,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     int rb = ra, staged = 0;
     while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
     __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
+    if (tid == THREADS - 1) S.hard_n = 0;
     if (tid <= rb - ra) {
       const int v = ra + tid;
       int acc = 0;
@@ -220,7 +230,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           S.lo[dst + k] = make_uint4(0, 0, 0, 0);
           S.hi[dst + k] = make_uint4(0, 0, 0, 0);
           S.xr[dst + k] = make_uint2(kNone, kNone);
-          S.q[dst + k] = make_uint2(kNone, kNone);
+          S.q[dst + k] = kNone;
         }
       }
     }
@@ -240,7 +250,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       int v = r0, vlo = kBig, vhi = 0;
       uint32_t oxy = 0;
       uint4 a = make_uint4(0, 0, 0, 0), b = a;
-      uint2 qa = make_uint2(0, 0);
+      uint32_t qa = 0;
       uint32_t bestk = kNone;
       if (valid) {
         while (t.prefO[cc][v + 1] <= o) v++;
@@ -271,11 +281,13 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         uint32_t k1 = kNone;
         for (int r = smin; r <= smax; r++) {
           const int p1 = t.segOff[r][jown + 1];
-          for (int p = t.segOff[r][jown]; p < p1; p += 2) {
-            const uint4 qq = Q4[p >> 1];
-            const uint32_t ka = (uint32_t)sadq(qa, qq.x, qq.y) * 0x100000u + (uint32_t)p;
-            const uint32_t kb = (uint32_t)sadq(qa, qq.z, qq.w) * 0x100000u + (uint32_t)(p + 1);
-            k1 = min(k1, min(ka, kb));
+          for (int p = t.segOff[r][jown]; p < p1; p += 4) {  // bin lists are padded to 4
+            const uint4 qq = Q4[p >> 2];
+            const uint32_t ka = (uint32_t)sadq(qa, qq.x) * 0x100000u + (uint32_t)p;
+            const uint32_t kb = (uint32_t)sadq(qa, qq.y) * 0x100000u + (uint32_t)(p + 1);
+            const uint32_t kc = (uint32_t)sadq(qa, qq.z) * 0x100000u + (uint32_t)(p + 2);
+            const uint32_t kd = (uint32_t)sadq(qa, qq.w) * 0x100000u + (uint32_t)(p + 3);
+            k1 = min(k1, min(min(ka, kb), min(kc, kd)));
           }
         }
         if (k1 != kNone && vlo < vhi) {
@@ -285,9 +297,28 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       }
       sbest[lane] = bestk;
       __syncwarp();
-      // tq: a candidate can still win (or tie) only if its lower bound 4Q-24 <= best SAD so far
-      int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(((bestk >> 19) + 24u) >> 2);
+      // tq: a candidate can still win (or tie) only if its lower bound Q <= best SAD so far
+      int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
       int qn = 0;  // queued groups (warp-uniform)
+      int hits = 0;
+      // An origin the filter cannot prune (no near-exact match: every candidate may still win) would
+      // flood the queue; it leaves the lane-per-origin walk and is matched by a whole warp after the
+      // tasks of this chunk (k2_hard_origins).  Its partial best stays valid and is merged there.
+      auto hand_over = [&]() {
+        const int hs = atomicAdd(&S.hard_n, 1);
+        hits = -kBig;  // once per task (if the list is full the origin stays on the queue path)
+        if (hs < kHardCap) {
+          S.hard[hs] = (uint16_t)((cc << 15) | o);
+          vlo = kBig; vhi = 0;
+          return true;
+        }
+        return false;
+      };
+      K2STAT(0, valid ? 1 : 0);
+      K2STAT(1, (valid && vlo < vhi) ? 1 : 0);
+      K2STAT(2, (valid && vlo < vhi && bestk == kNone) ? 1 : 0);
+      K2STAT(3, (valid && vlo < vhi && bestk != kNone && (bestk >> 19) == 0) ? 1 : 0);
+      if (PRUNE && vlo < vhi && bestk == kNone) hand_over();  // no seed: every group would hit
 
       // exact SAD + window test of up to 32 queued (origin, group of 4 candidates) entries, one per
       // lane; the origin's record comes from its owner lane by shuffle, the result goes back
@@ -313,58 +344,118 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         }
         __syncwarp();
         bestk = sbest[lane];
-        tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(((bestk >> 19) + 24u) >> 2);
+        tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
       };
 
       for (int r = rlo; r < rhi; r++) {
-        const bool act = (r >= vlo) && (r < vhi);
+        bool act = (r >= vlo) && (r < vhi);
         int tqe = act ? tq : -1;  // tq while this lane searches the current row, else -1 (never passes)
         int pg = t.segOff[r][j0] >> 2;            // candidate groups of 4 (every bin list is padded to 4)
         const int pg1 = t.segOff[r][j1] >> 2;
-        const uint4* qp = Q4 + 2 * pg;
-        // queue the groups of this lane that may still hold a winner (warp-uniform control flow)
-        auto enqueue = [&](bool hit, int grp4) {
-          const uint32_t bal = __ballot_sync(FULL, hit);
-          uint32_t* dst = hit ? queue + qn + __popc(bal & lt_mask) : qdump;  // branch-free: misses hit a dump slot
-          *dst = lane16 | (uint32_t)grp4;
-          qn += __popc(bal);
-          if (qn >= 32) {
-            __syncwarp();
-            flush();
-            tqe = act ? tq : -1;
-          }
-        };
-        if (PRUNE) {
-          // two groups (8 candidates) per vote: independent loads and SAD chains in flight
+        // Chunks of up to 32 groups: every lane first collects a private bit mask of the groups that may
+        // still hold a winner (no votes, no branches in the filter loop), then the warp compacts the set
+        // bits into the exact-evaluation queue, one entry per lane and round.
+        while (pg < pg1) {
+          const int nb = min(32, pg1 - pg);
+          uint32_t m = 0;  // MISS bits while filtering, newest group in bit 0
+          if (PRUNE) {
+            const uint4* qp = Q4 + pg;  // one uint4 = the signatures of one group of 4 candidates
+            int i = 0;
 #pragma unroll 2
-          for (; pg + 1 < pg1; pg += 2, qp += 4) {
-            const uint4 qx = qp[0], qy = qp[1], qz = qp[2], qw = qp[3];
-            const int Q0 = sadq(qa, qx.x, qx.y), Q1 = sadq(qa, qx.z, qx.w);
-            const int Q2 = sadq(qa, qy.x, qy.y), Q3 = sadq(qa, qy.z, qy.w);
-            const int Q4_ = sadq(qa, qz.x, qz.y), Q5 = sadq(qa, qz.z, qz.w);
-            const int Q6 = sadq(qa, qw.x, qw.y), Q7 = sadq(qa, qw.z, qw.w);
-            const int ma = min(min(Q0, Q1), min(Q2, Q3)), mb = min(min(Q4_, Q5), min(Q6, Q7));
-            if (__any_sync(FULL, min(ma, mb) <= tqe)) {
-              enqueue(ma <= tqe, pg);
-              enqueue(mb <= tqe, pg + 1);
+            for (; i + 3 < nb; i += 4, qp += 4) {
+              const uint4 qx = qp[0], qy = qp[1], qz = qp[2], qw = qp[3];
+              const int ma = min(min(sadq(qa, qx.x), sadq(qa, qx.y)), min(sadq(qa, qx.z), sadq(qa, qx.w)));
+              const int mb = min(min(sadq(qa, qy.x), sadq(qa, qy.y)), min(sadq(qa, qy.z), sadq(qa, qy.w)));
+              const int mc = min(min(sadq(qa, qz.x), sadq(qa, qz.y)), min(sadq(qa, qz.z), sadq(qa, qz.w)));
+              const int md = min(min(sadq(qa, qw.x), sadq(qa, qw.y)), min(sadq(qa, qw.z), sadq(qa, qw.w)));
+              m = __funnelshift_l((uint32_t)(tqe - ma), m, 1);  // shifts in the sign: 1 = lower bound above the threshold
+              m = __funnelshift_l((uint32_t)(tqe - mb), m, 1);
+              m = __funnelshift_l((uint32_t)(tqe - mc), m, 1);
+              m = __funnelshift_l((uint32_t)(tqe - md), m, 1);
+            }
+            for (; i < nb; i++, qp++) {
+              const uint4 qx = qp[0];
+              const int ma = min(min(sadq(qa, qx.x), sadq(qa, qx.y)), min(sadq(qa, qx.z), sadq(qa, qx.w)));
+              m = __funnelshift_l((uint32_t)(tqe - ma), m, 1);
+            }
+            m = ~m;
+          } else {
+            m = act ? kNone : 0u;
+          }
+          m &= kNone >> (32 - nb);  // bit b <-> group pg + nb-1-b
+          if (PRUNE) {
+            hits += __popc(m);
+            K2STAT(4, __popc(m));
+            if (hits > kHitBudget) { K2STAT(6, tq == 0 ? 1 : 0); K2STAT(7, hits); }
+            if (hits > kHitBudget && hand_over()) { m = 0u; act = false; tqe = -1; K2STAT(5, 1); }
+          }
+          const uint32_t gfirst = lane16 + (uint32_t)(pg + nb - 32);  // owner lane << 16 + group of bit 31 (mod 2^32)
+          for (;;) {
+            const uint32_t bal = __ballot_sync(FULL, m != 0u);
+            if (bal == 0u) break;
+            const int z = __clz((int)m);  // 32 when this lane has nothing left
+            const int slot = (m != 0u) ? qn + __popc(bal & lt_mask) : kQueue + lane;  // branch-free: idle lanes hit a dump slot
+            queue[slot] = gfirst + (uint32_t)z;
+            m &= ~__funnelshift_rc(0x80000000u, 0u, z);  // clears the bit; shift 32 -> 0
+            qn += __popc(bal);
+            if (qn >= 32) {
+              __syncwarp();
+              flush();
+              tqe = act ? tq : -1;
             }
           }
-          if (pg < pg1) {
-            const uint4 qx = qp[0], qy = qp[1];
-            const int Q0 = sadq(qa, qx.x, qx.y), Q1 = sadq(qa, qx.z, qx.w);
-            const int Q2 = sadq(qa, qy.x, qy.y), Q3 = sadq(qa, qy.z, qy.w);
-            const bool hit = min(min(Q0, Q1), min(Q2, Q3)) <= tqe;
-            if (__any_sync(FULL, hit)) enqueue(hit, pg);
-          }
-        } else {
-          for (; pg < pg1; pg++)
-            if (__any_sync(FULL, act)) enqueue(act, pg);
+          pg += nb;
         }
       }
       __syncwarp();
       while (qn > 0) flush();
       if (valid) bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
       __syncwarp();  // sbest/queue are reused by this warp's next task
+    }
+    if (PRUNE) {
+      // ---- handed-over origins: one warp per origin, lanes stride its candidates.  Pass 1 takes the
+      //      candidate of smallest lower bound per lane and evaluates it exactly -> bound T; pass 2
+      //      evaluates exactly every candidate whose lower bound is <= T (all that can win or tie). ----
+      __syncthreads();
+      const int nh = min(S.hard_n, kHardCap);
+      for (int h = warp; h < nh; h += NW) {
+        const uint32_t e = S.hard[h];
+        const int cc = (int)(e >> 15), o = (int)(e & 0x7FFFu);
+        const int ub = ub0 + cc;
+        const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo;
+        uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
+        int v = r0;
+        while (t.prefO[cc][v + 1] <= o) v++;
+        const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
+        const uint32_t oxy = __ldg(&xy_from[rec]);
+        const uint4 a = __ldg(&desc_from[2 * rec]), b = __ldg(&desc_from[2 * rec + 1]);
+        const uint32_t qa = __ldg(&q_from[rec]);
+        const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
+        const int lo_r = max(max(vb - 3, 0), ra), hi_r = min(min(vb + 3, V - 1), rb);
+        const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
+        const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);
+        const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
+        uint32_t k1 = kNone;
+        for (int r = lo_r; r < hi_r; r++) {
+          const int p1 = t.segOff[r][j1];
+          for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) k1 = min(k1, ((uint32_t)sadq(qa, S.q[p]) << 11) | (uint32_t)p);
+        }
+        uint32_t bk = (k1 != kNone) ? cand_key(S, (int)(k1 & 2047u), a, b, lo_p, hi_p) : kNone;
+        const uint32_t prev = bo[o];  // the lane path's partial result (and earlier chunks)
+        if (prev != kNone) bk = min(bk, prev + ((uint32_t)j0 << 16));
+        int tl = (int)(__reduce_min_sync(FULL, bk) >> 19);  // kNone >> 19 = 8191 > any SAD
+        for (int r = lo_r; r < hi_r; r++) {
+          const int p1 = t.segOff[r][j1];
+          for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) {
+            if (sadq(qa, S.q[p]) <= tl) {
+              bk = min(bk, cand_key(S, p, a, b, lo_p, hi_p));
+              tl = min(tl, (int)(bk >> 19));
+            }
+          }
+        }
+        bk = __reduce_min_sync(FULL, bk);
+        if (lane == 0) bo[o] = (bk == kNone) ? kNone : bk - ((uint32_t)j0 << 16);
+      }
     }
     first_chunk = false;
     ra = rb;
@@ -593,3 +684,12 @@ cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, i
 }
 
 }  // namespace vo
+#ifdef VO_K2_STATS
+extern "C" int vo_debug_k2_stats(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  cudaError_t e = cudaMemcpyFromSymbol(out, vo::g_k2_stats, sizeof(unsigned long long) * 8);
+  unsigned long long z[8] = {0};
+  cudaMemcpyToSymbol(vo::g_k2_stats, z, sizeof(z));
+  return (int)e;
+}
+#endif
