@@ -301,15 +301,17 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
       int qn = 0;  // queued groups (warp-uniform)
       int hits = 0;
+      bool handed = false;
       // An origin the filter cannot prune (no near-exact match: every candidate may still win) would
       // flood the queue; it leaves the lane-per-origin walk and is matched by a whole warp after the
-      // tasks of this chunk (k2_hard_origins).  Its partial best stays valid and is merged there.
+      // tasks of this chunk (k2_hard_origins).  It is matched from scratch there.
       auto hand_over = [&]() {
         const int hs = atomicAdd(&S.hard_n, 1);
         hits = -kBig;  // once per task (if the list is full the origin stays on the queue path)
         if (hs < kHardCap) {
           S.hard[hs] = (uint16_t)((cc << 15) | o);
           vlo = kBig; vhi = 0;
+          handed = true;
           return true;
         }
         return false;
@@ -409,13 +411,11 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       }
       __syncwarp();
       while (qn > 0) flush();
-      if (valid) bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
+      if (valid && !handed) bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
       __syncwarp();  // sbest/queue are reused by this warp's next task
     }
     if (PRUNE) {
-      // ---- handed-over origins: one warp per origin, lanes stride its candidates.  Pass 1 takes the
-      //      candidate of smallest lower bound per lane and evaluates it exactly -> bound T; pass 2
-      //      evaluates exactly every candidate whose lower bound is <= T (all that can win or tie). ----
+      // ---- handed-over origins: one warp per origin, lanes stride its candidates ----------------------
       __syncthreads();
       const int nh = min(S.hard_n, kHardCap);
       for (int h = warp; h < nh; h += NW) {
@@ -435,23 +435,27 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
         const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);
         const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
-        uint32_t k1 = kNone;
-        for (int r = lo_r; r < hi_r; r++) {
-          const int p1 = t.segOff[r][j1];
-          for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) k1 = min(k1, ((uint32_t)sadq(qa, S.q[p]) << 11) | (uint32_t)p);
+        uint32_t bk = kNone;
+        if (!first_chunk) {  // result of the earlier chunks
+          const uint32_t prev = bo[o];
+          if (prev != kNone) bk = prev + ((uint32_t)j0 << 16);
         }
-        uint32_t bk = (k1 != kNone) ? cand_key(S, (int)(k1 & 2047u), a, b, lo_p, hi_p) : kNone;
-        const uint32_t prev = bo[o];  // the lane path's partial result (and earlier chunks)
-        if (prev != kNone) bk = min(bk, prev + ((uint32_t)j0 << 16));
-        int tl = (int)(__reduce_min_sync(FULL, bk) >> 19);  // kNone >> 19 = 8191 > any SAD
-        for (int r = lo_r; r < hi_r; r++) {
+        int tl = (int)(bk >> 19);  // kNone >> 19 = 8191 > any SAD
+        // one pass, the origin's own row first (zero-flow prior): a candidate is evaluated exactly iff its
+        // lower bound is <= the best SAD known to this lane; the bound is shared warp-wide after every row
+        const bool own = (v >= lo_r) && (v < hi_r);
+        for (int rr = own ? lo_r - 1 : lo_r; rr < hi_r; rr++) {
+          const int r = (rr < lo_r) ? v : rr;
+          if (own && rr == v) continue;
           const int p1 = t.segOff[r][j1];
+#pragma unroll 2
           for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) {
             if (sadq(qa, S.q[p]) <= tl) {
               bk = min(bk, cand_key(S, p, a, b, lo_p, hi_p));
               tl = min(tl, (int)(bk >> 19));
             }
           }
+          tl = __reduce_min_sync(FULL, tl);
         }
         bk = __reduce_min_sync(FULL, bk);
         if (lane == 0) bo[o] = (bk == kNone) ? kNone : bk - ((uint32_t)j0 << 16);
