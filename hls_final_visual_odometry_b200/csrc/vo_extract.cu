@@ -19,7 +19,6 @@ constexpr int BW = 60, BH = 45;          // bin size this kernel is specialised 
 constexpr int TW = 96, TH = 59;          // TMA box: 74x59 needed; the box must START on a 16-byte boundary in x
                                          // (u8 elements: measured, unaligned inner coordinates fault), so up to 15
                                          // lead-in bytes + 74 -> 96
-constexpr int PW = 72;                   // row stride of the horizontal-pass planes
 constexpr int OW = 70, OH = 55;          // du/dv/f1/f2 region: tile cols 2..71, rows 2..56
 constexpr int NBX = BW / 3, NBY = BH / 3;  // 20 x 15 NMS blocks per tile
 constexpr int K1_THREADS = 320;
@@ -28,25 +27,33 @@ constexpr int K1_WARPS = K1_THREADS / 32;
 struct __align__(128) K1Smem {
   uint8_t img[TH * TW];
   unsigned long long bar;
-  int16_t hd[TH * PW];    // horizontal [1 2 0 -2 -1]
-  int16_t hg[TH * PW];    // horizontal [1 4 6 4 1]
-  int16_t hc[TH * PW];    // horizontal [-1 -1 0 1 1]
-  int16_t hs5[TH * PW];   // horizontal box-5 sum
-  int16_t ht[TH * PW];    // 2*box3 - box5
   uint16_t duv[OH * OW];  // du | dv<<8
-  int16_t f1[OH * OW];
-  int16_t f2[OH * OW];
+  uint16_t f1[OH * OW];   // blob response + kFBias
+  uint16_t f2[OH * OW];   // checkerboard response + kFBias
   int32_t warp_tot[K1_WARPS][4];
 };
+
+// Filter phase work split: a thread owns two adjacent output columns (packed into the two 16-bit
+// halves of a register) and slides down a strip of kStripRows output rows.
+constexpr int kColPairs = OW / 2;                        // 35
+constexpr int kStripRows = 7;
+constexpr int kStrips = (OH + kStripRows - 1) / kStripRows;  // 8
+constexpr uint32_t kHBias = 0x04000400u;                 // +1024 per half: keeps signed horizontal sums non-negative
+constexpr uint32_t kFBias = 4096;                        // f1/f2 are stored as value + 4096 (range [16, 8176])
+static_assert(kColPairs * kStrips <= K1_THREADS, "filter phase needs one thread per (column pair, strip)");
+static_assert(OW % 2 == 0, "column pairs");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-__device__ __forceinline__ int sobel_u8(int acc) {
-  // C division by 128 truncating toward zero, +128, clamp (src/myComputeFeature.cpp:84-106)
-  int q = ((acc + ((acc >> 31) & 127)) >> 7) + 128;
-  return min(max(q, 0), 255);
+// Two Sobel sums at once.  x holds acc + 16384 in each 16-bit half (|acc| <= 12240, so every half is in
+// [4144, 28624]).  The reference computes acc /= 128 with C truncation toward zero, then + 128 and a clamp
+// that can never fire (src/myComputeFeature.cpp:84-106):  trunc(acc/128) + 128 = floor((acc + 16384 +
+// (acc < 0 ? 127 : 0)) / 128), and acc < 0  <=>  bit 14 of the biased half is clear.
+__device__ __forceinline__ uint32_t sobel_u8x2(uint32_t x) {
+  const uint32_t neg = (~x >> 14) & 0x00010001u;
+  return ((x + neg * 127u) >> 7) & 0x01FF01FFu;
 }
 
 __global__ void __launch_bounds__(K1_THREADS)
@@ -88,33 +95,45 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
     }
   }
 
-  // ---- horizontal 5-tap pass: tile columns 2..71 of all 59 rows ---------------------------
-  for (int idx = tid; idx < TH * OW; idx += K1_THREADS) {
-    const int ty = idx / OW, px = idx - ty * OW;
-    const uint8_t* p = &s.img[ty * TW + xoff + px];
-    const int p0 = p[0], p1 = p[1], p2 = p[2], p3 = p[3], p4 = p[4];
-    const int o = ty * PW + px;
-    const int s3 = p1 + p2 + p3, s5 = s3 + p0 + p4;
-    s.hd[o] = (int16_t)(p0 + 2 * p1 - 2 * p3 - p4);
-    s.hg[o] = (int16_t)(p0 + p4 + 4 * (p1 + p3) + 6 * p2);
-    s.hc[o] = (int16_t)(p3 + p4 - p0 - p1);
-    s.hs5[o] = (int16_t)s5;
-    s.ht[o] = (int16_t)(2 * s3 - s5);
-  }
-  __syncthreads();
-
-  // ---- vertical pass -> du,dv (u8), f1 (blob), f2 (checkerboard) ---------------------------
-  for (int idx = tid; idx < OH * OW; idx += K1_THREADS) {
-    const int oy = idx / OW, ox = idx - oy * OW;
-    const int c0 = (oy + 2) * PW + ox;  // centre row in the planes
-    const int du_acc = s.hd[c0 - 2 * PW] + s.hd[c0 + 2 * PW] + 4 * (s.hd[c0 - PW] + s.hd[c0 + PW]) + 6 * s.hd[c0];
-    const int dv_acc = s.hg[c0 - 2 * PW] + 2 * s.hg[c0 - PW] - 2 * s.hg[c0 + PW] - s.hg[c0 + 2 * PW];
-    const int f2v = s.hc[c0 - 2 * PW] + s.hc[c0 - PW] - s.hc[c0 + PW] - s.hc[c0 + 2 * PW];
-    const int f1v = s.ht[c0 - PW] + s.ht[c0] + s.ht[c0 + PW] - s.hs5[c0 - 2 * PW] - s.hs5[c0 + 2 * PW] +
-                    7 * (int)s.img[(oy + 2) * TW + xoff + ox + 2];
-    s.duv[idx] = (uint16_t)(sobel_u8(du_acc) | (sobel_u8(dv_acc) << 8));
-    s.f1[idx] = (int16_t)f1v;
-    s.f2[idx] = (int16_t)f2v;
+  // ---- filters: du/dv (Sobel), f1 (blob), f2 (checkerboard) for tile columns 2..71, rows 2..56 ---------
+  // Separable, sliding down the strip with the last five horizontal rows in registers; all sums are the
+  // same integers as the reference's dense 5x5 correlations (src/myComputeFeature.cpp:58-151), two
+  // columns per 32-bit operation.  Halves never borrow from each other because every packed value is
+  // biased to be non-negative (kHBias on the horizontal sums, 16384 / kFBias on the vertical ones).
+  if (tid < kColPairs * kStrips) {
+    const int k = tid % kColPairs, strip = tid / kColPairs;
+    const uint8_t* col = &s.img[xoff + 2 * k];  // image column of output column 2k, minus 2
+    uint32_t HD[5], HG[5], HC[5], HS[5], HT[5], PC[5];
+#pragma unroll
+    for (int i = 0; i < kStripRows + 4; i++) {
+      const int ty = min(strip * kStripRows + i, TH - 1);  // the clamped row only feeds outputs that are not stored
+      const uint8_t* p = col + ty * TW;
+      const uint32_t b0 = p[0], b1 = p[1], b2 = p[2], b3 = p[3], b4 = p[4], b5 = p[5];
+      const uint32_t P0 = b0 | (b1 << 16), P1 = b1 | (b2 << 16), P2 = b2 | (b3 << 16), P3 = b3 | (b4 << 16), P4 = b4 | (b5 << 16);
+      const int w = i % 5;
+      const uint32_t S3 = P1 + P2 + P3, S5 = S3 + P0 + P4;
+      HD[w] = P0 + 2u * P1 + kHBias - 2u * P3 - P4;        // [1 2 0 -2 -1] + 1024
+      HG[w] = P0 + P4 + 4u * (P1 + P3) + 6u * P2;          // [1 4 6 4 1]
+      HC[w] = P3 + P4 + kHBias - P0 - P1;                  // [-1 -1 0 1 1] + 1024
+      HS[w] = S5;                                           // box 5
+      HT[w] = 2u * S3 + kHBias - S5;                        // 2*box3 - box5 + 1024
+      PC[w] = P2;
+      if (i >= 4) {
+        const int oy = strip * kStripRows + i - 4;
+        // window rows: r0 = oldest (i-4) ... r4 = newest (i)
+        const int r0 = (i + 1) % 5, r1 = (i + 2) % 5, r2 = (i + 3) % 5, r3 = (i + 4) % 5, r4 = w;
+        const uint32_t du = sobel_u8x2(HD[r0] + HD[r4] + 4u * (HD[r1] + HD[r3]) + 6u * HD[r2]);  // 16 * 1024 = 16384 of bias
+        const uint32_t dv = sobel_u8x2(HG[r0] + 2u * HG[r1] + 0x40004000u - 2u * HG[r3] - HG[r4]);
+        const uint32_t f2v = HC[r0] + HC[r1] + (kFBias * 0x10001u) - HC[r3] - HC[r4];
+        const uint32_t f1v = HT[r1] + HT[r2] + HT[r3] + 7u * PC[r2] + ((kFBias - 3072u) * 0x10001u) - HS[r0] - HS[r4];
+        if (oy < OH) {
+          const int idx = oy * OW + 2 * k;
+          *reinterpret_cast<uint32_t*>(&s.duv[idx]) = du | (dv << 8);
+          *reinterpret_cast<uint32_t*>(&s.f1[idx]) = f1v;
+          *reinterpret_cast<uint32_t*>(&s.f2[idx]) = f2v;
+        }
+      }
+    }
   }
   __syncthreads();
 
@@ -128,8 +147,8 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
     const int ox0 = 3 * bx + 5, oy0 = 3 * by + 5;
 #pragma unroll
     for (int pl = 0; pl < 2; pl++) {
-      const int16_t* f = pl ? s.f2 : s.f1;
-      int mn = 32767, mx = -32767, pmn = 0, pmx = 0;
+      const uint16_t* f = pl ? s.f2 : s.f1;  // value + kFBias
+      int mn = 65535, mx = -1, pmn = 0, pmx = 0;
 #pragma unroll
       for (int dy = 0; dy < 3; dy++)
 #pragma unroll
@@ -139,7 +158,7 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
           if (v < mn) { mn = v; pmn = pp; }   // strict: first in raster order wins (:199-224)
           if (v > mx) { mx = v; pmx = pp; }
         }
-      bool vmn = mn <= -g.tau, vmx = mx >= g.tau;
+      bool vmn = mn <= (int)kFBias - g.tau, vmx = mx >= (int)kFBias + g.tau;
       if (vmn) {
         const int cx = pmn & 255, cy = pmn >> 8;
 #pragma unroll
