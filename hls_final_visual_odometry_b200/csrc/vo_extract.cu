@@ -31,6 +31,7 @@ struct __align__(128) K1Smem {
   uint16_t f1[OH * OW];   // blob response + kFBias
   uint16_t f2[OH * OW];   // checkerboard response + kFBias
   int32_t warp_tot[K1_WARPS][4];
+  uint32_t work[4][NBX * NBY];  // per class, in list order: ox | oy<<8 | twin rank<<16 | twin class<<30 | has twin<<31
 };
 
 // Filter phase work split: a thread owns two adjacent output columns (packed into the two 16-bit
@@ -206,24 +207,35 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
   int32_t* cnt = fa.cnt + (int64_t)slot * fa.cnt_stride;
   if (tid < 4) cnt[bin0 + tid] = total[tid];
 
+  // every survivor leaves a one-word note at its list position; the records are then built densely,
+  // one thread per feature in list order (no divergence over empty blocks, coalesced record writes)
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    if (!flag[c]) continue;
+    uint32_t note = (uint32_t)pos[c];
+    if (c >= 2) {  // lower-class feature sharing this pixel (dedupe key of the reference's M[][])
+      if (flag[0] && pos[0] == pos[c]) note |= 0x80000000u | ((uint32_t)rank[0] << 16);
+      else if (flag[1] && pos[1] == pos[c]) note |= 0xC0000000u | ((uint32_t)rank[1] << 16);
+    }
+    s.work[c][rank[c]] = note;
+  }
+  __syncthreads();
+
   uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride;
   uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride;
   uint4* desc = fa.desc + (int64_t)slot * fa.rec_stride * 2;
   uint32_t* qsig = fa.q + (int64_t)slot * fa.rec_stride;
   constexpr int sdx[16] = {-3, -3, -1, -1, 3, 3, 1, 1, -1, -1, 1, 1, -5, -5, 5, 5};
   constexpr int sdy[16] = {-1, 1, -1, 1, -1, 1, -1, 1, -5, 5, -5, 5, -3, 3, -3, 3};
-#pragma unroll
-  for (int c = 0; c < 4; c++) {
-    if (!flag[c]) continue;
-    const int ox = pos[c] & 255, oy = pos[c] >> 8;
-    const int64_t rec = (int64_t)(bin0 + c) * g.cap + rank[c];
+  const int e1 = total[0], e2 = e1 + total[1], e3 = e2 + total[2], e4 = e3 + total[3];
+  for (int f = tid; f < e4; f += K1_THREADS) {
+    const int c = (f >= e1) + (f >= e2) + (f >= e3);
+    const int r = f - (c == 0 ? 0 : (c == 1 ? e1 : (c == 2 ? e2 : e3)));
+    const uint32_t note = s.work[c][r];
+    const int ox = (int)(note & 255u), oy = (int)((note >> 8) & 255u);
+    const int64_t rec = (int64_t)(bin0 + c) * g.cap + r;
     xy[rec] = (uint32_t)(x0 - 5 + ox) | ((uint32_t)(y0 - 5 + oy) << 16);
-    uint32_t tw = kNone;  // lower-class feature sharing this pixel (dedupe key of the reference's M[][])
-    if (c >= 2) {
-      if (flag[0] && pos[0] == pos[c]) tw = (0u << 16) | (uint32_t)rank[0];
-      else if (flag[1] && pos[1] == pos[c]) tw = (1u << 16) | (uint32_t)rank[1];
-    }
-    meta[rec] = tw;
+    meta[rec] = (note & 0x80000000u) ? (((note >> 30) & 1u) << 16) | ((note >> 16) & 0x3FFFu) : kNone;
     uint32_t w[8];
     const uint16_t* base = &s.duv[oy * OW + ox];
 #pragma unroll
