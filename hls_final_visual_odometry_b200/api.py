@@ -52,7 +52,15 @@ EXPORTS = [
     "vo_batch_extract_host", "vo_batch_extract_device", "vo_batch_match", "vo_batch_counts",
     "vo_batch_get_matches", "vo_batch_download_async", "vo_slot_dump_features", "vo_slot_feature_count",
     "vo_launch_count", "vo_profile_enable", "vo_profile_read", "vo_host_alloc", "vo_host_free",
+    "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
+    "vo_egomotion_rand", "vo_transformation_vector_to_matrix",
 ]
+
+class VoMonoParams(C.Structure):  # vo_mono_params: /root/reference/src/viso_mono.h:32-46, src/viso.h:56-64
+    _fields_ = [("f", C.c_double), ("cu", C.c_double), ("cv", C.c_double), ("height", C.c_double), ("pitch", C.c_double),
+                ("ransac_iters", C.c_int32), ("reserved", C.c_int32), ("inlier_threshold", C.c_double),
+                ("motion_threshold", C.c_double)]
+
 
 _lib = None
 
@@ -105,11 +113,21 @@ def load_library() -> C.CDLL:
         "vo_fence_wait": [vp, i32],
         "vo_host_alloc": [C.POINTER(vp), i64],
         "vo_host_free": [vp],
+        "vo_egomotion_create": [C.c_uint32, i32, C.POINTER(vp)],
+        "vo_egomotion_destroy": [vp],
+        "vo_estimate_motion_mono": [vp, vp, i32, C.POINTER(VoMonoParams), C.POINTER(C.c_double), C.POINTER(i32)],
+        "vo_egomotion_inliers": [vp, vp, i32, C.POINTER(i32)],
+        "vo_egomotion_rand": [vp],
+        "vo_transformation_vector_to_matrix": [C.POINTER(C.c_double), C.POINTER(C.c_double)],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
         fn.argtypes = args
-        if name != "vo_engine_destroy":
+        if name in ("vo_engine_destroy", "vo_egomotion_destroy", "vo_transformation_vector_to_matrix"):
+            fn.restype = None
+        elif name == "vo_egomotion_rand":
+            fn.restype = C.c_uint32
+        else:
             fn.restype = C.c_int
     _lib = lib
     return lib
@@ -361,3 +379,115 @@ class Matcher:
 
     def getMatches(self):
         return self.engine.get_matches()
+
+
+class Egomotion:
+    """Host stage F2 (vo_estimate_motion_mono): VisualOdometryMono::estimateMotion,
+    /root/reference/src/viso_mono.cpp:41-160, with the reference's rand() sample stream (seed 0)."""
+
+    def __init__(self, f=1.0, cu=0.0, cv=0.0, height=1.0, pitch=0.0, ransac_iters=2000, inlier_threshold=1e-5,
+                 motion_threshold=100.0, seed: int = 0, threads: int = 0):
+        self.lib = load_library()
+        self.prm = VoMonoParams(f=f, cu=cu, cv=cv, height=height, pitch=pitch, ransac_iters=ransac_iters,
+                                inlier_threshold=inlier_threshold, motion_threshold=motion_threshold)
+        h = C.c_void_p()
+        st = self.lib.vo_egomotion_create(seed, threads, C.byref(h))
+        if st != VO_OK:
+            raise VoError(st, "vo_egomotion_create")
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vo_egomotion_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def estimate(self, matches: np.ndarray):
+        """-> 6-vector (rx,ry,rz,tx,ty,tz) or None where the reference returns an empty vector."""
+        m = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)
+        tr = (C.c_double * 6)()
+        ok = C.c_int32(0)
+        st = self.lib.vo_estimate_motion_mono(self.h, _ptr(m) if len(m) else None, len(m), C.byref(self.prm), tr, C.byref(ok))
+        if st != VO_OK:
+            raise VoError(st, "vo_estimate_motion_mono")
+        return np.array(tr[:], dtype=np.float64) if ok.value else None
+
+    def inliers(self) -> np.ndarray:
+        n = C.c_int32(0)
+        self.lib.vo_egomotion_inliers(self.h, None, 0, C.byref(n))
+        out = np.zeros(max(n.value, 1), dtype=np.int32)
+        self.lib.vo_egomotion_inliers(self.h, _ptr(out), len(out), C.byref(n))
+        return out[: n.value]
+
+    def rand(self) -> int:
+        return int(self.lib.vo_egomotion_rand(self.h))
+
+
+def transformation_vector_to_matrix(tr) -> np.ndarray:
+    """VisualOdometry::transformationVectorToMatrix, /root/reference/src/viso.cpp:59-84."""
+    lib = load_library()
+    a = (C.c_double * 6)(*[float(x) for x in tr])
+    out = (C.c_double * 16)()
+    lib.vo_transformation_vector_to_matrix(a, out)
+    return np.array(out[:], dtype=np.float64).reshape(4, 4)
+
+
+class VisualOdometryMono:
+    """Python mirror of /root/reference/src/viso_mono.h:27-84 + src/viso.h:31-113: process() = pushBack ->
+    matchFeatures (GPU circular matching + host removeOutliers) -> bucketFeatures -> getMatches ->
+    updateMotion (host egomotion)."""
+
+    class parameters:
+        def __init__(self):
+            self.match = Matcher.parameters()
+            self.max_features, self.bucket_width, self.bucket_height = 2, 50.0, 50.0   # src/viso.h:43-53
+            self.f, self.cu, self.cv = 1.0, 0.0, 0.0                                   # src/viso.h:56-64
+            self.height, self.pitch = 1.0, 0.0                                         # src/viso_mono.h:32-46
+            self.ransac_iters, self.inlier_threshold, self.motion_threshold = 2000, 1e-5, 100.0
+
+    def __init__(self, width: int, height: int, param: "VisualOdometryMono.parameters | None" = None, device: int = 0):
+        self.param = param or VisualOdometryMono.parameters()
+        p = self.param
+        self.matcher = Matcher(width, height, p.match, device=device)
+        self.ego = Egomotion(p.f, p.cu, p.cv, p.height, p.pitch, p.ransac_iters, p.inlier_threshold, p.motion_threshold)
+        self.Tr_delta = np.eye(4)
+        self.Tr_valid = False
+        self.p_matched = np.zeros(0, dtype=P_MATCH_DTYPE)
+
+    def process(self, I, dims=None, replace=False) -> bool:
+        if isinstance(I, np.ndarray) and I.dtype == P_MATCH_DTYPE:      # process(p_matched): src/viso.h:75-78
+            self.p_matched = I
+            return self.updateMotion()
+        self.matcher.pushBack(I, dims, replace)
+        self.matcher.matchFeatures(0)
+        self.matcher.bucketFeatures(self.param.max_features, self.param.bucket_width, self.param.bucket_height)
+        self.p_matched = self.matcher.getMatches()
+        return self.updateMotion()
+
+    def updateMotion(self) -> bool:  # src/viso.cpp:42-57
+        tr = self.ego.estimate(self.p_matched)
+        if tr is None:
+            return False
+        self.Tr_delta = transformation_vector_to_matrix(tr)
+        self.Tr_valid = True
+        return True
+
+    def getMotion(self):
+        return self.Tr_delta
+
+    def getMatches(self):
+        return self.matcher.getMatches()
+
+    def getNumberOfMatches(self):
+        return len(self.p_matched)
+
+    def getNumberOfInliers(self):
+        return len(self.ego.inliers())
+
+    def getInlierIndices(self):
+        return self.ego.inliers()

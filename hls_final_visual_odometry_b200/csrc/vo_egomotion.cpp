@@ -1,0 +1,493 @@
+// Host stage F2 of SURVEY.md section 8: monocular egomotion from a bucketed match list.
+//
+// Replaces, within a stated floating-point tolerance (tests/test_egomotion.py: 1e-6 on the six motion
+// parameters against the compiled reference), the reference's
+//   VisualOdometryMono::estimateMotion        src/viso_mono.cpp:41-160
+//   ::normalizeFeaturePoints                  src/viso_mono.cpp:187-240
+//   ::fundamentalMatrix                       src/viso_mono.cpp:242-275
+//   ::getInlier                               src/viso_mono.cpp:277-325
+//   ::EtoRt / ::triangulateChieral            src/viso_mono.cpp:327-401
+//   VisualOdometry::getRandomSample           src/viso.cpp:86-106   (glibc rand() stream after srand(0), :34)
+//   VisualOdometry::transformationVectorToMatrix  src/viso.cpp:59-84
+// This is tiny dense double-precision math on <= a few hundred points: a host stage by design (the
+// reference's FPGA build keeps it on the host too, hls_opencl/host/main2.cpp:398-402).  What is new
+// here: no heap Matrix class (fixed-size stack arrays), a one-sided Jacobi SVD instead of the
+// reference's Golub-Reinsch routine (src/matrix.cpp:579-760; every quantity used downstream is
+// invariant to the sign/rotation freedom of singular vectors, see the notes at each call), a private
+// re-entrant copy of glibc's TYPE_3 rand() so engines do not share the process-wide generator, and
+// RANSAC hypotheses evaluated by a pool of host threads with the reference's sequential
+// "first strictly larger inlier set wins" rule applied afterwards.
+//
+// Mixed precision is mirrored where the reference has it: match coordinates live in float fields, so the
+// centroid shift, the scaling and the products of the constraint matrix round to float exactly where
+// src/viso_mono.cpp does.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "../../include/vo_b200.h"
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// glibc rand(): TYPE_3 additive feedback generator r[i] = r[i-3] + r[i-31], seeded by the Lehmer
+// recurrence 16807 * x mod (2^31 - 1), first 310 outputs discarded, result >> 1.
+// ---------------------------------------------------------------------------------------------
+struct GlibcRand {
+  int f, b;  // positions of r[i-3] and r[i-31] in the 31-word ring
+  uint32_t ring[31];
+  void seed(uint32_t s) {
+    if (s == 0) s = 1;
+    int32_t word = (int32_t)s;
+    ring[0] = s;
+    for (int i = 1; i < 31; i++) {
+      const int32_t hi = word / 127773, lo = word % 127773;
+      word = 16807 * lo - 2836 * hi;
+      if (word < 0) word += 2147483647;
+      ring[i] = (uint32_t)word;
+    }
+    f = 3; b = 0;
+    for (int i = 0; i < 310; i++) next();
+  }
+  uint32_t next() {
+    ring[f] += ring[b];
+    const uint32_t out = ring[f] >> 1;
+    f = (f + 1 == 31) ? 0 : f + 1;
+    b = (b + 1 == 31) ? 0 : b + 1;
+    return out;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// One-sided Jacobi SVD of a row-major m x n matrix (any m, n <= kMaxN columns).
+// Output: w[n] singular values in descending order, V (n x n, row-major, orthogonal: a product of plane
+// rotations), and G = A*V (m x n), whose column j has norm w[j] (u_j = G[:,j] / w[j] where w[j] > 0).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxN = 9;
+
+void jacobi_svd(const double* A, int m, int n, std::vector<double>& G, double* w, double* V, bool want_g = false) {
+  G.assign(A, A + (size_t)m * n);
+  double fro = 0;
+  for (size_t i = 0; i < (size_t)m * n; i++) fro += A[i] * A[i];
+  // a column whose norm has dropped to rounding level of the whole matrix is a null direction already;
+  // rotating it further only chases noise (this is what ends the sweeps for the 8 x 9 systems of RANSAC)
+  const double tiny = fro * 1e-30;
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) V[i * n + j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 60; sweep++) {
+    bool rotated = false;
+    for (int p = 0; p < n - 1; p++) {
+      for (int q = p + 1; q < n; q++) {
+        double alpha = 0, beta = 0, gamma = 0;
+        for (int k = 0; k < m; k++) {
+          const double gp = G[(size_t)k * n + p], gq = G[(size_t)k * n + q];
+          alpha += gp * gp; beta += gq * gq; gamma += gp * gq;
+        }
+        if (alpha <= tiny || beta <= tiny || gamma * gamma <= 1e-30 * alpha * beta) continue;
+        rotated = true;
+        const double zeta = (beta - alpha) / (2.0 * gamma);
+        const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
+        const double c = 1.0 / std::sqrt(1.0 + t * t), s = c * t;
+        for (int k = 0; k < m; k++) {
+          const double gp = G[(size_t)k * n + p], gq = G[(size_t)k * n + q];
+          G[(size_t)k * n + p] = c * gp - s * gq;
+          G[(size_t)k * n + q] = s * gp + c * gq;
+        }
+        for (int k = 0; k < n; k++) {
+          const double vp = V[k * n + p], vq = V[k * n + q];
+          V[k * n + p] = c * vp - s * vq;
+          V[k * n + q] = s * vp + c * vq;
+        }
+      }
+    }
+    if (!rotated) break;
+  }
+  double nrm[kMaxN];
+  int order[kMaxN];
+  for (int j = 0; j < n; j++) {
+    double s = 0;
+    for (int k = 0; k < m; k++) s += G[(size_t)k * n + j] * G[(size_t)k * n + j];
+    nrm[j] = std::sqrt(s);
+    order[j] = j;
+  }
+  std::stable_sort(order, order + n, [&](int a, int b) { return nrm[a] > nrm[b]; });  // descending (src/matrix.cpp:759)
+  double V2[kMaxN * kMaxN];
+  for (int j = 0; j < n; j++) {
+    w[j] = nrm[order[j]];
+    for (int k = 0; k < n; k++) V2[k * n + j] = V[k * n + order[j]];
+  }
+  std::memcpy(V, V2, sizeof(double) * n * n);
+  if (want_g) {  // only the 3 x 3 callers need the left vectors
+    std::vector<double> G2(G.size());
+    for (int j = 0; j < n; j++)
+      for (int k = 0; k < m; k++) G2[(size_t)k * n + j] = G[(size_t)k * n + order[j]];
+    G.swap(G2);
+  }
+}
+
+struct Svd3 { double U[9], w[3], V[9]; };
+
+// 3x3 SVD with an orthogonal U even when the matrix has rank 2: u2 = u0 x u1.  (The reference's U comes
+// from Householder/Givens products and is orthogonal too; its sign of u2 is arbitrary, and so is ours.)
+Svd3 svd3(const double* A) {
+  Svd3 r;
+  std::vector<double> G;
+  jacobi_svd(A, 3, 3, G, r.w, r.V, true);
+  for (int j = 0; j < 2; j++) {
+    const double inv = r.w[j] > 0 ? 1.0 / r.w[j] : 0.0;
+    for (int k = 0; k < 3; k++) r.U[k * 3 + j] = G[k * 3 + j] * inv;
+  }
+  if (r.w[2] > 1e-9 * r.w[0]) {
+    for (int k = 0; k < 3; k++) r.U[k * 3 + 2] = G[k * 3 + 2] / r.w[2];
+  } else {
+    r.U[0 * 3 + 2] = r.U[1 * 3 + 0] * r.U[2 * 3 + 1] - r.U[2 * 3 + 0] * r.U[1 * 3 + 1];
+    r.U[1 * 3 + 2] = r.U[2 * 3 + 0] * r.U[0 * 3 + 1] - r.U[0 * 3 + 0] * r.U[2 * 3 + 1];
+    r.U[2 * 3 + 2] = r.U[0 * 3 + 0] * r.U[1 * 3 + 1] - r.U[1 * 3 + 0] * r.U[0 * 3 + 1];
+  }
+  return r;
+}
+
+inline void mul3(const double* A, const double* B, double* C) {  // C = A*B, all 3x3 row-major
+  double T[9];
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += A[i * 3 + k] * B[k * 3 + j];
+      T[i * 3 + j] = s;
+    }
+  std::memcpy(C, T, sizeof(T));
+}
+inline void transpose3(const double* A, double* T) {
+  double R[9];
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) R[j * 3 + i] = A[i * 3 + j];
+  std::memcpy(T, R, sizeof(R));
+}
+inline double det3(const double* A) {
+  return A[0] * (A[4] * A[8] - A[5] * A[7]) - A[1] * (A[3] * A[8] - A[5] * A[6]) + A[2] * (A[3] * A[7] - A[4] * A[6]);
+}
+
+// U * diag(w0, w1, 0) * V^T : the rank-2 projection of src/viso_mono.cpp:271-274 and :93-97
+void rank2(const double* M, double* out) {
+  const Svd3 s = svd3(M);
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++)
+      out[i * 3 + j] = s.U[i * 3 + 0] * s.w[0] * s.V[j * 3 + 0] + s.U[i * 3 + 1] * s.w[1] * s.V[j * 3 + 1];
+}
+
+struct Pt { float u1p, v1p, u1c, v1c; };
+
+}  // namespace
+
+struct vo_egomotion {
+  GlibcRand rng;
+  int threads;
+  std::vector<int32_t> inliers;
+};
+
+namespace {
+
+// src/viso_mono.cpp:187-240.  Float fields, double accumulators: rounding points as in the reference.
+bool normalize_points(std::vector<Pt>& p, double Tp[9], double Tc[9]) {
+  const double n = (double)p.size();
+  double cpu = 0, cpv = 0, ccu = 0, ccv = 0;
+  for (const Pt& m : p) { cpu += m.u1p; cpv += m.v1p; ccu += m.u1c; ccv += m.v1c; }
+  cpu /= n; cpv /= n; ccu /= n; ccv /= n;
+  for (Pt& m : p) {
+    m.u1p = (float)(m.u1p - cpu); m.v1p = (float)(m.v1p - cpv);
+    m.u1c = (float)(m.u1c - ccu); m.v1c = (float)(m.v1c - ccv);
+  }
+  double sp = 0, sc = 0;
+  for (const Pt& m : p) {
+    sp += std::sqrt(m.u1p * m.u1p + m.v1p * m.v1p);  // float product, float sum, float sqrt
+    sc += std::sqrt(m.u1c * m.u1c + m.v1c * m.v1c);
+  }
+  if (std::fabs(sp) < 1e-10 || std::fabs(sc) < 1e-10) return false;
+  sp = std::sqrt(2.0) * n / sp;
+  sc = std::sqrt(2.0) * n / sc;
+  for (Pt& m : p) {
+    m.u1p = (float)(m.u1p * sp); m.v1p = (float)(m.v1p * sp);
+    m.u1c = (float)(m.u1c * sc); m.v1c = (float)(m.v1c * sc);
+  }
+  const double tp[9] = {sp, 0, -sp * cpu, 0, sp, -sp * cpv, 0, 0, 1};
+  const double tc[9] = {sc, 0, -sc * ccu, 0, sc, -sc * ccv, 0, 0, 1};
+  std::memcpy(Tp, tp, sizeof(tp));
+  std::memcpy(Tc, tc, sizeof(tc));
+  return true;
+}
+
+// src/viso_mono.cpp:242-275: 8-point constraint matrix (products rounded to float, as `m.u1c*m.u1p` on float
+// fields is), null vector = right singular vector of the smallest singular value, then rank 2.
+// The null vector's sign is free; everything downstream (Sampson distance, U*diag*V^T of F) is even in it.
+void fundamental(const std::vector<Pt>& p, const int32_t* active, int n_active, double F[9], std::vector<double>& A,
+                 std::vector<double>& G) {
+  A.resize((size_t)n_active * 9);
+  for (int i = 0; i < n_active; i++) {
+    const Pt& m = p[active[i]];
+    double* a = &A[(size_t)i * 9];
+    a[0] = m.u1c * m.u1p; a[1] = m.u1c * m.v1p; a[2] = m.u1c;
+    a[3] = m.v1c * m.u1p; a[4] = m.v1c * m.v1p; a[5] = m.v1c;
+    a[6] = m.u1p;         a[7] = m.v1p;         a[8] = 1;
+  }
+  double w[9], V[81];
+  jacobi_svd(A.data(), n_active, 9, G, w, V);
+  double F0[9];
+  for (int k = 0; k < 9; k++) F0[k] = V[k * 9 + 8];
+  rank2(F0, F);
+}
+
+// src/viso_mono.cpp:277-325: Sampson distance below the threshold
+void sampson_inliers(const std::vector<Pt>& p, const double F[9], double thr, std::vector<int32_t>& out) {
+  out.clear();
+  for (int32_t i = 0; i < (int32_t)p.size(); i++) {
+    const double u1 = p[i].u1p, v1 = p[i].v1p, u2 = p[i].u1c, v2 = p[i].v1c;
+    const double Fx1u = F[0] * u1 + F[1] * v1 + F[2];
+    const double Fx1v = F[3] * u1 + F[4] * v1 + F[5];
+    const double Fx1w = F[6] * u1 + F[7] * v1 + F[8];
+    const double Ftx2u = F[0] * u2 + F[3] * v2 + F[6];
+    const double Ftx2v = F[1] * u2 + F[4] * v2 + F[7];
+    const double x2tFx1 = u2 * Fx1u + v2 * Fx1v + Fx1w;
+    const double d = x2tFx1 * x2tFx1 / (Fx1u * Fx1u + Fx1v * Fx1v + Ftx2u * Ftx2u + Ftx2v * Ftx2v);
+    if (std::fabs(d) < thr) out.push_back(i);
+  }
+}
+
+// src/viso_mono.cpp:363-401: linear triangulation (null vector of the 4x4 system) and chirality count
+int triangulate(const std::vector<Pt>& p, const double K[9], const double R[9], const double t[3], std::vector<double>& X) {
+  const int n = (int)p.size();
+  X.assign((size_t)4 * n, 0.0);
+  double P1[12], P2[12], Rt[12];
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < 3; j++) { P1[i * 4 + j] = K[i * 3 + j]; Rt[i * 4 + j] = R[i * 3 + j]; }
+    P1[i * 4 + 3] = 0; Rt[i * 4 + 3] = t[i];
+  }
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 4; j++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += K[i * 3 + k] * Rt[k * 4 + j];
+      P2[i * 4 + j] = s;
+    }
+  std::vector<double> G;
+  double J[16], w[4], V[16];
+  for (int i = 0; i < n; i++) {
+    for (int j = 0; j < 4; j++) {
+      J[0 * 4 + j] = P1[2 * 4 + j] * p[i].u1p - P1[0 * 4 + j];
+      J[1 * 4 + j] = P1[2 * 4 + j] * p[i].v1p - P1[1 * 4 + j];
+      J[2 * 4 + j] = P2[2 * 4 + j] * p[i].u1c - P2[0 * 4 + j];
+      J[3 * 4 + j] = P2[2 * 4 + j] * p[i].v1c - P2[1 * 4 + j];
+    }
+    jacobi_svd(J, 4, 4, G, w, V);
+    for (int k = 0; k < 4; k++) X[(size_t)k * n + i] = V[k * 4 + 3];
+  }
+  int num = 0;
+  for (int i = 0; i < n; i++) {
+    double a = 0, b = 0;
+    for (int k = 0; k < 4; k++) { a += P1[2 * 4 + k] * X[(size_t)k * n + i]; b += P2[2 * 4 + k] * X[(size_t)k * n + i]; }
+    const double x3 = X[(size_t)3 * n + i];
+    if (a * x3 > 0 && b * x3 > 0) num++;
+  }
+  return num;
+}
+
+// src/viso_mono.cpp:327-361.  T = U Z U^T and {U W V^T, U W^T V^T} do not depend on the rotation freedom of
+// the two equal singular vectors; flipping u2 swaps the two rotations after the determinant fix, so only the
+// ORDER in which the four (R, t) candidates are tried can differ from the reference -- and that matters
+// only for an exact tie of the chirality counts.
+void e_to_rt(const double E[9], const double K[9], const std::vector<Pt>& p, std::vector<double>& X, double R[9], double t[3]) {
+  const Svd3 s = svd3(E);
+  const double Wm[9] = {0, -1, 0, 1, 0, 0, 0, 0, 1}, Zm[9] = {0, 1, 0, -1, 0, 0, 0, 0, 0};
+  double Ut[9], Vt[9], Wt[9], T[9], Ra[9], Rb[9], tmp[9];
+  transpose3(s.U, Ut); transpose3(s.V, Vt); transpose3(Wm, Wt);
+  mul3(s.U, Zm, tmp); mul3(tmp, Ut, T);
+  mul3(s.U, Wm, tmp); mul3(tmp, Vt, Ra);
+  mul3(s.U, Wt, tmp); mul3(tmp, Vt, Rb);
+  double t0[3] = {T[2 * 3 + 1], T[0 * 3 + 2], T[1 * 3 + 0]};
+  if (det3(Ra) < 0) for (double& x : Ra) x = -x;
+  if (det3(Rb) < 0) for (double& x : Rb) x = -x;
+  int best = 0;
+  std::vector<double> Xc;
+  double tb[3] = {t0[0], t0[1], t0[2]};  // the reference leaves t = +t0 and R, X empty when no candidate has an inlier
+  std::memset(R, 0, sizeof(double) * 9);
+  X.clear();
+  for (int i = 0; i < 4; i++) {
+    const double* Ri = (i < 2) ? Ra : Rb;
+    const double sg = (i & 1) ? -1.0 : 1.0;
+    const double ti[3] = {sg * t0[0], sg * t0[1], sg * t0[2]};
+    const int num = triangulate(p, K, Ri, ti, Xc);
+    if (num > best) {
+      best = num;
+      X = Xc;
+      std::memcpy(R, Ri, sizeof(double) * 9);
+      std::memcpy(tb, ti, sizeof(tb));
+    }
+  }
+  std::memcpy(t, tb, sizeof(tb));
+}
+
+}  // namespace
+
+namespace {
+
+// VisualOdometry::getRandomSample(N, 8): src/viso.cpp:86-106 (draw without replacement from a shrinking set)
+void draw_sample(GlibcRand& rng, int32_t N, std::vector<int32_t>& pool, int32_t out[8]) {
+  pool.resize(N);
+  for (int32_t i = 0; i < N; i++) pool[i] = i;
+  for (int i = 0; i < 8; i++) {
+    const int32_t j = (int32_t)(rng.next() % (uint32_t)pool.size());
+    out[i] = pool[j];
+    pool.erase(pool.begin() + j);
+  }
+}
+
+// src/viso_mono.cpp:41-160.  Returns false where the reference returns an empty vector.
+bool estimate_motion(vo_egomotion* eg, const vo_p_match* matches, int32_t N, const vo_mono_params& prm, double tr[6]) {
+  eg->inliers.clear();  // the reference clears its inlier list only after normalisation (:62); callers never look at it on failure
+  if (N < 10) return false;
+  std::vector<Pt> raw(N), p;
+  for (int32_t i = 0; i < N; i++) raw[i] = Pt{matches[i].u1p, matches[i].v1p, matches[i].u1c, matches[i].v1c};
+  p = raw;
+  const double K[9] = {prm.f, 0, prm.cu, 0, prm.f, prm.cv, 0, 0, 1};
+  double Tp[9], Tc[9];
+  if (!normalize_points(p, Tp, Tc)) return false;
+
+  // ---- RANSAC: the sample stream is drawn sequentially (it is the reference's rand() stream); the
+  //      hypotheses are independent, so they are scored by a pool of threads; the winner is the FIRST
+  //      hypothesis with the largest inlier count == the sequential `if (curr.size() > best.size())`.
+  const int iters = std::max(0, prm.ransac_iters);
+  std::vector<int32_t> samples((size_t)iters * 8), pool;
+  for (int k = 0; k < iters; k++) draw_sample(eg->rng, N, pool, &samples[(size_t)k * 8]);
+  std::vector<int32_t> counts(iters, 0);
+  auto score = [&](int k0, int k1) {
+    std::vector<double> A, G;
+    std::vector<int32_t> inl;
+    double F[9];
+    for (int k = k0; k < k1; k++) {
+      fundamental(p, &samples[(size_t)k * 8], 8, F, A, G);
+      sampson_inliers(p, F, prm.inlier_threshold, inl);
+      counts[k] = (int32_t)inl.size();
+    }
+  };
+  const int nt = std::max(1, std::min(eg->threads, iters / 64 + 1));
+  if (nt == 1) {
+    score(0, iters);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; t++) th.emplace_back(score, (int)((int64_t)iters * t / nt), (int)((int64_t)iters * (t + 1) / nt));
+    for (auto& t : th) t.join();
+  }
+  int best_k = -1, best_n = 0;
+  for (int k = 0; k < iters; k++)
+    if (counts[k] > best_n) { best_n = counts[k]; best_k = k; }
+  std::vector<double> A, G;
+  double F[9];
+  if (best_k >= 0) {
+    fundamental(p, &samples[(size_t)best_k * 8], 8, F, A, G);
+    sampson_inliers(p, F, prm.inlier_threshold, eg->inliers);
+  }
+  if (eg->inliers.size() < 10) return false;
+
+  // refine on all inliers, denormalise, essential matrix, rank 2 (:85-97)
+  fundamental(p, eg->inliers.data(), (int)eg->inliers.size(), F, A, G);
+  double Tct[9], Kt[9], E[9], tmp[9];
+  transpose3(Tc, Tct); transpose3(K, Kt);
+  mul3(Tct, F, tmp); mul3(tmp, Tp, F);
+  mul3(Kt, F, tmp); mul3(tmp, K, E);
+  rank2(E, E);
+
+  std::vector<double> X;
+  double R[9], t[3];
+  e_to_rt(E, K, raw, X, R, t);
+  if (X.empty()) return false;
+
+  // 3-D points with positive depth (:103-113)
+  std::vector<double> d, dist;  // d = n^T (y, z), dist = |x|+|y|+|z|
+  const double n0 = std::cos(-prm.pitch), n1 = std::sin(-prm.pitch);
+  for (int32_t i = 0; i < N; i++) {
+    const double w = X[(size_t)3 * N + i];
+    const double x = X[i] / w, y = X[(size_t)N + i] / w, z = X[(size_t)2 * N + i] / w;
+    if (z > 0) {
+      dist.push_back(std::fabs(x) + std::fabs(y) + std::fabs(z));
+      d.push_back(n0 * y + n1 * z);
+    }
+  }
+  const int np = (int)d.size();
+  if (np < 10) return false;
+  std::vector<double> sorted = dist;
+  std::nth_element(sorted.begin(), sorted.begin() + np / 2, sorted.end());
+  const double median = sorted[np / 2];
+  if (median > prm.motion_threshold) return false;
+
+  // ground-plane distance by kernel density over the candidate heights (:127-151)
+  const double sigma = median / 50.0, weight = 1.0 / (2.0 * sigma * sigma);
+  double best_sum = 0;
+  int best_idx = 0;
+  for (int i = 0; i < np; i++) {
+    if (d[i] > median / prm.motion_threshold) {
+      double sum = 0;
+      for (int j = 0; j < np; j++) {
+        const double dd = d[j] - d[i];
+        sum += std::exp(-dd * dd * weight);
+      }
+      if (sum > best_sum) { best_sum = sum; best_idx = i; }
+    }
+  }
+  const double scale = prm.height / d[best_idx];
+  const double ry = std::asin(R[2]);
+  const double rx = std::asin(-R[5] / std::cos(ry));
+  const double rz = std::asin(-R[1] / std::cos(ry));
+  tr[0] = rx; tr[1] = ry; tr[2] = rz;
+  tr[3] = t[0] * scale; tr[4] = t[1] * scale; tr[5] = t[2] * scale;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+vo_status vo_egomotion_create(uint32_t seed, int32_t threads, vo_egomotion** out) {
+  if (!out) return VO_ERR_INVALID;
+  vo_egomotion* eg = new vo_egomotion();
+  eg->rng.seed(seed);  // VisualOdometry::VisualOdometry calls srand(0): src/viso.cpp:34
+  int hw = (int)std::thread::hardware_concurrency();
+  if (hw <= 0) hw = 1;
+  eg->threads = threads > 0 ? threads : std::min(hw, 16);
+  *out = eg;
+  return VO_OK;
+}
+
+void vo_egomotion_destroy(vo_egomotion* eg) { delete eg; }
+
+vo_status vo_estimate_motion_mono(vo_egomotion* eg, const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
+                                  double tr_delta[6], int32_t* ok) {
+  if (!eg || !prm || !tr_delta || !ok || n < 0 || (n > 0 && !matches)) return VO_ERR_INVALID;
+  *ok = estimate_motion(eg, matches, n, *prm, tr_delta) ? 1 : 0;
+  return VO_OK;
+}
+
+vo_status vo_egomotion_inliers(const vo_egomotion* eg, int32_t* out, int32_t cap, int32_t* n) {
+  if (!eg || !n) return VO_ERR_INVALID;
+  *n = (int32_t)eg->inliers.size();
+  if (out) {
+    if (cap < *n) return VO_ERR_CAPACITY;
+    std::memcpy(out, eg->inliers.data(), sizeof(int32_t) * eg->inliers.size());
+  }
+  return VO_OK;
+}
+
+uint32_t vo_egomotion_rand(vo_egomotion* eg) { return eg ? eg->rng.next() : 0u; }
+
+// VisualOdometry::transformationVectorToMatrix: src/viso.cpp:59-84 (row-major 4x4)
+void vo_transformation_vector_to_matrix(const double tr[6], double Tr[16]) {
+  const double sx = std::sin(tr[0]), cx = std::cos(tr[0]), sy = std::sin(tr[1]), cy = std::cos(tr[1]);
+  const double sz = std::sin(tr[2]), cz = std::cos(tr[2]);
+  const double M[16] = {+cy * cz,                -cy * sz,                +sy,      tr[3],
+                        +sx * sy * cz + cx * sz, -sx * sy * sz + cx * cz, -sx * cy, tr[4],
+                        -cx * sy * cz + sx * sz, +cx * sy * sz + sx * cz, +cx * cy, tr[5],
+                        0, 0, 0, 1};
+  std::memcpy(Tr, M, sizeof(M));
+}
+
+}  // extern "C"

@@ -1,5 +1,6 @@
 // vo_demo: the reference's src/demo.cpp loop (read raw I1_%06d.dat frames, process(), print the
-// number of matches per frame) on the C++ shim.  Usage: vo_demo <dir> <width> <height> <n_frames>
+// number of matches and inliers per frame, accumulate the pose as src/demo.cpp:222-236 does) on the C++ shim.
+// Usage: vo_demo <dir> <width> <height> <n_frames> [f cu cv]
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
@@ -17,7 +18,13 @@ int main(int argc, char** argv) {
   const std::string dir = argv[1];
   const int32_t width = atoi(argv[2]), height = atoi(argv[3]), n = atoi(argv[4]);
   VisualOdometryMono::parameters param;
+  param.calib.f = argc > 5 ? atof(argv[5]) : 491.543832;   // calibration of the reference demo: src/demo.cpp:60-65
+  param.calib.cu = argc > 6 ? atof(argv[6]) : 484.474328;
+  param.calib.cv = argc > 7 ? atof(argv[7]) : 147.888234;
+  param.height = 1.6;
+  param.pitch = -0.08;
   VisualOdometryMono viso(param);
+  Matrix pose = Matrix::eye(4);
   std::vector<uint8_t> img((size_t)width * height);
   for (int32_t i = 0; i < n; i++) {
     char name[256];
@@ -28,14 +35,19 @@ int main(int argc, char** argv) {
       return 1;
     }
     int32_t dims[] = {width, height, width};
-    viso.process(img.data(), dims);
+    const bool ok = viso.process(img.data(), dims);
     if (viso.getMatcher()->lastStatus() != 0) return 2;
     std::vector<Matcher::p_match> m = viso.getMatches();
     double su = 0, sv = 0;
     for (size_t k = 0; k < m.size(); k++) { su += m[k].u1c - m[k].u1p; sv += m[k].v1c - m[k].v1p; }
     std::cout << "Processing: Frame: " << i << ", Matches: " << m.size();
     if (!m.empty()) std::cout << ", mean flow: " << su / m.size() << " " << sv / m.size();
-    std::cout << std::endl;
+    if (ok) {  // src/demo.cpp:225-232
+      pose = pose * Matrix::inv(viso.getMotion());
+      std::cout << ", Inliers: " << 100.0 * viso.getNumberOfInliers() / viso.getNumberOfMatches() << " %" << std::endl << pose << std::endl;
+    } else {
+      std::cout << " ... failed!" << std::endl;
+    }
   }
   std::cout << "Demo complete! Exiting ..." << std::endl;
   return 0;

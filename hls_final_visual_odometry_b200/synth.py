@@ -56,3 +56,70 @@ def make_sequence(width: int, height: int, n_frames: int, seed: int = 0, blur_pa
     """(n_frames, height, width) uint8 frames of one synthetic sequence."""
     canvas = make_canvas(width, height, seed, blur_passes, contrast)
     return np.stack([frame_from_canvas(canvas, width, height, f) for f in range(n_frames)])
+
+
+# ------------------------------------------------------------------------------------------------
+# Match lists from a 3-D scene (SURVEY.md section 8 rows D1/F2): the blurred-noise sequence above is a pure
+# image translation (a planar, degenerate configuration for the 8-point algorithm: the reference's
+# mono egomotion returns false on it), so the egomotion stage is exercised with match lists projected
+# from a static, non-planar point cloud seen by a forward-moving KITTI-like camera.
+# ------------------------------------------------------------------------------------------------
+KITTI_CALIB = dict(f=718.856, cu=607.1928, cv=185.2157)   # KITTI odometry sequence 00 colour-left intrinsics
+KITTI_HEIGHT, KITTI_PITCH = 1.6, -0.08                      # the reference demo's values (src/demo.cpp:63-64)
+
+
+def _rot(rx, ry, rz):
+    sx, cx, sy, cy, sz, cz = math.sin(rx), math.cos(rx), math.sin(ry), math.cos(ry), math.sin(rz), math.cos(rz)
+    return np.array([[cy * cz, -cy * sz, sy],
+                     [sx * sy * cz + cx * sz, -sx * sy * sz + cx * cz, -sx * cy],
+                     [-cx * sy * cz + sx * sz, cx * sy * sz + sx * cz, cx * cy]])
+
+
+def make_scene_matches(n_lists: int, seed: int = 0, width: int = 1241, height: int = 376, n_points: int = 320,
+                       step: float = 0.9, outlier_frac: float = 0.05, calib=None, cam_height: float = KITTI_HEIGHT):
+    """n_lists match lists (structured arrays with fields u1p,v1p,u1c,v1c,... like Matcher::p_match) of a camera
+    driving forward `step` metres per frame with a small yaw/pitch wobble through a static scene: a ground
+    plane cam_height below the camera plus random structure on both sides.  Coordinates are rounded to integer
+    pixels like the matcher's output; outlier_frac of the matches get a random wrong partner.
+    Returns (lists, true_motions[n_lists, 6]) with motion = (rx,ry,rz,tx,ty,tz) of Tr_delta (prev -> curr)."""
+    from .api import P_MATCH_DTYPE
+    calib = calib or KITTI_CALIB
+    f, cu, cv = calib["f"], calib["cu"], calib["cv"]
+    rng = np.random.default_rng(seed)
+    lists, motions = [], []
+    for _ in range(n_lists):
+        # scene in the PREVIOUS camera frame (x right, y down, z forward)
+        n_ground = n_points // 2
+        gz = rng.uniform(5.0, 40.0, n_ground)
+        gx = rng.uniform(-8.0, 8.0, n_ground)
+        ground = np.stack([gx, np.full(n_ground, cam_height), gz], 1)
+        n_struct = 3 * n_points
+        sz_ = rng.uniform(6.0, 60.0, n_struct)
+        side = rng.choice([-1.0, 1.0], n_struct)
+        sx_ = side * rng.uniform(4.0, 15.0, n_struct)
+        sy_ = rng.uniform(-6.0, cam_height, n_struct)
+        pts = np.concatenate([ground, np.stack([sx_, sy_, sz_], 1)])
+        rx, ry, rz = rng.normal(0, 0.002), rng.normal(0, 0.01), rng.normal(0, 0.002)
+        R = _rot(rx, ry, rz)
+        t = np.array([rng.normal(0, 0.02), rng.normal(0, 0.01), -step * rng.uniform(0.8, 1.2)])  # p_curr = R p_prev + t
+        pc = pts @ R.T + t
+        up, vp = f * pts[:, 0] / pts[:, 2] + cu, f * pts[:, 1] / pts[:, 2] + cv
+        uc, vc = f * pc[:, 0] / pc[:, 2] + cu, f * pc[:, 1] / pc[:, 2] + cv
+        ok = (pc[:, 2] > 1.0) & (up >= 9) & (up <= width - 9) & (vp >= 9) & (vp <= height - 9) & \
+             (uc >= 9) & (uc <= width - 9) & (vc >= 9) & (vc <= height - 9)
+        idx = np.flatnonzero(ok)[:n_points]
+        m = np.zeros(len(idx), dtype=P_MATCH_DTYPE)
+        m["u1p"], m["v1p"] = np.rint(up[idx]), np.rint(vp[idx])
+        m["u1c"], m["v1c"] = np.rint(uc[idx]), np.rint(vc[idx])
+        n_out = int(outlier_frac * len(idx))
+        if n_out:
+            bad = rng.choice(len(idx), n_out, replace=False)
+            m["u1c"][bad] = np.rint(rng.uniform(9, width - 9, n_out))
+            m["v1c"][bad] = np.rint(rng.uniform(9, height - 9, n_out))
+        for fld in ("u2p", "v2p", "u2c", "v2c"):
+            m[fld] = -1.0
+        for fld in ("i1p", "i2p", "i1c", "i2c"):
+            m[fld] = -1
+        lists.append(m)
+        motions.append([rx, ry, rz, t[0], t[1], t[2]])
+    return lists, np.array(motions)

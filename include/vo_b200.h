@@ -21,6 +21,7 @@
  *       bucketFeatures / getMatches (src/matcher.h:116-143, src/matcher.cpp:51-187)
  *  3. batch level     == many frames / frame pairs per launch (what the reference's FPGA host
  *       pipelines by hand, hls_opencl/host/main2.cpp:395-519); this is the throughput path.
+ *  4. host stage F2   == VisualOdometryMono::estimateMotion (src/viso_mono.cpp:41-160), pure host math.
  *
  * Threading: an engine is not re-entrant; different engines are independent (one CUDA stream
  * each, or a caller-supplied stream).
@@ -196,6 +197,40 @@ vo_status vo_slot_dump_features(vo_engine* e, int32_t slot, int32_t* max2, int32
                                 int32_t cap_stride);
 /* number of features in a slot (sum of max2_num) -- for the algorithmic-bytes formula */
 vo_status vo_slot_feature_count(vo_engine* e, int32_t slot, int32_t* n);
+
+/* ---------------------------------------------------------------------------------------- */
+/* 4. host stage F2: monocular egomotion from a bucketed match list (no engine, no GPU)        */
+/* ---------------------------------------------------------------------------------------- */
+
+/* VisualOdometryMono::parameters, src/viso_mono.h:32-46 + VisualOdometry::calibration, src/viso.h:56-64 */
+typedef struct vo_mono_params {
+  double f, cu, cv;          /* calibration: focal length, principal point (pixels) */
+  double height, pitch;      /* camera height above ground (m) and pitch (rad); reference defaults 1.0 / 0.0 */
+  int32_t ransac_iters;      /* 2000 */
+  int32_t reserved;
+  double inlier_threshold;   /* 1e-5 (Sampson distance in normalised coordinates) */
+  double motion_threshold;   /* 100.0 */
+} vo_mono_params;
+
+typedef struct vo_egomotion vo_egomotion;
+
+/* Owns the RANSAC sample stream: bit-identical to glibc's rand() after srand(seed), which is what the
+ * reference uses (VisualOdometry::VisualOdometry calls srand(0), src/viso.cpp:34; getRandomSample,
+ * src/viso.cpp:86-106), but private to the handle.  threads: host threads scoring RANSAC hypotheses
+ * (0 = min(hardware threads, 16)); the result does not depend on it. */
+vo_status vo_egomotion_create(uint32_t seed, int32_t threads, vo_egomotion** out);
+void      vo_egomotion_destroy(vo_egomotion* eg);
+/* VisualOdometryMono::estimateMotion(p_matched): src/viso_mono.cpp:41-160.  tr_delta = {rx,ry,rz,tx,ty,tz};
+ * *ok = 0 where the reference returns an empty vector (process() == false): fewer than 10 matches or
+ * inliers, degenerate normalisation, too little motion. */
+vo_status vo_estimate_motion_mono(vo_egomotion* eg, const vo_p_match* matches, int32_t n,
+                                  const vo_mono_params* prm, double tr_delta[6], int32_t* ok);
+/* VisualOdometry::getInlierIndices / getNumberOfInliers: src/viso.h:96-99 (out may be NULL) */
+vo_status vo_egomotion_inliers(const vo_egomotion* eg, int32_t* out, int32_t cap, int32_t* n);
+/* next value of the handle's sample stream (== glibc rand()); test hook */
+uint32_t  vo_egomotion_rand(vo_egomotion* eg);
+/* VisualOdometry::transformationVectorToMatrix: src/viso.cpp:59-84; Tr is a row-major 4x4 */
+void      vo_transformation_vector_to_matrix(const double tr[6], double Tr[16]);
 
 /* ---------------------------------------------------------------------------------------- */
 /* instrumentation                                                                           */

@@ -155,3 +155,18 @@ class RefMatcher:
         max2, num = self.ref.new_feature_arrays()
         self.ref.lib.ref_matcher_dump_features(self.h, C.c_int(which), _p(max2), _p(num))
         return max2, num
+
+
+def mono_motion_seq(ref: "RefLib", lists, f, cu, cv, height=1.0, pitch=0.0, ransac_iters=2000, inlier_threshold=1e-5,
+                    motion_threshold=100.0):
+    """VisualOdometryMono::estimateMotion (/root/reference/src/viso_mono.cpp:41) on a sequence of match lists
+    processed by ONE reference object (srand(0) once, rand() stream carried over).  Returns (tr[n,6], ok[n], n_inliers[n])."""
+    lists = [np.ascontiguousarray(m, dtype=P_MATCH_DTYPE) for m in lists]
+    counts = np.array([len(m) for m in lists], dtype=np.int32)
+    flat = np.concatenate(lists) if lists else np.zeros(0, dtype=P_MATCH_DTYPE)
+    prm = np.array([f, cu, cv, height, pitch, ransac_iters, inlier_threshold, motion_threshold], dtype=np.float64)
+    tr = np.zeros((len(lists), 6), dtype=np.float64)
+    ok = np.zeros(len(lists), dtype=np.int32)
+    ninl = np.zeros(len(lists), dtype=np.int32)
+    ref.lib.ref_mono_motion_seq(_p(flat), _p(counts), C.c_int32(len(lists)), _p(prm), _p(tr), _p(ok), _p(ninl))
+    return tr, ok, ninl

@@ -12,12 +12,16 @@
 //   myMatching          /root/reference/src/myMatch.cpp:122
 //   removeOutliers      /root/reference/src/remove_outliers.cpp:4
 //   Matcher::*          /root/reference/src/matcher.cpp:32-187
+//   VisualOdometryMono::estimateMotion   /root/reference/src/viso_mono.cpp:41  (row F2, host egomotion)
 // The reference keeps multi-megabyte arrays on the stack, so every call is executed on a
 // helper thread with a 1 GiB stack; std::cout chatter of the reference is muted.
 
-#define private public      // reach Matcher::p_matched_2 / max2c for the parity dumps
+#define private public      // reach Matcher::p_matched_2 / max2c for the parity dumps, VisualOdometryMono::estimateMotion
+#define protected public
 #include "matcher.h"
+#include "viso_mono.h"
 #undef private
+#undef protected
 
 #include <pthread.h>
 #include <functional>
@@ -148,5 +152,34 @@ void ref_matcher_dump_features(void* h, int which, int32_t* max2, int32_t* max2_
   std::memcpy(max2, which ? m->max2c : m->max2p, 4 * size_t(MAX_FEATURE_ARRAY_SIZE));
   std::memcpy(max2_num, which ? m->max2c_num : m->max2p_num, 4 * size_t(BIN_NUM));
 }
+
+// ---- row F2: monocular egomotion on injected match lists -----------------------------------------
+// One VisualOdometryMono object (its constructor calls srand(0), src/viso.cpp:34) processes n_lists match
+// lists in order, so the glibc rand() stream carries over from list to list exactly as in a sequence.
+// prm = {f, cu, cv, height, pitch, ransac_iters, inlier_threshold, motion_threshold};
+// tr_out[6*i..] = estimateMotion's vector, ok[i] = 1 if it had 6 entries, n_inliers[i] = inliers.size().
+void ref_mono_motion_seq(const void* lists, const int32_t* counts, int32_t n_lists, const double* prm,
+                         double* tr_out, int32_t* ok, int32_t* n_inliers) {
+  on_big_stack([&] {
+    VisualOdometryMono::parameters p;
+    p.calib.f = prm[0]; p.calib.cu = prm[1]; p.calib.cv = prm[2];
+    p.height = prm[3]; p.pitch = prm[4];
+    p.ransac_iters = (int32_t)prm[5]; p.inlier_threshold = prm[6]; p.motion_threshold = prm[7];
+    VisualOdometryMono vo(p);
+    const Matcher::p_match* cur = (const Matcher::p_match*)lists;
+    for (int32_t i = 0; i < n_lists; i++) {
+      std::vector<Matcher::p_match> v(cur, cur + counts[i]);
+      cur += counts[i];
+      std::vector<double> tr = vo.estimateMotion(v);
+      ok[i] = tr.size() == 6 ? 1 : 0;
+      for (int k = 0; k < 6; k++) tr_out[6 * i + k] = ok[i] ? tr[k] : 0.0;
+      n_inliers[i] = (int32_t)vo.inliers.size();
+    }
+  });
+}
+
+// the C library generator the reference samples from (src/viso.cpp:98), for pinning our private copy
+void ref_srand(uint32_t seed) { srand(seed); }
+int32_t ref_rand() { return rand(); }
 
 }  // extern "C"
