@@ -53,7 +53,9 @@ EXPORTS = [
     "vo_batch_get_matches", "vo_batch_download_async", "vo_slot_dump_features", "vo_slot_feature_count",
     "vo_launch_count", "vo_profile_enable", "vo_profile_read", "vo_host_alloc", "vo_host_free",
     "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
-    "vo_egomotion_rand", "vo_transformation_vector_to_matrix",
+    "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
+    "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
+    "vo_pipeline_process",
 ]
 
 class VoMonoParams(C.Structure):  # vo_mono_params: /root/reference/src/viso_mono.h:32-46, src/viso.h:56-64
@@ -119,11 +121,18 @@ def load_library() -> C.CDLL:
         "vo_egomotion_inliers": [vp, vp, i32, C.POINTER(i32)],
         "vo_egomotion_rand": [vp],
         "vo_transformation_vector_to_matrix": [C.POINTER(C.c_double), C.POINTER(C.c_double)],
+        "vo_egomotion_draw_samples": [vp, vp, i32, C.POINTER(VoMonoParams), vp, C.POINTER(i32)],
+        "vo_estimate_motion_mono_samples": [vp, i32, C.POINTER(VoMonoParams), vp, i32, i32, C.POINTER(C.c_double), C.POINTER(i32),
+                                            vp, i32, C.POINTER(i32)],
+        "vo_batch_bucket_host": [vp, i32, vp, i64, vp, i32, f32, f32],
+        "vo_pipeline_create": [vp, C.POINTER(VoMonoParams), i32, f32, f32, i32, C.POINTER(vp)],
+        "vo_pipeline_destroy": [vp],
+        "vo_pipeline_process": [vp, i32, vp, i64, i32, vp, vp, vp, vp, vp, i64],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
         fn.argtypes = args
-        if name in ("vo_engine_destroy", "vo_egomotion_destroy", "vo_transformation_vector_to_matrix"):
+        if name in ("vo_engine_destroy", "vo_egomotion_destroy", "vo_transformation_vector_to_matrix", "vo_pipeline_destroy"):
             fn.restype = None
         elif name == "vo_egomotion_rand":
             fn.restype = C.c_uint32
@@ -491,3 +500,45 @@ class VisualOdometryMono:
 
     def getInlierIndices(self):
         return self.ego.inliers()
+
+
+class Pipeline:
+    """Sequence level (vo_pipeline_*): VisualOdometryMono::process for batches of consecutive frames of one
+    sequence -- GPU extraction/matching/bucketing of the whole batch, host Delaunay filter and egomotion of all
+    pairs on a thread pool; per-frame results equal frame-by-frame process() (/root/reference/src/viso_mono.cpp:33-39)."""
+
+    def __init__(self, width: int, height: int, batch: int, f=1.0, cu=0.0, cv=0.0, cam_height=1.0, pitch=0.0, ransac_iters=2000,
+                 inlier_threshold=1e-5, motion_threshold=100.0, max_features=2, bucket_w=50.0, bucket_h=50.0,
+                 host_threads: int = 0, device: int = 0):
+        self.engine = Engine(width, height, max_frames=batch + 1, max_pairs=batch, device=device)
+        self.lib = self.engine.lib
+        self.batch = batch
+        self.prm = VoMonoParams(f=f, cu=cu, cv=cv, height=cam_height, pitch=pitch, ransac_iters=ransac_iters,
+                                inlier_threshold=inlier_threshold, motion_threshold=motion_threshold)
+        h = C.c_void_p()
+        st = self.lib.vo_pipeline_create(self.engine.h, C.byref(self.prm), max_features, bucket_w, bucket_h, host_threads, C.byref(h))
+        if st != VO_OK:
+            raise VoError(st, "vo_pipeline_create")
+        self.h = h
+        self.cap = (int(width / bucket_w) + 2) * (int(height / bucket_h) + 2) * max_features
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vo_pipeline_destroy(self.h)
+            self.h = None
+            self.engine.close()
+
+    def process(self, frames: np.ndarray, want_matches: bool = False):
+        """frames: (n, H, pitch>=W) uint8, n <= batch.  -> ok[n], tr[n,6], n_matches[n], n_inliers[n] (, lists)."""
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        n = frames.shape[0]
+        ok = np.zeros(n, np.int32); tr = np.zeros((n, 6), np.float64)
+        nm = np.zeros(n, np.int32); ni = np.zeros(n, np.int32)
+        lists = np.zeros((n, self.cap), dtype=P_MATCH_DTYPE) if want_matches else None
+        st = self.lib.vo_pipeline_process(self.h, n, _ptr(frames), frames.strides[0], frames.strides[1], _ptr(ok), _ptr(tr),
+                                          _ptr(nm), _ptr(ni), _ptr(lists), self.cap)
+        if st != VO_OK:
+            raise VoError(st, self.lib.vo_last_error().decode() or "vo_pipeline_process")
+        if want_matches:
+            return ok, tr, nm, ni, [lists[i, : nm[i]].copy() for i in range(n)]
+        return ok, tr, nm, ni

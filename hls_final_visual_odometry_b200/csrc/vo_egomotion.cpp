@@ -342,23 +342,31 @@ void draw_sample(GlibcRand& rng, int32_t N, std::vector<int32_t>& pool, int32_t 
   }
 }
 
-// src/viso_mono.cpp:41-160.  Returns false where the reference returns an empty vector.
-bool estimate_motion(vo_egomotion* eg, const vo_p_match* matches, int32_t N, const vo_mono_params& prm, double tr[6]) {
-  eg->inliers.clear();  // the reference clears its inlier list only after normalisation (:62); callers never look at it on failure
+// Does a match list reach the RANSAC loop of estimateMotion (N >= 10 and a non-degenerate normalisation,
+// src/viso_mono.cpp:45-56)?  Only then does the reference consume rand() values: 8 per iteration.
+bool prepare_points(const vo_p_match* matches, int32_t N, std::vector<Pt>& raw, std::vector<Pt>& p, double Tp[9], double Tc[9]) {
   if (N < 10) return false;
-  std::vector<Pt> raw(N), p;
+  raw.resize(N);
   for (int32_t i = 0; i < N; i++) raw[i] = Pt{matches[i].u1p, matches[i].v1p, matches[i].u1c, matches[i].v1c};
   p = raw;
+  return normalize_points(p, Tp, Tc);
+}
+
+// src/viso_mono.cpp:41-160 with the RANSAC sample sets given (8 indices per iteration, in the order the
+// reference draws them).  Stateless.  Returns false where the reference returns an empty vector.
+bool estimate_motion(const vo_p_match* matches, int32_t N, const vo_mono_params& prm, const int32_t* samples_in, int iters,
+                     int threads, std::vector<int32_t>& inliers, double tr[6]) {
+  inliers.clear();
+  std::vector<Pt> raw, p;
   const double K[9] = {prm.f, 0, prm.cu, 0, prm.f, prm.cv, 0, 0, 1};
   double Tp[9], Tc[9];
-  if (!normalize_points(p, Tp, Tc)) return false;
+  if (!prepare_points(matches, N, raw, p, Tp, Tc)) return false;
+  struct EgView { std::vector<int32_t>& inliers; int threads; } view{inliers, threads};
+  EgView* eg = &view;
+  const int32_t* samples = samples_in;
 
-  // ---- RANSAC: the sample stream is drawn sequentially (it is the reference's rand() stream); the
-  //      hypotheses are independent, so they are scored by a pool of threads; the winner is the FIRST
-  //      hypothesis with the largest inlier count == the sequential `if (curr.size() > best.size())`.
-  const int iters = std::max(0, prm.ransac_iters);
-  std::vector<int32_t> samples((size_t)iters * 8), pool;
-  for (int k = 0; k < iters; k++) draw_sample(eg->rng, N, pool, &samples[(size_t)k * 8]);
+  // ---- RANSAC: the hypotheses are independent, so they are scored by a pool of threads; the winner is
+  //      the FIRST hypothesis with the largest inlier count == the sequential `if (curr.size() > best.size())`.
   std::vector<int32_t> counts(iters, 0);
   auto score = [&](int k0, int k1) {
     std::vector<double> A, G;
@@ -460,10 +468,44 @@ vo_status vo_egomotion_create(uint32_t seed, int32_t threads, vo_egomotion** out
 
 void vo_egomotion_destroy(vo_egomotion* eg) { delete eg; }
 
+// Draws the sample sets the reference would draw for this match list (advancing the handle's stream) --
+// nothing if the list never reaches RANSAC.  samples: int32[ransac_iters * 8]; *n_iters = iterations drawn.
+vo_status vo_egomotion_draw_samples(vo_egomotion* eg, const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
+                                    int32_t* samples, int32_t* n_iters) {
+  if (!eg || !prm || !samples || !n_iters || n < 0 || (n > 0 && !matches)) return VO_ERR_INVALID;
+  std::vector<Pt> raw, p;
+  double Tp[9], Tc[9];
+  *n_iters = 0;
+  if (!prepare_points(matches, n, raw, p, Tp, Tc)) return VO_OK;
+  const int iters = std::max(0, prm->ransac_iters);
+  std::vector<int32_t> pool;
+  for (int k = 0; k < iters; k++) draw_sample(eg->rng, n, pool, samples + (size_t)k * 8);
+  *n_iters = iters;
+  return VO_OK;
+}
+
+vo_status vo_estimate_motion_mono_samples(const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
+                                          const int32_t* samples, int32_t n_iters, int32_t threads, double tr_delta[6],
+                                          int32_t* ok, int32_t* inliers, int32_t inliers_cap, int32_t* n_inliers) {
+  if (!prm || !tr_delta || !ok || n < 0 || (n > 0 && !matches) || n_iters < 0 || (n_iters > 0 && !samples)) return VO_ERR_INVALID;
+  std::vector<int32_t> inl;
+  *ok = estimate_motion(matches, n, *prm, samples, n_iters, std::max(1, threads), inl, tr_delta) ? 1 : 0;
+  if (n_inliers) *n_inliers = (int32_t)inl.size();
+  if (inliers) {
+    if (inliers_cap < (int32_t)inl.size()) return VO_ERR_CAPACITY;
+    std::memcpy(inliers, inl.data(), sizeof(int32_t) * inl.size());
+  }
+  return VO_OK;
+}
+
 vo_status vo_estimate_motion_mono(vo_egomotion* eg, const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
                                   double tr_delta[6], int32_t* ok) {
   if (!eg || !prm || !tr_delta || !ok || n < 0 || (n > 0 && !matches)) return VO_ERR_INVALID;
-  *ok = estimate_motion(eg, matches, n, *prm, tr_delta) ? 1 : 0;
+  std::vector<int32_t> samples((size_t)std::max(0, prm->ransac_iters) * 8);
+  int32_t iters = 0;
+  vo_status st = vo_egomotion_draw_samples(eg, matches, n, prm, samples.data(), &iters);
+  if (st != VO_OK) return st;
+  *ok = estimate_motion(matches, n, *prm, samples.data(), iters, eg->threads, eg->inliers, tr_delta) ? 1 : 0;
   return VO_OK;
 }
 

@@ -739,6 +739,36 @@ vo_status vo_batch_match(vo_engine* e, int32_t n_pairs, const int32_t* prev_slot
   return do_match(e, 0, n_pairs, max_features, bucket_w, bucket_h);
 }
 
+vo_status vo_batch_bucket_host(vo_engine* e, int32_t n_pairs, const vo_p_match* lists, int64_t stride_matches,
+                               const int32_t* counts, int32_t max_features, float bucket_w, float bucket_h) {
+  if (!e || !lists || !counts) return fail(VO_ERR_INVALID, "null argument");
+  if (n_pairs < 1 || n_pairs > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "n_pairs %d outside [1,%d]", n_pairs, e->cfg.max_pairs);
+  if (max_features < 1 || !(bucket_w > 0.f) || !(bucket_h > 0.f)) return fail(VO_ERR_INVALID, "bad bucketing parameters");
+  CU_TRY(cudaSetDevice(e->device));
+  if (e->d2h_pending) {  // the pair buffers may still be downloading
+    CU_TRY(cudaStreamWaitEvent(e->stream, e->ev_d2h_done, 0));
+    e->d2h_pending = false;
+  }
+  for (int i = 0; i < n_pairs; i++) {
+    if (counts[i] < 0 || counts[i] > e->cfg.max_matches || counts[i] > stride_matches)
+      return fail(VO_ERR_CAPACITY, "pair %d: %d matches > capacity", i, counts[i]);
+    if (counts[i] > 0)
+      CU_TRY(cudaMemcpyAsync(e->d_raw + (int64_t)i * e->cfg.max_matches, lists + (int64_t)i * stride_matches,
+                             sizeof(vo_p_match) * (size_t)counts[i], cudaMemcpyHostToDevice, e->stream));
+  }
+  CU_TRY(cudaMemcpyAsync(e->d_n_raw, counts, 4 * (size_t)n_pairs, cudaMemcpyHostToDevice, e->stream));
+  {
+    Scope sc(e, F_BUCKET);
+    CU_TRY(vo::launch_k4(e->d_raw, e->cfg.max_matches, e->d_n_raw, n_pairs, max_features, bucket_w, bucket_h, e->d_lfsr,
+                         kLfsrLen, e->d_scratch, e->scratch_stride, kNbMax, kQCap, e->d_bucketed, e->cfg.max_matches,
+                         e->cfg.max_matches, e->d_n_bucketed, e->d_status, e->stream));
+    e->launches += 1;
+  }
+  e->last_batch_pairs = n_pairs;
+  e->cur_which = 1;
+  return VO_OK;
+}
+
 vo_status vo_batch_counts(vo_engine* e, int32_t n_pairs, int32_t* raw, int32_t* bucketed) {
   if (!e || n_pairs < 1 || n_pairs > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "bad argument");
   CU_TRY(cudaSetDevice(e->device));

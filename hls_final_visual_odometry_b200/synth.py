@@ -123,3 +123,76 @@ def make_scene_matches(n_lists: int, seed: int = 0, width: int = 1241, height: i
         lists.append(m)
         motions.append([rx, ry, rz, t[0], t[1], t[2]])
     return lists, np.array(motions)
+
+
+# ------------------------------------------------------------------------------------------------
+# Rendered 3-D sequence (BASELINE.json config 3, "full process() loop"): a textured corridor -- ground
+# plane, two side walls, an end wall -- seen by a forward-moving camera.  Three orthogonal planes make the
+# epipolar geometry well conditioned, so the reference's mono egomotion succeeds on these frames (it fails
+# on the pure-translation crops above).  Integer-only texture, float ray casting with fixed evaluation
+# order: frames are reproducible across hosts to the last bit in practice, but the committed goldens of
+# the hot path do NOT depend on this generator.
+# ------------------------------------------------------------------------------------------------
+def _noise_texture(size: int, seed: int, blur_passes: int = 10, contrast: int = 45) -> np.ndarray:
+    rng = np.random.default_rng(seed)
+    x = rng.integers(0, 256, size=(size, size), dtype=np.int64)
+    for _ in range(blur_passes):
+        rows = np.roll(x, 1, 1) + x + np.roll(x, -1, 1)
+        x = np.roll(rows, 1, 0) + rows + np.roll(rows, -1, 0)
+    shift = max(0, int(x.max()).bit_length() - 20)
+    x = x >> shift
+    mean = int(x.sum()) // x.size
+    d = x - mean
+    std = max(1, math.isqrt(int((d * d).sum()) // x.size))
+    return np.clip(128 + (d * contrast) // std, 0, 255).astype(np.uint8)
+
+
+def make_corridor_sequence(width: int = 1241, height: int = 376, n_frames: int = 8, seed: int = 0, step: float = 0.6,
+                           calib=None, cam_height: float = KITTI_HEIGHT, half_width: float = 6.0, yaw_amp: float = 0.01,
+                           tex_size: int = 1024, levels: int = 6, texel_px: float = 2.0):
+    """-> (frames uint8 (n, height, width), poses (n, 4, 4) camera-to-world).  The camera drives along +z, `step`
+    metres per frame, with a slow sinusoidal yaw; y points down (ground at y = +cam_height)."""
+    calib = calib or KITTI_CALIB
+    f, cu, cv = calib["f"], calib["cu"], calib["cv"]
+    tex = np.stack([_noise_texture(tex_size, seed * 1000 + 10 * lv + s) for lv in range(levels) for s in range(4)]).astype(np.float64)
+    uu, vv = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    rays_c = np.stack([(uu - cu) / f, (vv - cv) / f, np.ones_like(uu)], -1)      # camera frame
+    base_texel = texel_px * 10.0 / f                                                 # one texel ~ texel_px pixels at 10 m
+    wall_h_top = -8.0                                                                # walls reach 8 m above the camera
+    frames, poses = [], []
+    for k in range(n_frames):
+        yaw = yaw_amp * math.sin(0.35 * k)
+        R = _rot(0.0, yaw, 0.0)                                                      # camera-to-world rotation
+        c = np.array([0.3 * math.sin(0.2 * k), 0.0, step * k])                       # camera centre in the world
+        d = rays_c @ R.T
+        big = 1e9
+        with np.errstate(divide="ignore", invalid="ignore"):
+            tg = np.where(d[..., 1] > 1e-9, (cam_height - c[1]) / d[..., 1], big)                   # ground y = cam_height
+            tl = np.where(d[..., 0] < -1e-9, (-half_width - c[0]) / d[..., 0], big)                 # left wall
+            tr = np.where(d[..., 0] > 1e-9, (half_width - c[0]) / d[..., 0], big)                   # right wall
+            zend = step * n_frames + 80.0
+            te = np.where(d[..., 2] > 1e-9, (zend - c[2]) / d[..., 2], big)                         # end wall
+        t = np.minimum(np.minimum(tg, tl), np.minimum(tr, te))
+        which = np.where(t == tg, 0, np.where(t == tl, 1, np.where(t == tr, 2, 3)))
+        P = c + d * t[..., None]
+        depth = t * (d @ R[:, 2])                                                    # distance along the optical axis
+        lv = np.clip(np.floor(np.log2(np.maximum(depth, 1e-3) / 10.0) + 0.5).astype(np.int64), 0, levels - 1)
+        texel = base_texel * (2.0 ** lv)
+        a = np.where(which == 0, P[..., 0], np.where(which == 3, P[..., 0], P[..., 1]))              # texture axes per surface
+        b = np.where(which == 3, P[..., 1], P[..., 2])
+        fa, fb = a / texel, b / texel                                                # bilinear texture lookup
+        a0, b0 = np.floor(fa), np.floor(fb)
+        wa, wb = fa - a0, fb - b0
+        ia, ib = a0.astype(np.int64) % tex_size, b0.astype(np.int64) % tex_size
+        ia1, ib1 = (ia + 1) % tex_size, (ib + 1) % tex_size
+        ls = lv * 4 + which
+        val = ((1 - wa) * (1 - wb) * tex[ls, ib, ia] + wa * (1 - wb) * tex[ls, ib, ia1] +
+               (1 - wa) * wb * tex[ls, ib1, ia] + wa * wb * tex[ls, ib1, ia1])
+        img = np.clip(np.floor(val + 0.5), 0, 255).astype(np.uint8)
+        sky = (which != 0) & (P[..., 1] < wall_h_top)
+        img[sky] = 128
+        frames.append(img)
+        T = np.eye(4)
+        T[:3, :3], T[:3, 3] = R, c
+        poses.append(T)
+    return np.stack(frames), np.stack(poses)

@@ -182,6 +182,12 @@ vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n,
 vo_status vo_batch_match(vo_engine* e, int32_t n_pairs, const int32_t* prev_slot,
                          const int32_t* curr_slot, int32_t max_features, float bucket_w,
                          float bucket_h);
+/* Replace the raw lists of pairs 0..n_pairs-1 by host lists (lists + i*stride_matches, counts[i] entries; e.g. the
+ * raw lists after the host-side removeOutliers, src/matcher.cpp:108) and bucket them (src/matcher.cpp:140-187) in one
+ * launch.  The host buffers must stay valid until a later fence / synchronize.  Results: vo_batch_counts /
+ * vo_batch_get_matches / vo_batch_download_async with which = 1. */
+vo_status vo_batch_bucket_host(vo_engine* e, int32_t n_pairs, const vo_p_match* lists, int64_t stride_matches,
+                               const int32_t* counts, int32_t max_features, float bucket_w, float bucket_h);
 /* Counts of the last vo_batch_match: raw[i], bucketed[i] (either may be NULL). Synchronises. */
 vo_status vo_batch_counts(vo_engine* e, int32_t n_pairs, int32_t* raw, int32_t* bucketed);
 /* Copy pair i's raw (which=0) or bucketed (which=1) list to the host. Synchronises. */
@@ -225,12 +231,44 @@ void      vo_egomotion_destroy(vo_egomotion* eg);
  * inliers, degenerate normalisation, too little motion. */
 vo_status vo_estimate_motion_mono(vo_egomotion* eg, const vo_p_match* matches, int32_t n,
                                   const vo_mono_params* prm, double tr_delta[6], int32_t* ok);
+/* The same in two steps, for callers that estimate many frame pairs in parallel and still want the reference's
+ * results: the reference's rand() stream runs through the frames of a sequence in order, so the sample sets are
+ * DRAWN in frame order (cheap) and the estimation itself is stateless and may run on any thread.
+ * samples: int32[ransac_iters * 8]; *n_iters = 0 if the list never reaches RANSAC (the reference then consumes
+ * no random numbers either). */
+vo_status vo_egomotion_draw_samples(vo_egomotion* eg, const vo_p_match* matches, int32_t n,
+                                    const vo_mono_params* prm, int32_t* samples, int32_t* n_iters);
+vo_status vo_estimate_motion_mono_samples(const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
+                                          const int32_t* samples, int32_t n_iters, int32_t threads,
+                                          double tr_delta[6], int32_t* ok, int32_t* inliers,
+                                          int32_t inliers_cap, int32_t* n_inliers);
 /* VisualOdometry::getInlierIndices / getNumberOfInliers: src/viso.h:96-99 (out may be NULL) */
 vo_status vo_egomotion_inliers(const vo_egomotion* eg, int32_t* out, int32_t cap, int32_t* n);
 /* next value of the handle's sample stream (== glibc rand()); test hook */
 uint32_t  vo_egomotion_rand(vo_egomotion* eg);
 /* VisualOdometry::transformationVectorToMatrix: src/viso.cpp:59-84; Tr is a row-major 4x4 */
 void      vo_transformation_vector_to_matrix(const double tr[6], double Tr[16]);
+
+/* ---------------------------------------------------------------------------------------- */
+/* 5. sequence level: VisualOdometryMono::process for a batch of consecutive frames           */
+/* ---------------------------------------------------------------------------------------- */
+
+/* process() (src/viso_mono.cpp:33-39) of up to max_pairs consecutive frames of ONE sequence per call, scheduled as
+ * a pipeline (what the reference's FPGA host does by hand, hls_opencl/host/main2.cpp:395-519): GPU extraction +
+ * circular matching of the whole batch, host removeOutliers of all pairs on `host_threads` threads, GPU bucketing
+ * of all pairs in one launch, RANSAC sample sets drawn in frame order from the sequence's rand() stream, host
+ * egomotion of all pairs on the threads.  Per-frame results equal those of process() called frame by frame.
+ * The engine needs max_frames >= max_pairs + 1 and must not be used for anything else meanwhile. */
+typedef struct vo_pipeline vo_pipeline;
+vo_status vo_pipeline_create(vo_engine* e, const vo_mono_params* prm, int32_t max_features, float bucket_w,
+                             float bucket_h, int32_t host_threads /* 0 = all */, vo_pipeline** out);
+void      vo_pipeline_destroy(vo_pipeline* p);
+/* frames at images + i*frame_stride_bytes (host), rows pitch_bytes apart.  Outputs per frame i: ok[i] = process()
+ * result, tr_delta[6*i..6*i+5] valid when ok[i], n_matches[i] (after bucketing), n_inliers[i]; matches_out
+ * (may be NULL): the bucketed list of frame i at matches_out + i*matches_stride. */
+vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, int64_t frame_stride_bytes,
+                              int32_t pitch_bytes, int32_t* ok, double* tr_delta, int32_t* n_matches,
+                              int32_t* n_inliers, vo_p_match* matches_out, int64_t matches_stride);
 
 /* ---------------------------------------------------------------------------------------- */
 /* instrumentation                                                                           */
