@@ -183,13 +183,17 @@ def test_cpp_shim_demo(tmp_path):
         seq[f].tofile(str(tmp_path / f"I1_{f:06d}.dat"))
     out = subprocess.run([build.DEMO, str(tmp_path), str(w), str(h), str(n)], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0, out.stderr
-    counts = [int(l.split("Matches:")[1].split(",")[0]) for l in out.stdout.splitlines() if "Matches:" in l]
+    import re
+    counts = [int(re.search(r"Matches: (\d+)", l).group(1)) for l in out.stdout.splitlines() if "Matches:" in l]
+    # process() = pushBack -> matchFeatures (GPU matching + host removeOutliers) -> bucketFeatures(2, 50, 50):
+    # src/viso_mono.cpp:33-39; expected counts from the oracle's matching + bucketing around the host filter
+    from hls_final_visual_odometry_b200.api import remove_outliers_host
     orc = Oracle(w, h)
     feats = [orc.compute_features(seq[f])[:2] for f in range(n)]
     want = [0]
     for f in range(1, n):
         raw, _ = orc.matching(feats[f - 1][0], feats[f - 1][1], feats[f][0], feats[f][1])
-        want.append(len(orc.bucket_features(raw, 2, 50.0, 50.0)))
+        want.append(len(orc.bucket_features(remove_outliers_host(raw), 2, 50.0, 50.0)))
     assert counts == want
     assert "mean flow: -3 -1" in out.stdout
 
