@@ -33,7 +33,8 @@ class VoConfig(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bin_w", C.c_int32), ("bin_h", C.c_int32),
                 ("nms_tau", C.c_int32), ("max_frames", C.c_int32), ("max_pairs", C.c_int32),
                 ("max_matches", C.c_int32), ("match_rows_per_cta", C.c_int32), ("match_exhaustive", C.c_int32),
-                ("match_threads", C.c_int32), ("reserved", C.c_int32 * 5)]
+                ("match_threads", C.c_int32), ("stereo", C.c_int32), ("match_disp_tolerance", C.c_int32),
+                ("reserved", C.c_int32 * 3)]
 
 
 class VoGeometry(C.Structure):
@@ -55,7 +56,7 @@ EXPORTS = [
     "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
     "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
-    "vo_pipeline_process",
+    "vo_pipeline_process", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
 ]
 
 class VoMonoParams(C.Structure):  # vo_mono_params: /root/reference/src/viso_mono.h:32-46, src/viso.h:56-64
@@ -128,6 +129,10 @@ def load_library() -> C.CDLL:
         "vo_pipeline_create": [vp, C.POINTER(VoMonoParams), i32, f32, f32, i32, C.POINTER(vp)],
         "vo_pipeline_destroy": [vp],
         "vo_pipeline_process": [vp, i32, vp, i64, i32, vp, vp, vp, vp, vp, i64],
+        "vo_batch_match_quad": [vp, i32, vp, vp, vp, vp, i32, i32, i32, f32, f32],
+        "vo_batch_refine": [vp, i32],
+        "vo_refine_matches": [vp],
+        "vo_profile_read_ext": [vp, C.POINTER(C.c_double), C.POINTER(i64), i32],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -155,12 +160,15 @@ class Engine:
 
     def __init__(self, width: int, height: int, max_frames: int = 2, max_pairs: int = 1, device: int = 0,
                  stream: int | None = None, max_matches: int = 0, match_rows_per_cta: int = 0, nms_tau: int = 0,
-                 bin_w: int = 0, bin_h: int = 0, match_exhaustive: bool = False, match_threads: int = 0):
+                 bin_w: int = 0, bin_h: int = 0, match_exhaustive: bool = False, match_threads: int = 0,
+                 stereo: bool = False, match_disp_tolerance: int = 0):
         self.lib = load_library()
+        if stereo:
+            max_frames = max(max_frames, 4)  # left and right prev/curr ring
         cfg = VoConfig(width=width, height=height, bin_w=bin_w, bin_h=bin_h, nms_tau=nms_tau,
                        max_frames=max_frames, max_pairs=max_pairs, max_matches=max_matches,
                        match_rows_per_cta=match_rows_per_cta, match_exhaustive=int(match_exhaustive),
-                       match_threads=match_threads)
+                       match_threads=match_threads, stereo=int(stereo), match_disp_tolerance=match_disp_tolerance)
         h = C.c_void_p()
         self.h = None
         self._check(self.lib.vo_engine_create(C.byref(cfg), device, C.c_void_p(stream or 0), C.byref(h)))
@@ -228,6 +236,9 @@ class Engine:
     # ---- Matcher level -------------------------------------------------------------------
     def push_back(self, img: np.ndarray, replace: bool = False, img2=None):
         img = np.ascontiguousarray(img, dtype=np.uint8)
+        if img2 is not None:
+            img2 = np.ascontiguousarray(img2, dtype=np.uint8)
+            assert img2.shape == img.shape and img2.strides == img.strides
         dims = (C.c_int32 * 3)(img.shape[1], img.shape[0], img.strides[0])
         self._check(self.lib.vo_push_back(self.h, _ptr(img), _ptr(img2), dims, int(replace)))
 
@@ -237,6 +248,10 @@ class Engine:
     def remove_outliers(self):
         """The removeOutliers call of Matcher::matchFeatures (src/matcher.cpp:108) on the current raw list."""
         self._check(self.lib.vo_remove_outliers(self.h))
+
+    def refine_matches(self):
+        """EXTENSION (row F3): sub-pixel refinement of the current list (parameters::refinement == 2)."""
+        self._check(self.lib.vo_refine_matches(self.h))
 
     def bucket_features(self, max_features=2, bw=50.0, bh=50.0):
         self._check(self.lib.vo_bucket_features(self.h, max_features, bw, bh))
@@ -278,6 +293,15 @@ class Engine:
         cu = np.ascontiguousarray(curr_slots, dtype=np.int32)
         self._check(self.lib.vo_batch_match(self.h, len(pv), _ptr(pv), _ptr(cu), max_features, bw, bh))
 
+    def batch_match_quad(self, s1p, s2p, s1c, s2c, disp_tolerance=2, refinement=0, max_features=0, bw=50.0, bh=50.0):
+        """EXTENSION (row F3): quad matching of stereo frame pairs; slots of left/right x prev/curr per item."""
+        a = [np.ascontiguousarray(x, dtype=np.int32) for x in (s1p, s2p, s1c, s2c)]
+        self._check(self.lib.vo_batch_match_quad(self.h, len(a[0]), _ptr(a[0]), _ptr(a[1]), _ptr(a[2]), _ptr(a[3]),
+                                                 disp_tolerance, refinement, max_features, bw, bh))
+
+    def batch_refine(self, n_items: int):
+        self._check(self.lib.vo_batch_refine(self.h, n_items))
+
     def batch_counts(self, n_pairs: int):
         raw = np.zeros(n_pairs, np.int32)
         bk = np.zeros(n_pairs, np.int32)
@@ -318,6 +342,13 @@ class Engine:
         calls = (C.c_int64 * 4)()
         self._check(self.lib.vo_profile_read(self.h, ms, calls, int(reset)))
         names = ("extract", "match", "emit", "bucket")
+        return {k: (ms[i], calls[i]) for i, k in enumerate(names)}
+
+    def profile_read_ext(self, reset: bool = True):
+        ms = (C.c_double * 8)()
+        calls = (C.c_int64 * 8)()
+        self._check(self.lib.vo_profile_read_ext(self.h, ms, calls, int(reset)))
+        names = ("extract", "match", "emit", "bucket", "refine")
         return {k: (ms[i], calls[i]) for i, k in enumerate(names)}
 
 

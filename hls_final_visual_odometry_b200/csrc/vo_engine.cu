@@ -20,8 +20,14 @@ cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t*
                         int cap_stride, int32_t* overflow, cudaStream_t st);
 cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
                         int cap_stride, cudaStream_t st);
-cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
+cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
                       int rows_per_group, int prune, int threads, cudaStream_t st);
+cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* quads, const int2* pairs, int n_items,
+                           const uint32_t* best, uint8_t* flags, int32_t* list_cnt, uint32_t* qxy, void* out,
+                           int64_t out_stride_matches, int32_t max_matches, int32_t* n_raw, int32_t* status,
+                           cudaStream_t st);
+cudaError_t launch_k5(const Geom& g, const FrameArrays& fa, const int4* quads, int n_items, void* lists,
+                      int64_t stride_matches, int32_t max_n, int32_t* n_list, uint8_t* keep, cudaStream_t st);
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
                       uint8_t* flags, int32_t* list_cnt, void* out, int64_t out_stride_matches, int32_t max_matches,
                       int32_t* n_raw, int32_t* status, cudaStream_t st);
@@ -56,7 +62,8 @@ constexpr int kLfsrLen = 1 << 18;
 constexpr int kNbMax = 4096;   // buckets per list supported by K4
 constexpr int kQCap = 16384;   // kept matches per list supported by K4
 
-enum Family { F_EXTRACT = 0, F_MATCH = 1, F_EMIT = 2, F_BUCKET = 3 };
+enum Family { F_EXTRACT = 0, F_MATCH = 1, F_EMIT = 2, F_BUCKET = 3, F_REFINE = 4, F_FAMILIES = 8 };
+constexpr int kFlowReach = 1 << 10;  // row reach of a flow edge: no restriction beyond the reference's vb +- 3
 
 }  // namespace
 
@@ -80,6 +87,17 @@ struct vo_engine {
   // pair buffers
   int2* d_pairs = nullptr;
   int2* h_pairs = nullptr;              // pinned
+  int epi = 2;                          // K2 edges (and `best` arrays) per pair buffer: 2, or 4 on a stereo engine
+  int4* d_edges = nullptr;              // [n_pairbuf * epi] {origin slot, target slot, rad_v, row reach}
+  int4* h_edges = nullptr;              // pinned
+  int4* d_quads = nullptr;              // [n_pairbuf] {1p, 2p, 1c, 2c} slots of the last match call (2p = 2c = -1: flow)
+  int4* h_quads = nullptr;              // pinned
+  uint32_t* d_qxy = nullptr;            // stereo engines: partner coordinates per current-left feature (k3q_flags)
+  uint8_t* d_keep = nullptr;            // refinement: keep flag per match
+  std::vector<uint8_t> slot_has_image;  // frame bytes resident in the slot (not when extraction read caller memory in place)
+  int ring_r_prev = 2, ring_r_curr = 3; // stereo engines: right-image ring
+  int right_pushed = 0;
+  bool last_was_quad = false;
   uint32_t* d_best = nullptr;
   uint8_t* d_flags = nullptr;
   int32_t* d_list_cnt = nullptr;
@@ -107,8 +125,8 @@ struct vo_engine {
   struct Ev { cudaEvent_t a, b; int fam; };
   std::vector<Ev> evs;
   size_t ev_used = 0;
-  double prof_ms[4] = {0, 0, 0, 0};
-  int64_t prof_calls[4] = {0, 0, 0, 0};
+  double prof_ms[F_FAMILIES] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int64_t prof_calls[F_FAMILIES] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 namespace {
@@ -210,6 +228,7 @@ vo_status upload_images(vo_engine* e, int first_slot, int n, const uint8_t* imag
                         cudaMemcpyKind kind, cudaStream_t st = nullptr) {
   if (!st) st = e->stream;
   const vo::Geom& g = e->g;
+  for (int i = 0; i < n; i++) e->slot_has_image[first_slot + i] = 1;
   uint8_t* dst = e->fa.img + (int64_t)first_slot * e->fa.img_stride;
   if (pitch == g.pitch && frame_stride == e->fa.img_stride) {
     // caller's layout == slot layout (16-byte row pitch): one linear copy at full link speed; the
@@ -233,8 +252,9 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
   }
   {
     Scope sc(e, F_MATCH);
-    CU_TRY(vo::launch_k2(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
-                         e->rows_per_group, e->prune, e->match_threads, e->stream));
+    CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)pair0 * 2, 2 * n_pairs,
+                         e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap, e->rows_per_group, e->prune,
+                         e->match_threads, e->stream));
     e->launches += 1;
   }
   {
@@ -261,8 +281,96 @@ vo_status set_pairs(vo_engine* e, int pair0, int n, const int32_t* prev, const i
     if (prev[i] < 0 || prev[i] >= e->n_slots || curr[i] < 0 || curr[i] >= e->n_slots)
       return fail(VO_ERR_INVALID, "pair %d: slot out of range", i);
     e->h_pairs[pair0 + i] = make_int2(prev[i], curr[i]);
+    // the two searches of myMatching (src/myMatch.cpp:148-176): curr -> prev, prev -> curr, both with the flow window
+    e->h_edges[2 * (pair0 + i)] = make_int4(curr[i], prev[i], e->g.rad_v, kFlowReach);
+    e->h_edges[2 * (pair0 + i) + 1] = make_int4(prev[i], curr[i], e->g.rad_v, kFlowReach);
+    e->h_quads[pair0 + i] = make_int4(prev[i], -1, curr[i], -1);
   }
   CU_TRY(cudaMemcpyAsync(e->d_pairs + pair0, e->h_pairs + pair0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_edges + 2 * pair0, e->h_edges + 2 * pair0, sizeof(int4) * 2 * n, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_quads + pair0, e->h_quads + pair0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->stream));
+  e->last_was_quad = false;
+  return VO_OK;
+}
+
+// EXTENSION (row F3): sub-pixel refinement of the raw lists of items [item0, item0 + n) in place
+vo_status do_refine(vo_engine* e, int item0, int n_items, int32_t max_n) {
+  for (int i = 0; i < n_items; i++) {
+    const int4 q = e->h_quads[item0 + i];
+    for (int s : {q.x, q.y, q.z, q.w})
+      if (s >= 0 && !e->slot_has_image[s])
+        return fail(VO_ERR_STATE, "refinement needs the frame of slot %d resident in the engine (it was extracted in place "
+                    "from caller memory by vo_batch_extract_device)", s);
+  }
+  if (!e->d_keep) {
+    cudaError_t ce = cudaMalloc((void**)&e->d_keep, (size_t)e->n_pairbuf * e->cfg.max_matches);
+    if (ce != cudaSuccess) return fail(VO_ERR_CUDA, "cudaMalloc(keep flags): %s", cudaGetErrorString(ce));
+  }
+  Scope sc(e, F_REFINE);
+  CU_TRY(vo::launch_k5(e->g, e->fa, e->d_quads + item0, n_items, e->d_raw + (int64_t)item0 * e->cfg.max_matches,
+                       e->cfg.max_matches, max_n, e->d_n_raw + item0, e->d_keep + (int64_t)item0 * e->cfg.max_matches,
+                       e->stream));
+  e->launches += 2;
+  return VO_OK;
+}
+
+// EXTENSION (row F3): quad matching of items [item0, item0 + n): four K2 edges, cycle + emit, optional refinement
+// and bucketing.  h_quads/h_pairs/h_edges of the items must be set (set_quads).
+vo_status do_match_quad(vo_engine* e, int item0, int n_items, int refinement, int max_features, float bw, float bh) {
+  const vo::Geom& g = e->g;
+  if (e->d2h_pending) {
+    CU_TRY(cudaStreamWaitEvent(e->stream, e->ev_d2h_done, 0));
+    e->d2h_pending = false;
+  }
+  const int64_t lists = (int64_t)g.U * 4 * g.col_cap;
+  {
+    Scope sc(e, F_MATCH);
+    CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)item0 * 4, 4 * n_items, e->d_best + (int64_t)item0 * 4 * lists,
+                         e->rows_per_group, e->prune, e->match_threads, e->stream));
+    e->launches += 1;
+  }
+  {
+    Scope sc(e, F_EMIT);
+    CU_TRY(vo::launch_k3_quad(g, e->fa, e->d_quads + item0, e->d_pairs + item0, n_items, e->d_best + (int64_t)item0 * 4 * lists,
+                              e->d_flags + (int64_t)item0 * lists, e->d_list_cnt + (int64_t)item0 * g.U * 4,
+                              e->d_qxy + (int64_t)item0 * lists * 3, e->d_raw + (int64_t)item0 * e->cfg.max_matches,
+                              e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + item0, e->d_status, e->stream));
+    e->launches += 2;
+  }
+  if (refinement == 2) {
+    vo_status s = do_refine(e, item0, n_items, e->cfg.max_matches);
+    if (s != VO_OK) return s;
+  }
+  if (max_features > 0) {
+    Scope sc(e, F_BUCKET);
+    CU_TRY(vo::launch_k4(e->d_raw + (int64_t)item0 * e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + item0, n_items,
+                         max_features, bw, bh, e->d_lfsr, kLfsrLen, e->d_scratch + (int64_t)item0 * e->scratch_stride,
+                         e->scratch_stride, kNbMax, kQCap, e->d_bucketed + (int64_t)item0 * e->cfg.max_matches,
+                         e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + item0, e->d_status, e->stream));
+    e->launches += 1;
+  }
+  return VO_OK;
+}
+
+vo_status set_quads(vo_engine* e, int item0, int n, const int32_t* s1p, const int32_t* s2p, const int32_t* s1c,
+                    const int32_t* s2c, int disp_tolerance) {
+  if (e->epi != 4) return fail(VO_ERR_STATE, "quad matching needs an engine created with vo_config.stereo = 1");
+  if (disp_tolerance < 0 || disp_tolerance > 16) return fail(VO_ERR_INVALID, "match_disp_tolerance %d outside [0,16]", disp_tolerance);
+  for (int i = 0; i < n; i++) {
+    for (int s : {s1p[i], s2p[i], s1c[i], s2c[i]})
+      if (s < 0 || s >= e->n_slots) return fail(VO_ERR_INVALID, "item %d: slot out of range", i);
+    const int k = item0 + i;
+    e->h_quads[k] = make_int4(s1p[i], s2p[i], s1c[i], s2c[i]);
+    e->h_pairs[k] = make_int2(s1p[i], s1c[i]);
+    e->h_edges[4 * k + 0] = make_int4(s1c[i], s1p[i], e->g.rad_v, kFlowReach);  // flow   1c -> 1p
+    e->h_edges[4 * k + 1] = make_int4(s1p[i], s2p[i], disp_tolerance, 1);       // stereo 1p -> 2p
+    e->h_edges[4 * k + 2] = make_int4(s2p[i], s2c[i], e->g.rad_v, kFlowReach);  // flow   2p -> 2c
+    e->h_edges[4 * k + 3] = make_int4(s2c[i], s1c[i], disp_tolerance, 1);       // stereo 2c -> 1c
+  }
+  CU_TRY(cudaMemcpyAsync(e->d_pairs + item0, e->h_pairs + item0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_edges + 4 * item0, e->h_edges + 4 * item0, sizeof(int4) * 4 * n, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_quads + item0, e->h_quads + item0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->stream));
+  e->last_was_quad = true;
   return VO_OK;
 }
 
@@ -289,7 +397,10 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   if (cfg.bin_w == 0) cfg.bin_w = 60;
   if (cfg.bin_h == 0) cfg.bin_h = 45;
   if (cfg.nms_tau == 0) cfg.nms_tau = 50;
-  if (cfg.max_frames == 0) cfg.max_frames = 2;
+  if (cfg.match_disp_tolerance == 0) cfg.match_disp_tolerance = 2;  // src/matcher.h:64
+  if (cfg.max_frames == 0) cfg.max_frames = cfg.stereo ? 4 : 2;
+  if (cfg.stereo != 0 && cfg.stereo != 1) return fail(VO_ERR_INVALID, "vo_config.stereo must be 0 or 1");
+  if (cfg.stereo && cfg.max_frames < 4) return fail(VO_ERR_INVALID, "a stereo engine needs max_frames >= 4 (left and right prev/curr)");
   if (cfg.max_pairs == 0) cfg.max_pairs = 1;
   if (cfg.width < 128 || cfg.height < 64 || cfg.width > 16384 || cfg.height > 16384)
     return fail(VO_ERR_INVALID, "image size %dx%d outside [128..16384]x[64..16384]", cfg.width, cfg.height);
@@ -337,6 +448,8 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   // (2048x1024: V = 23; measured 8.7k -> 9.7k pairs/s), so that a CTA's candidate window fits one staging chunk
   e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : (g.V <= 12 ? g.V : 8);
   e->prune = cfg.match_exhaustive ? 0 : 1;
+  e->epi = cfg.stereo ? 4 : 2;
+  e->slot_has_image.assign((size_t)e->n_slots, 0);
   e->match_threads = cfg.match_threads;
 
   if (stream) { e->stream = (cudaStream_t)stream; e->own_stream = false; }
@@ -374,7 +487,10 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   cudaMemsetAsync(e->fa.img, 0, (size_t)(S * e->fa.img_stride + 256), e->stream);
   const int64_t lists = (int64_t)g.U * 4 * g.col_cap;
   ALLOC(e->d_pairs, sizeof(int2) * P);
-  ALLOC(e->d_best, sizeof(uint32_t) * P * 2 * lists);
+  ALLOC(e->d_best, sizeof(uint32_t) * P * e->epi * lists);
+  ALLOC(e->d_edges, sizeof(int4) * P * e->epi);
+  ALLOC(e->d_quads, sizeof(int4) * P);
+  if (cfg.stereo) ALLOC(e->d_qxy, sizeof(uint32_t) * 3 * P * lists);
   ALLOC(e->d_flags, (size_t)(P * lists));
   ALLOC(e->d_list_cnt, sizeof(int32_t) * P * g.U * 4);
   ALLOC(e->d_raw, sizeof(vo_p_match) * P * cfg.max_matches);
@@ -386,7 +502,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   cudaMemsetAsync(e->d_n_raw, 0, sizeof(int32_t) * P, e->stream);
   cudaMemsetAsync(e->d_n_bucketed, 0, sizeof(int32_t) * P, e->stream);
   cudaMemsetAsync(e->d_status, 0, sizeof(int32_t), e->stream);
-  cudaMemsetAsync(e->d_best, 0xFF, sizeof(uint32_t) * P * 2 * lists, e->stream);
+  cudaMemsetAsync(e->d_best, 0xFF, sizeof(uint32_t) * P * e->epi * lists, e->stream);
   e->scratch_stride = vo::k4_scratch_ints_host(kNbMax, kQCap);
   ALLOC(e->d_scratch, sizeof(int32_t) * P * e->scratch_stride);
   ALLOC(e->d_lfsr, sizeof(uint32_t) * kLfsrLen);
@@ -399,7 +515,9 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
       return fail(VO_ERR_CUDA, "lfsr upload");
     }
   }
-  if (cudaMallocHost((void**)&e->h_pairs, sizeof(int2) * P) != cudaSuccess ||
+  if (cudaMallocHost((void**)&e->h_edges, sizeof(int4) * P * e->epi) != cudaSuccess ||
+      cudaMallocHost((void**)&e->h_quads, sizeof(int4) * P) != cudaSuccess ||
+      cudaMallocHost((void**)&e->h_pairs, sizeof(int2) * P) != cudaSuccess ||
       cudaMallocHost((void**)&e->h_counts, sizeof(int32_t) * (2 * P + 4)) != cudaSuccess) {
     vo_engine_destroy(e);
     return fail(VO_ERR_CUDA, "pinned alloc");
@@ -424,6 +542,9 @@ void vo_engine_destroy(vo_engine* e) {
   cudaFree(e->d_pairs); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
   cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);
+  cudaFree(e->d_edges); cudaFree(e->d_quads); cudaFree(e->d_qxy); cudaFree(e->d_keep);
+  if (e->h_edges) cudaFreeHost(e->h_edges);
+  if (e->h_quads) cudaFreeHost(e->h_quads);
   if (e->h_pairs) cudaFreeHost(e->h_pairs);
   if (e->h_counts) cudaFreeHost(e->h_counts);
   for (auto& ev : e->evs) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
@@ -573,7 +694,8 @@ vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, in
 // ---------------------------------------------------------------------------------------------
 
 vo_status vo_push_back(vo_engine* e, const uint8_t* I1, const uint8_t* I2, const int32_t dims[3], int32_t replace) {
-  (void)I2;  // ignored, as in the reference (src/matcher.cpp:51-91 never reads I2)
+  // I2: ignored, as in the reference (src/matcher.cpp:51-91 never reads I2), unless the engine was created with
+  // vo_config.stereo = 1 (extension): then the right frame goes through the same extraction
   if (!e || !dims) return fail(VO_ERR_INVALID, "null argument");
   const int32_t width = dims[0], height = dims[1], bpl = dims[2];
   if (width <= 0 || height <= 0 || bpl < width || I1 == nullptr)
@@ -591,19 +713,48 @@ vo_status vo_push_back(vo_engine* e, const uint8_t* I1, const uint8_t* I2, const
   if (s != VO_OK) return s;
   s = do_extract(e, e->tmap_slots, e->ring_curr, e->ring_curr, 1);
   if (s != VO_OK) return s;
+  if (e->cfg.stereo) {
+    if (I2) {
+      if (!replace) {
+        const int t = e->ring_r_prev; e->ring_r_prev = e->ring_r_curr; e->ring_r_curr = t;
+        e->right_pushed += 1;
+      } else if (e->right_pushed == 0) {
+        e->right_pushed = 1;
+      }
+      s = upload_images(e, e->ring_r_curr, 1, I2, (int64_t)bpl * height, bpl, cudaMemcpyHostToDevice);
+      if (s != VO_OK) return s;
+      s = do_extract(e, e->tmap_slots, e->ring_r_curr, e->ring_r_curr, 1);
+      if (s != VO_OK) return s;
+    } else if (!replace) {
+      e->right_pushed = 0;  // a mono frame breaks the right-image history
+    }
+  }
   // the caller's image is borrowed only for the duration of the call
   CU_TRY(cudaStreamSynchronize(e->stream));
   return VO_OK;
 }
 
 vo_status vo_match_features(vo_engine* e, int32_t method) {
-  (void)method;  // ignored, as in the reference (src/matcher.cpp:93-111)
+  // `method` is ignored, as in the reference (src/matcher.cpp:93-111: always the flow matcher), except on a stereo
+  // engine, where method 2 runs the quad matcher once two stereo frames have been pushed (extension, row F3)
   if (!e) return fail(VO_ERR_INVALID, "null engine");
   CU_TRY(cudaSetDevice(e->device));
   e->cur_which = 0;
   if (e->frames_pushed < 2) {  // frame-0 contract: zero matches
     CU_TRY(cudaMemsetAsync(e->d_n_raw + 0, 0, 4, e->stream));
     return VO_OK;
+  }
+  if (e->cfg.stereo && method == 2) {
+    if (e->right_pushed < 2) {
+      CU_TRY(cudaMemsetAsync(e->d_n_raw + 0, 0, 4, e->stream));
+      return VO_OK;
+    }
+    const int32_t s1p = e->ring_prev, s2p = e->ring_r_prev, s1c = e->ring_curr, s2c = e->ring_r_curr;
+    vo_status s = set_quads(e, 0, 1, &s1p, &s2p, &s1c, &s2c, e->cfg.match_disp_tolerance);
+    if (s != VO_OK) return s;
+    s = do_match_quad(e, 0, 1, 0, 0, 0.f, 0.f);
+    if (s != VO_OK) return s;
+    return check_device_status(e);
   }
   int32_t pv = e->ring_prev, cu = e->ring_curr;
   vo_status s = set_pairs(e, 0, 1, &pv, &cu);
@@ -721,6 +872,7 @@ vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n, c
     CUtensorMap tm;
     vo_status s = make_tmap(&tm, d_images, e->g.W, e->g.H, n, pitch_bytes, frame_stride_bytes);
     if (s != VO_OK) return s;
+    for (int i = 0; i < n; i++) e->slot_has_image[first_slot + i] = 0;  // the slots hold features only
     return do_extract(e, tm, first_slot, 0, n);
   }
   vo_status s = upload_images(e, first_slot, n, d_images, frame_stride_bytes, pitch_bytes, cudaMemcpyDeviceToDevice);
@@ -739,6 +891,40 @@ vo_status vo_batch_match(vo_engine* e, int32_t n_pairs, const int32_t* prev_slot
   e->last_batch_pairs = n_pairs;
   e->cur_which = max_features > 0 ? 1 : 0;
   return do_match(e, 0, n_pairs, max_features, bucket_w, bucket_h);
+}
+
+vo_status vo_batch_match_quad(vo_engine* e, int32_t n_items, const int32_t* slot_1p, const int32_t* slot_2p,
+                              const int32_t* slot_1c, const int32_t* slot_2c, int32_t disp_tolerance, int32_t refinement,
+                              int32_t max_features, float bucket_w, float bucket_h) {
+  if (!e || !slot_1p || !slot_2p || !slot_1c || !slot_2c) return fail(VO_ERR_INVALID, "null argument");
+  if (n_items < 1 || n_items > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "n_items %d outside [1,%d]", n_items, e->cfg.max_pairs);
+  if (refinement != 0 && refinement != 2) return fail(VO_ERR_UNSUPPORTED, "refinement %d: 0 (none) or 2 (sub-pixel)", refinement);
+  if (max_features > 0 && (!(bucket_w > 0.f) || !(bucket_h > 0.f))) return fail(VO_ERR_INVALID, "bucket size must be positive");
+  CU_TRY(cudaSetDevice(e->device));
+  vo_status s = set_quads(e, 0, n_items, slot_1p, slot_2p, slot_1c, slot_2c, disp_tolerance);
+  if (s != VO_OK) return s;
+  e->last_batch_pairs = n_items;
+  e->cur_which = max_features > 0 ? 1 : 0;
+  return do_match_quad(e, 0, n_items, refinement, max_features, bucket_w, bucket_h);
+}
+
+vo_status vo_batch_refine(vo_engine* e, int32_t n_items) {
+  if (!e || n_items < 1 || n_items > e->cfg.max_pairs) return fail(VO_ERR_INVALID, "bad argument");
+  CU_TRY(cudaSetDevice(e->device));
+  return do_refine(e, 0, n_items, e->cfg.max_matches);
+}
+
+vo_status vo_refine_matches(vo_engine* e) {
+  if (!e) return fail(VO_ERR_INVALID, "null engine");
+  if (e->cur_which != 0) return fail(VO_ERR_STATE, "refinement runs on the match list before bucketing");
+  if (e->frames_pushed < 2) return VO_OK;
+  CU_TRY(cudaSetDevice(e->device));
+  int32_t n = 0;
+  vo_status s = vo_num_matches(e, &n);
+  if (s != VO_OK || n == 0) return s;
+  s = do_refine(e, 0, 1, n);
+  if (s != VO_OK) return s;
+  return check_device_status(e);
 }
 
 vo_status vo_batch_bucket_host(vo_engine* e, int32_t n_pairs, const vo_p_match* lists, int64_t stride_matches,
@@ -862,7 +1048,16 @@ vo_status vo_profile_read(vo_engine* e, double ms[4], int64_t calls[4], int32_t 
   CU_TRY(cudaStreamSynchronize(e->stream));
   drain_events(e);
   for (int i = 0; i < 4; i++) { ms[i] = e->prof_ms[i]; calls[i] = e->prof_calls[i]; }
-  if (reset) for (int i = 0; i < 4; i++) { e->prof_ms[i] = 0; e->prof_calls[i] = 0; }
+  if (reset) for (int i = 0; i < F_FAMILIES; i++) { e->prof_ms[i] = 0; e->prof_calls[i] = 0; }
+  return VO_OK;
+}
+
+vo_status vo_profile_read_ext(vo_engine* e, double ms[8], int64_t calls[8], int32_t reset) {
+  if (!e || !ms || !calls) return fail(VO_ERR_INVALID, "null argument");
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  drain_events(e);
+  for (int i = 0; i < F_FAMILIES; i++) { ms[i] = e->prof_ms[i]; calls[i] = e->prof_calls[i]; }
+  if (reset) for (int i = 0; i < F_FAMILIES; i++) { e->prof_ms[i] = 0; e->prof_calls[i] = 0; }
   return VO_OK;
 }
 

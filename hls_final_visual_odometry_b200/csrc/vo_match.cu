@@ -116,7 +116,7 @@ __device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 template <bool PRUNE, int THREADS>
 __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
                                            uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
-                                           int rows_per_group) {
+                                           int rows_per_group, int rad_v, int reach) {
   constexpr int NW = THREADS / 32;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   K2Tables& t = S.t;
@@ -173,11 +173,14 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     if (n > 0) {  // rows any origin of this group can see: vb is non-decreasing along the column list
       int v_first = r0;
       while (t.prefO[cc][v_first + 1] <= ob) v_first++;
-      row_lo = min(row_lo, max(origin_vb(t, cc, ob, v_first) - 3, 0));
+      row_lo = min(row_lo, max(max(origin_vb(t, cc, ob, v_first) - 3, v_first - reach), 0));
     }
   }
   if (ntasks == 0) return true;
-  const int row_hi = min(r1 + 3, V - 1);  // exclusive: src/myMatch.cpp:93,99
+  // exclusive: src/myMatch.cpp:93,99.  `reach` (>= V on flow edges: no restriction) narrows the rows of a
+  // left<->right edge to those that can hold a candidate inside its +-rad_v window: a bin row spans 45 block
+  // rows, so |dv| <= rad_v <= 16 keeps the candidate's row within +-1 of the origin's own row
+  const int row_hi = min(min(r1 + 3, V - 1), r1 + reach);
   if (noc > 1)
     for (int v = row_lo; v < row_hi; v++)
       if (t.rowTot[v] > kCandCap) return false;
@@ -261,7 +264,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         qa = __ldg(&q_from[rec]);
         // lagging v_bin (src/myMatch.cpp:153-158): only the first origins after empty bins
         const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
-        const int lo_r = max(max(vb - 3, 0), ra), hi_r = min(min(vb + 3, V - 1), rb);  // src/myMatch.cpp:92-93,99
+        const int lo_r = max(max(max(vb - 3, 0), ra), v - reach);  // src/myMatch.cpp:92-93,99
+        const int hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
         if (lo_r < hi_r) { vlo = lo_r; vhi = hi_r; }
         if (!first_chunk) {
           bestk = bo[o];
@@ -270,8 +274,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       }
       const int rlo = __reduce_min_sync(FULL, vlo), rhi = __reduce_max_sync(FULL, vhi);
       const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
-      const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
-      const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
+      const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
+      const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
 
       if (PRUNE) {
         // seed: the candidate with the smallest lower bound among the bins the origins themselves
@@ -431,10 +435,10 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const uint4 a = __ldg(&desc_from[2 * rec]), b = __ldg(&desc_from[2 * rec + 1]);
         const uint32_t qa = __ldg(&q_from[rec]);
         const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
-        const int lo_r = max(max(vb - 3, 0), ra), hi_r = min(min(vb + 3, V - 1), rb);
+        const int lo_r = max(max(max(vb - 3, 0), ra), v - reach), hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
         const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
-        const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - g.rad_v, 0) << 16);
-        const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + g.rad_v + 1) << 16);
+        const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);
+        const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
         uint32_t bk = kNone;
         if (!first_chunk) {  // result of the earlier chunks
           const uint32_t prev = bo[o];
@@ -470,21 +474,22 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 
 template <bool PRUNE, int THREADS>
 __global__ void __launch_bounds__(THREADS, 2)
-k2_match(Geom g, FrameArrays fa, const int2* __restrict__ pairs, uint32_t* __restrict__ best, int rows_per_group,
+k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best, int rows_per_group,
          int ngroups) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   K2Smem& S = *reinterpret_cast<K2Smem*>(smem_raw);
   const int cg = blockIdx.x / ngroups, grp = blockIdx.x - cg * ngroups;
-  const int c = blockIdx.y >> 1, dir = blockIdx.y & 1;
-  const int2 pr = pairs[blockIdx.z];  // x = prev slot, y = curr slot
-  const int from_slot = dir ? pr.x : pr.y, to_slot = dir ? pr.y : pr.x;
+  const int c = blockIdx.y >> 1;
+  const int edge = blockIdx.z * 2 + (blockIdx.y & 1);
+  const int4 ed = edges[edge];  // x = origin slot, y = target slot, z = rad_v, w = row reach (MatchEdge)
+  const int from_slot = ed.x, to_slot = ed.y;
   const int ub0 = cg * kOC;
   const int noc = min(kOC, (g.U - 1) - ub0);  // origin columns 0..U-2 only (src/myMatch.cpp:141-146)
-  uint32_t* best_dir = best + (int64_t)(blockIdx.z * 2 + dir) * g.U * 4 * g.col_cap;
+  uint32_t* best_dir = best + (int64_t)edge * g.U * 4 * g.col_cap;
   // joint pass over both columns; if a row of the shared window does not fit, one pass per column
   for (int it = -1;;) {
     const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
-                                               it < 0 ? noc : 1, grp, rows_per_group);
+                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w);
     if (it < 0 && ok) break;
     if (++it >= noc) break;
   }
@@ -564,12 +569,121 @@ k3_flags(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t*
   }
 }
 
+// ---- EXTENSION (parity unpinned: absent from the reference; oracle = oracle/vo_oracle.c
+// vo_oracle_quad_matching) -- quad cycle 1c -> 1p -> 2p -> 2c -> 1c over four K2 edges ---------------------------
+// coordinates of feature (u_bin, class, col_idx) of a slot: walk the column's v-bin counts
+__device__ __forceinline__ uint32_t feature_xy(const Geom& g, const FrameArrays& fa, int slot, int u, int c, int k) {
+  const int32_t* cnt = fa.cnt + (int64_t)slot * fa.cnt_stride;
+  int v = 0, rem = k;
+  for (; v < g.V - 1; v++) {
+    const int nn = cnt[(v * g.U + u) * 4 + c];
+    if (rem < nn) break;
+    rem -= nn;
+  }
+  return fa.xy[(int64_t)slot * fa.rec_stride + (int64_t)((v * g.U + u) * 4 + c) * g.cap + rem];
+}
+
+// one hop of the cycle: best target of origin (ou, k) on an edge, false if none
+__device__ __forceinline__ bool hop(const uint32_t* __restrict__ best_e, int col_cap, int c, int ou, int ok, int& tu, int& tk) {
+  const uint32_t key = best_e[(int64_t)(ou * 4 + c) * col_cap + ok];
+  if (key == kNone) return false;
+  decode_key(key, ou, tu, tk);
+  return true;
+}
+
+// K3q: per current-left column u: does the cycle close with non-negative disparities (libviso2's quad rule)?
+// then the reference's same-pixel dedupe (lowest class wins) and the per-(u,class) counts, as k3_flags.
+__global__ void __launch_bounds__(K3_THREADS)
+k3q_flags(Geom g, FrameArrays fa, const int4* __restrict__ quads, const uint32_t* __restrict__ best,
+          uint8_t* __restrict__ flags, int32_t* __restrict__ list_cnt, uint32_t* __restrict__ qxy) {
+  __shared__ int32_t pref[4][kMaxV + 1];
+  __shared__ int32_t warp_cnt[K3_THREADS / 32];
+  const int u = blockIdx.x, item = blockIdx.y, tid = threadIdx.x;
+  const int U = g.U, V = g.V;
+  const int4 qd = quads[item];  // x = 1p, y = 2p, z = 1c, w = 2c
+  const int32_t* cnt = fa.cnt + (int64_t)qd.z * fa.cnt_stride;
+  if (tid < 4) {
+    int acc = 0;
+    pref[tid][0] = 0;
+    for (int v = 0; v < V; v++) { acc += cnt[(v * U + u) * 4 + tid]; pref[tid][v + 1] = acc; }
+  }
+  __syncthreads();
+  const int64_t L = (int64_t)U * 4 * g.col_cap;
+  const uint32_t* e0 = best + ((int64_t)item * 4 + 0) * L;  // 1c -> 1p (flow)
+  const uint32_t* e1 = best + ((int64_t)item * 4 + 1) * L;  // 1p -> 2p (stereo)
+  const uint32_t* e2 = best + ((int64_t)item * 4 + 2) * L;  // 2p -> 2c (flow)
+  const uint32_t* e3 = best + ((int64_t)item * 4 + 3) * L;  // 2c -> 1c (stereo)
+  const uint32_t* xy_c = fa.xy + (int64_t)qd.z * fa.rec_stride;
+  const uint32_t* meta = fa.meta + (int64_t)qd.z * fa.rec_stride;
+  uint8_t* fl = flags + (int64_t)item * L;
+  uint32_t* qx = qxy + (int64_t)item * L * 3;
+  if (u < U - 1) {  // the last column is never an origin (src/myMatch.cpp:141-146)
+    for (int c = 0; c < 4; c++) {
+      const int n = pref[c][V];
+      for (int k = tid; k < n; k += K3_THREADS) {
+        int au, ak, bu, bk, du, dk, su, sk;
+        bool ok = hop(e0, g.col_cap, c, u, k, au, ak) && hop(e1, g.col_cap, c, au, ak, bu, bk) &&
+                  hop(e2, g.col_cap, c, bu, bk, du, dk) && hop(e3, g.col_cap, c, du, dk, su, sk) && su == u && sk == k;
+        if (ok) {
+          int v = 0;
+          while (pref[c][v + 1] <= k) v++;
+          const uint32_t x1c = xy_c[(int64_t)((v * U + u) * 4 + c) * g.cap + (k - pref[c][v])];
+          const uint32_t x1p = feature_xy(g, fa, qd.x, au, c, ak), x2p = feature_xy(g, fa, qd.y, bu, c, bk);
+          const uint32_t x2c = feature_xy(g, fa, qd.w, du, c, dk);
+          ok = (x1p & 0xFFFFu) >= (x2p & 0xFFFFu) && (x1c & 0xFFFFu) >= (x2c & 0xFFFFu);  // u1p >= u2p, u1c >= u2c
+          if (ok) {
+            uint32_t* q3 = qx + ((int64_t)(u * 4 + c) * g.col_cap + k) * 3;
+            q3[0] = x1p; q3[1] = x2p; q3[2] = x2c;
+          }
+        }
+        fl[(int64_t)(u * 4 + c) * g.col_cap + k] = ok ? 1 : 0;
+      }
+    }
+  }
+  __syncthreads();
+  if (u < U - 1) {  // a lower class already claimed this current pixel (M[][] of src/myMatch.cpp:188-191)
+    for (int c = 2; c < 4; c++) {
+      const int n = pref[c][V];
+      for (int k = tid; k < n; k += K3_THREADS) {
+        uint8_t* f = &fl[(int64_t)(u * 4 + c) * g.col_cap + k];
+        if (!*f) continue;
+        int v = 0;
+        while (pref[c][v + 1] <= k) v++;
+        const uint32_t tw = meta[(int64_t)((v * U + u) * 4 + c) * g.cap + (k - pref[c][v])];
+        if (tw != kNone) {
+          const int tc = (int)(tw >> 16), tk = pref[tc][v] + (int)(tw & 0xFFFFu);
+          if (fl[(int64_t)(u * 4 + tc) * g.col_cap + tk]) *f = 0;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = 0; c < 4; c++) {
+    const int n = pref[c][V];
+    int mine = 0;
+    if (u < U - 1)
+      for (int k = tid; k < n; k += K3_THREADS) mine += fl[(int64_t)(u * 4 + c) * g.col_cap + k];
+    for (int d = 16; d > 0; d >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d);
+    if ((tid & 31) == 0) warp_cnt[tid >> 5] = mine;
+    __syncthreads();
+    if (tid == 0) {
+      int tot = 0;
+      for (int w = 0; w < K3_THREADS / 32; w++) tot += warp_cnt[w];
+      list_cnt[(int64_t)item * U * 4 + u * 4 + c] = tot;
+    }
+    __syncthreads();
+  }
+}
+
 // K3b: ordered emit.  One CTA per (u,class) list; its output offset is the sum of the counts of
 // all lists before it in (u_bin, class) order (src/myMatch.cpp:181-196).
+// QUAD: the partners' coordinates come from the qxy scratch k3q_flags filled ({1p, 2p, 2c} per current-left feature).
+template <bool QUAD>
 __global__ void __launch_bounds__(K3_THREADS)
 k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* __restrict__ best,
-        const uint8_t* __restrict__ flags, const int32_t* __restrict__ list_cnt, uint4* __restrict__ out,
-        int64_t out_stride_matches, int32_t max_matches, int32_t* __restrict__ n_raw, int32_t* __restrict__ status) {
+        const uint8_t* __restrict__ flags, const int32_t* __restrict__ list_cnt, const uint32_t* __restrict__ qxy,
+        uint4* __restrict__ out, int64_t out_stride_matches, int32_t max_matches, int32_t* __restrict__ n_raw,
+        int32_t* __restrict__ status) {
   __shared__ int32_t pref[kMaxV + 1];
   __shared__ int32_t warp_tot[K3_THREADS / 32];
   __shared__ int32_t s_off, s_total;
@@ -603,7 +717,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
   }
   if (lc[list] == 0) return;
   const int n = pref[V];
-  const uint32_t* best_cp = best + (int64_t)(pair * 2 + 0) * U * 4 * g.col_cap;
+  const uint32_t* best_cp = QUAD ? nullptr : best + (int64_t)(pair * 2 + 0) * U * 4 * g.col_cap;
   const uint8_t* fl = flags + ((int64_t)pair * U * 4 + list) * g.col_cap;
   const uint32_t* xy_c = fa.xy + (int64_t)pr.y * fa.rec_stride;
   const uint32_t* xy_p = fa.xy + (int64_t)pr.x * fa.rec_stride;
@@ -628,23 +742,33 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
       int v = 0;
       while (pref[v + 1] <= k) v++;
       const uint32_t cxy = xy_c[(int64_t)((v * U + u) * 4 + c) * g.cap + (k - pref[v])];
-      int pu, pk;
-      decode_key(best_cp[(int64_t)list * g.col_cap + k], u, pu, pk);
-      int pv = 0, rem = pk;
-      for (;; pv++) {  // locate the previous feature's (row, slot) from its col_idx
-        const int nn = cnt_p[(pv * U + pu) * 4 + c];
-        if (rem < nn) break;
-        rem -= nn;
-      }
-      const uint32_t pxy = xy_p[(int64_t)((pv * U + pu) * 4 + c) * g.cap + rem];
-      // p_match(u1p,v1p,-1,-1,-1,-1,u1c,v1c,-1,-1,-1,-1): src/myMatch.cpp:189
       const uint32_t m1f = __float_as_uint(-1.0f), m1i = 0xFFFFFFFFu;
-      const uint32_t u1p = __float_as_uint((float)(pxy & 0xFFFFu)), v1p = __float_as_uint((float)(pxy >> 16));
       const uint32_t u1c = __float_as_uint((float)(cxy & 0xFFFFu)), v1c = __float_as_uint((float)(cxy >> 16));
       uint4* rec = dst + (int64_t)posn * 3;
-      rec[0] = make_uint4(u1p, v1p, m1i, m1f);
-      rec[1] = make_uint4(m1f, m1i, u1c, v1c);
-      rec[2] = make_uint4(m1i, m1f, m1f, m1i);
+      if (QUAD) {
+        const uint32_t* qq = qxy + (((int64_t)pair * U * 4 + list) * g.col_cap + k) * 3;
+        const uint32_t x1p = qq[0], x2p = qq[1], x2c = qq[2];
+        // p_match(u1p,v1p,-1,u2p,v2p,-1,u1c,v1c,-1,u2c,v2c,-1): the fields of src/matcher.h:89-104, indices as src/myMatch.cpp:189
+        rec[0] = make_uint4(__float_as_uint((float)(x1p & 0xFFFFu)), __float_as_uint((float)(x1p >> 16)), m1i,
+                            __float_as_uint((float)(x2p & 0xFFFFu)));
+        rec[1] = make_uint4(__float_as_uint((float)(x2p >> 16)), m1i, u1c, v1c);
+        rec[2] = make_uint4(m1i, __float_as_uint((float)(x2c & 0xFFFFu)), __float_as_uint((float)(x2c >> 16)), m1i);
+      } else {
+        int pu, pk;
+        decode_key(best_cp[(int64_t)list * g.col_cap + k], u, pu, pk);
+        int pv = 0, rem = pk;
+        for (;; pv++) {  // locate the previous feature's (row, slot) from its col_idx
+          const int nn = cnt_p[(pv * U + pu) * 4 + c];
+          if (rem < nn) break;
+          rem -= nn;
+        }
+        const uint32_t pxy = xy_p[(int64_t)((pv * U + pu) * 4 + c) * g.cap + rem];
+        // p_match(u1p,v1p,-1,-1,-1,-1,u1c,v1c,-1,-1,-1,-1): src/myMatch.cpp:189
+        const uint32_t u1p = __float_as_uint((float)(pxy & 0xFFFFu)), v1p = __float_as_uint((float)(pxy >> 16));
+        rec[0] = make_uint4(u1p, v1p, m1i, m1f);
+        rec[1] = make_uint4(m1f, m1i, u1c, v1c);
+        rec[2] = make_uint4(m1i, m1f, m1f, m1i);
+      }
     }
     running += chunk_total;
     __syncthreads();
@@ -652,7 +776,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
 }
 
 template <bool PRUNE, int THREADS>
-static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
+static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
                                int rows_per_group, cudaStream_t st) {
   static bool attr_set = false;
   const int bytes = (int)sizeof(K2Smem);
@@ -663,17 +787,17 @@ static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int2*
   }
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   const int cgroups = (g.U - 1 + kOC - 1) / kOC;
-  dim3 grid(cgroups * ngroups, 8, n_pairs);
-  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, pairs, best, rows_per_group, ngroups);
+  dim3 grid(cgroups * ngroups, 8, n_edges / 2);  // edges come in twos (mono: curr->prev, prev->curr; quad: four)
+  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups);
   return cudaGetLastError();
 }
 
-cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, uint32_t* best,
+cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
                       int rows_per_group, int prune, int threads, cudaStream_t st) {
-  if (!prune) return launch_k2_t<false, 256>(g, fa, pairs, n_pairs, best, rows_per_group, st);
-  if (threads == 256) return launch_k2_t<true, 256>(g, fa, pairs, n_pairs, best, rows_per_group, st);
-  if (threads == 384) return launch_k2_t<true, 384>(g, fa, pairs, n_pairs, best, rows_per_group, st);
-  return launch_k2_t<true, 512>(g, fa, pairs, n_pairs, best, rows_per_group, st);
+  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, st);
+  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, st);
+  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, st);
+  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
@@ -682,8 +806,21 @@ cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, i
   k3_flags<<<dim3(g.U, n_pairs), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  k3_emit<<<dim3(g.U * 4, n_pairs), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt, (uint4*)out,
-                                                         out_stride_matches, max_matches, n_raw, status);
+  k3_emit<false><<<dim3(g.U * 4, n_pairs), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt, nullptr, (uint4*)out,
+                                                                out_stride_matches, max_matches, n_raw, status);
+  return cudaGetLastError();
+}
+
+// quad items: quads[i] = {1p, 2p, 1c, 2c} slots, pairs[i] = {1p, 1c} (for the shared emit), best = 4 edges per item
+cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* quads, const int2* pairs, int n_items,
+                           const uint32_t* best, uint8_t* flags, int32_t* list_cnt, uint32_t* qxy, void* out,
+                           int64_t out_stride_matches, int32_t max_matches, int32_t* n_raw, int32_t* status,
+                           cudaStream_t st) {
+  k3q_flags<<<dim3(g.U, n_items), K3_THREADS, 0, st>>>(g, fa, quads, best, flags, list_cnt, qxy);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  k3_emit<true><<<dim3(g.U * 4, n_items), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt, qxy, (uint4*)out,
+                                                               out_stride_matches, max_matches, n_raw, status);
   return cudaGetLastError();
 }
 

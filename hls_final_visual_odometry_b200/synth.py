@@ -58,6 +58,18 @@ def make_sequence(width: int, height: int, n_frames: int, seed: int = 0, blur_pa
     return np.stack([frame_from_canvas(canvas, width, height, f) for f in range(n_frames)])
 
 
+def make_stereo_sequence(width: int, height: int, n_frames: int, seed: int = 0, disparity=12, blur_passes: int = 10,
+                         contrast: int = 45):
+    """(left, right): two (n_frames, height, width) uint8 stacks of a rectified stereo rig looking at the translating
+    texture: right frame f is the same canvas cropped `disparity` pixels further right, so a feature at u in the left
+    image sits at u - disparity in the right one (disparity may be a per-frame sequence).  BASELINE.json config 4."""
+    canvas = make_canvas(width, height, seed, blur_passes, contrast)
+    d = [int(disparity)] * n_frames if np.isscalar(disparity) else [int(x) for x in disparity]
+    left = np.stack([frame_from_canvas(canvas, width, height, f) for f in range(n_frames)])
+    right = np.stack([frame_from_canvas(canvas, width, height, f, x0=16 + d[f]) for f in range(n_frames)])
+    return left, right
+
+
 # ------------------------------------------------------------------------------------------------
 # Match lists from a 3-D scene (SURVEY.md section 8 rows D1/F2): the blurred-noise sequence above is a pure
 # image translation (a planar, degenerate configuration for the 8-point algorithm: the reference's
@@ -149,9 +161,10 @@ def _noise_texture(size: int, seed: int, blur_passes: int = 10, contrast: int = 
 
 def make_corridor_sequence(width: int = 1241, height: int = 376, n_frames: int = 8, seed: int = 0, step: float = 0.6,
                            calib=None, cam_height: float = KITTI_HEIGHT, half_width: float = 6.0, yaw_amp: float = 0.01,
-                           tex_size: int = 1024, levels: int = 6, texel_px: float = 2.0):
+                           tex_size: int = 1024, levels: int = 6, texel_px: float = 2.0, cam_offset_x: float = 0.0):
     """-> (frames uint8 (n, height, width), poses (n, 4, 4) camera-to-world).  The camera drives along +z, `step`
-    metres per frame, with a slow sinusoidal yaw; y points down (ground at y = +cam_height)."""
+    metres per frame, with a slow sinusoidal yaw; y points down (ground at y = +cam_height).  cam_offset_x shifts the
+    camera centre along its own x axis (the right camera of a rectified rig: cam_offset_x = baseline)."""
     calib = calib or KITTI_CALIB
     f, cu, cv = calib["f"], calib["cu"], calib["cv"]
     tex = np.stack([_noise_texture(tex_size, seed * 1000 + 10 * lv + s) for lv in range(levels) for s in range(4)]).astype(np.float64)
@@ -163,7 +176,7 @@ def make_corridor_sequence(width: int = 1241, height: int = 376, n_frames: int =
     for k in range(n_frames):
         yaw = yaw_amp * math.sin(0.35 * k)
         R = _rot(0.0, yaw, 0.0)                                                      # camera-to-world rotation
-        c = np.array([0.3 * math.sin(0.2 * k), 0.0, step * k])                       # camera centre in the world
+        c = np.array([0.3 * math.sin(0.2 * k), 0.0, step * k]) + R[:, 0] * cam_offset_x  # camera centre in the world
         d = rays_c @ R.T
         big = 1e9
         with np.errstate(divide="ignore", invalid="ignore"):

@@ -68,7 +68,11 @@ typedef struct vo_config {
   int32_t match_exhaustive;   /* 0: exact lower-bound pruning in the SAD search (default); 1: evaluate every SAD.
                                  Results are bit-identical either way. */
   int32_t match_threads;      /* tuning: threads per matching CTA (256, 384 or 512; 0 = library default) */
-  int32_t reserved[5];
+  int32_t stereo;             /* EXTENSION (absent from the reference): 1 = keep a right-image ring
+                                 (vo_push_back extracts I2), vo_match_features(2) and vo_batch_match_quad run the
+                                 quad matcher.  0 (default) = the reference's behaviour: I2 and `method` are ignored. */
+  int32_t match_disp_tolerance; /* |dv| window of left<->right edges, src/matcher.h:51; 0 = the default 2 */
+  int32_t reserved[3];
 } vo_config;
 
 /* Derived geometry (what src/size.h spells as macros). */
@@ -182,6 +186,25 @@ vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n,
 vo_status vo_batch_match(vo_engine* e, int32_t n_pairs, const int32_t* prev_slot,
                          const int32_t* curr_slot, int32_t max_features, float bucket_w,
                          float bucket_h);
+/* ---- EXTENSION, parity unpinned: named by the reference's API (Matcher::pushBack(I1,I2,..), matchFeatures(2),
+ * parameters::match_disp_tolerance / refinement, the u2p..i2c fields of p_match: src/matcher.h:45-56,89-104;
+ * VisualOdometryStereo::process, src/viso_stereo.cpp:33-52) but not implemented by it -- its matcher is flow-only.
+ * Defined in DESIGN.md section 9; oracle: oracle/vo_oracle.c (EXTENSION section). --------------------------------- */
+/* Quad matching of n_items stereo frame pairs: the cycle 1c -> 1p -> 2p -> 2c -> 1c over four searches of the
+ * reference's find_match (flow window on prev<->curr edges, |dv| <= disp_tolerance on left<->right edges), both
+ * disparities >= 0, then the reference's emission rules.  Matches carry all eight coordinates.  refinement: 0, or 2 =
+ * sub-pixel (vo_batch_refine).  Needs an engine with vo_config.stereo = 1. */
+vo_status vo_batch_match_quad(vo_engine* e, int32_t n_items, const int32_t* slot_1p, const int32_t* slot_2p,
+                              const int32_t* slot_1c, const int32_t* slot_2c, int32_t disp_tolerance, int32_t refinement,
+                              int32_t max_features, float bucket_w, float bucket_h);
+/* Sub-pixel refinement (parameters::refinement == 2, src/matcher.h:56) of the raw lists of the last vo_batch_match /
+ * vo_batch_match_quad, in place: libviso2's parabolic fit on the small descriptor (computeSmallDescriptor,
+ * src/matcher.cpp:516-543) with the current left feature as anchor; rejected matches are dropped.  The frames must
+ * still be resident in their slots (VO_ERR_STATE after an in-place vo_batch_extract_device). */
+vo_status vo_batch_refine(vo_engine* e, int32_t n_items);
+/* the same on the Matcher-level list (after vo_match_features / vo_remove_outliers, before vo_bucket_features) */
+vo_status vo_refine_matches(vo_engine* e);
+
 /* Replace the raw lists of pairs 0..n_pairs-1 by host lists (lists + i*stride_matches, counts[i] entries; e.g. the
  * raw lists after the host-side removeOutliers, src/matcher.cpp:108) and bucket them (src/matcher.cpp:140-187) in one
  * launch.  The host buffers must stay valid until a later fence / synchronize.  Results: vo_batch_counts /
@@ -280,6 +303,8 @@ vo_status vo_launch_count(const vo_engine* e, int64_t* n);
  * profiling is enabled: ms[0]=extract ms[1]=match ms[2]=cycle+emit ms[3]=bucket; calls[] likewise. */
 vo_status vo_profile_enable(vo_engine* e, int32_t on);
 vo_status vo_profile_read(vo_engine* e, double ms[4], int64_t calls[4], int32_t reset);
+/* eight families: the four above, [4] = refine, the rest reserved */
+vo_status vo_profile_read_ext(vo_engine* e, double ms[8], int64_t calls[8], int32_t reset);
 /* pinned host memory helpers for callers without a CUDA runtime of their own */
 vo_status vo_host_alloc(void** p, int64_t bytes);
 vo_status vo_host_free(void* p);

@@ -95,6 +95,29 @@ class Oracle:
                                            C.c_float(bh))
         return buf[: n.value].copy()
 
+    # ---- EXTENSION, parity unpinned (vo_oracle.c "EXTENSION" section) ----
+    def quad_matching(self, f1p, f2p, f1c, f2c, disp_tolerance: int = 2, cap: int = 1 << 17):
+        """matchFeatures(method=2) on four feature sets (max2, num) -> matches with all 8 coordinates"""
+        out = np.zeros(cap, P_MATCH_DTYPE)
+        n = C.c_int32(0)
+        self.lib.vo_oracle_quad_matching.restype = C.c_int32
+        ovf = self.lib.vo_oracle_quad_matching(C.byref(self.g), _p(f1p[0]), _p(f1p[1]), _p(f2p[0]), _p(f2p[1]),
+                                               _p(f1c[0]), _p(f1c[1]), _p(f2c[0]), _p(f2c[1]),
+                                               C.c_int32(disp_tolerance), _p(out), C.c_int32(cap), C.byref(n))
+        assert ovf == 0
+        return out[: n.value].copy()
+
+    def refine(self, matches, img_1p, img_1c, img_2p=None, img_2c=None):
+        """parabolic sub-pixel refinement (param.refinement == 2) of a flow or quad list; drops rejected matches"""
+        buf = np.array(matches, dtype=P_MATCH_DTYPE, copy=True)
+        if len(buf) == 0:
+            return buf
+        n = C.c_int32(len(buf))
+        imgs = [None if i is None else self._img(i) for i in (img_1p, img_2p, img_1c, img_2c)]
+        self.lib.vo_oracle_refine(C.byref(self.g), *[C.c_void_p(None) if i is None else _p(i) for i in imgs],
+                                  _p(buf), C.byref(n))
+        return buf[: n.value].copy()
+
     def rand_number(self, x: int) -> int:
         return int(self.lib.vo_oracle_rand_number(C.c_uint32(x)))
 

@@ -250,9 +250,9 @@ static int32_t sad32(const uint8_t* a, const uint8_t* b) {
 /* One direction: every origin column u < U-1 of `from` searches `to` (find_match, :70-119, driven
  * by the per-column loops :148-176).  stats[0] += SAD evaluations, stats[1] += origins without any
  * candidate (outside the dead column), stats[2] += candidates range-tested. */
-static void match_direction(const vo_oracle_geom* g, col_list* from, const col_list* to, int64_t* stats) {
+static void match_direction(const vo_oracle_geom* g, col_list* from, const col_list* to, int64_t* stats, int32_t rad_v) {
   const int32_t U = g->u_bins, V = g->v_bins;
-  const int32_t rad_u = g->bin_w * 3, rad_v = g->bin_h * 3;  /* src/size.h:14-15 */
+  const int32_t rad_u = g->bin_w * 3;  /* src/size.h:14; rad_v = bin_h*3 (src/size.h:15) for flow edges */
   for (int32_t ub = 0; ub < U; ub++)
     for (int32_t c = 0; c < 4; c++) {
       col_list* L = &from[ub * 4 + c];
@@ -294,8 +294,8 @@ int32_t vo_oracle_matching(const vo_oracle_geom* g, const int32_t* m1p, const in
   col_list* prv = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
   build_columns(g, m1c, n1c, cur);
   build_columns(g, m1p, n1p, prv);
-  match_direction(g, cur, prv, stats);
-  match_direction(g, prv, cur, stats);
+  match_direction(g, cur, prv, stats, g->bin_h * 3);
+  match_direction(g, prv, cur, stats, g->bin_h * 3);
 
   uint8_t* taken = (uint8_t*)calloc((size_t)g->width * g->height, 1);  /* M[][] (:133) */
   int32_t n = 0, overflow = 0;
@@ -385,4 +385,165 @@ void vo_oracle_bucket_features(vo_oracle_match* list, int32_t* n, int32_t max_fe
   }
   *n = out;
   free(id); free(start); free(sorted); free(fill);
+}
+
+/* =============================================================================================
+ * EXTENSION -- PARITY UNPINNED.
+ *
+ * Quad (left/right x prev/curr) circular matching and sub-pixel refinement are named by the
+ * reference's API (Matcher::pushBack(I1,I2,..), matchFeatures(method=2), parameters
+ * match_disp_tolerance / refinement, p_match fields u2p..i2c: src/matcher.h:45-56,89-104;
+ * VisualOdometryStereo::process calls matchFeatures(2): src/viso_stereo.cpp:33-52) but NOT implemented by it:
+ * pushBack ignores I2, matchFeatures ignores `method`, `refinement` is never read.  What follows is OUR
+ * restatement, built from
+ *   - the reference's own search (find_match, src/myMatch.cpp:70-119, as match_direction above) for every
+ *     edge of the cycle, with the window |dv| <= match_disp_tolerance on left<->right edges (the meaning
+ *     src/matcher.h:51 gives the field; libviso2's published rule), |dv| <= SEARCH_RAD_V on flow edges;
+ *   - libviso2's published quad rule (Geiger et al., libviso2 matcher.cpp `matching`, method 2): the cycle
+ *     1c -> 1p -> 2p -> 2c -> 1c must close and both disparities must be non-negative;
+ *   - the reference's emission rules (order, same-pixel dedupe, "<5 -> 0": src/myMatch.cpp:181-203);
+ *   - libviso2's published parabolicFitting on the 16-byte "small" descriptor, whose definition the
+ *     reference does carry (computeSmallDescriptor, src/matcher.cpp:516-543; margin = 7, src/matcher.cpp:38),
+ *     over the Sobel responses of the reference's executed filter (mySobel5x5).
+ * There is no reference output to pin these against; tests compare the CUDA path with THIS code only and
+ * report the results separately from the pinned mono path.
+ * ============================================================================================= */
+
+/* matchFeatures(method = 2).  Returns 0, or 1 if out_cap was too small. */
+int32_t vo_oracle_quad_matching(const vo_oracle_geom* g, const int32_t* m1p, const int32_t* n1p, const int32_t* m2p,
+                                const int32_t* n2p, const int32_t* m1c, const int32_t* n1c, const int32_t* m2c,
+                                const int32_t* n2c, int32_t disp_tolerance, vo_oracle_match* out, int32_t out_cap,
+                                int32_t* n_out) {
+  const int32_t U = g->u_bins;
+  int64_t stats[3] = {0, 0, 0};
+  col_list* c1 = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
+  col_list* p1 = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
+  col_list* p2 = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
+  col_list* c2 = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
+  build_columns(g, m1c, n1c, c1); build_columns(g, m1p, n1p, p1);
+  build_columns(g, m2p, n2p, p2); build_columns(g, m2c, n2c, c2);
+  match_direction(g, c1, p1, stats, g->bin_h * 3);   /* flow   1c -> 1p */
+  match_direction(g, p1, p2, stats, disp_tolerance); /* stereo 1p -> 2p */
+  match_direction(g, p2, c2, stats, g->bin_h * 3);   /* flow   2p -> 2c */
+  match_direction(g, c2, c1, stats, disp_tolerance); /* stereo 2c -> 1c */
+
+  uint8_t* taken = (uint8_t*)calloc((size_t)g->width * g->height, 1);
+  int32_t n = 0, overflow = 0;
+  for (int32_t u = 0; u < U; u++)
+    for (int32_t c = 0; c < 4; c++) {
+      const col_list* L = &c1[u * 4 + c];
+      for (int32_t k = 0; k < L->n; k++) {
+        if (L->best_ubin[k] < 0) continue;
+        const col_list* A = &p1[L->best_ubin[k] * 4 + c]; const int32_t ak = L->best_idx[k];
+        if (A->best_ubin[ak] < 0) continue;
+        const col_list* B = &p2[A->best_ubin[ak] * 4 + c]; const int32_t bk = A->best_idx[ak];
+        if (B->best_ubin[bk] < 0) continue;
+        const col_list* D = &c2[B->best_ubin[bk] * 4 + c]; const int32_t dk = B->best_idx[bk];
+        if (D->best_ubin[dk] != u || D->best_idx[dk] != k) continue;   /* circle closes */
+        const int32_t* f1c = L->rec[k]; const int32_t* f1p = A->rec[ak];
+        const int32_t* f2p = B->rec[bk]; const int32_t* f2c = D->rec[dk];
+        if (f1p[0] < f2p[0] || f1c[0] < f2c[0]) continue;               /* disparities >= 0 */
+        uint8_t* flag = &taken[(size_t)f1c[1] * g->width + f1c[0]];
+        if (*flag) continue;
+        *flag = 1;
+        if (n < out_cap) {
+          vo_oracle_match m;
+          m.u1p = (float)f1p[0]; m.v1p = (float)f1p[1]; m.i1p = -1;
+          m.u2p = (float)f2p[0]; m.v2p = (float)f2p[1]; m.i2p = -1;
+          m.u1c = (float)f1c[0]; m.v1c = (float)f1c[1]; m.i1c = -1;
+          m.u2c = (float)f2c[0]; m.v2c = (float)f2c[1]; m.i2c = -1;
+          out[n] = m;
+        } else {
+          overflow = 1;
+        }
+        n++;
+      }
+    }
+  *n_out = (n < 5) ? 0 : n;
+  free(taken);
+  free_columns(g, c1); free_columns(g, p1); free_columns(g, p2); free_columns(g, c2);
+  free(c1); free(p1); free(p2); free(c2);
+  return overflow;
+}
+
+/* computeSmallDescriptor, src/matcher.cpp:516-543: 12 du + 4 dv samples (the centre du twice) */
+static const int8_t k_small_dx[16] = {0, -2, 0, 2, -1, 0, 0, 1, -2, 0, 2, 0,  0, -1, 1, 0};
+static const int8_t k_small_dy[16] = {-2, -1, -1, -1, 0, 0, 0, 0, 1, 1, 1, 2, -1, 0, 0, 1};
+
+static void small_descriptor(const uint8_t* du, const uint8_t* dv, int32_t w, int32_t u, int32_t v, uint8_t d[16]) {
+  for (int s = 0; s < 16; s++) {
+    const int32_t a = (v + k_small_dy[s]) * w + (u + k_small_dx[s]);
+    d[s] = (s < 12) ? du[a] : dv[a];
+  }
+}
+
+/* parabolicFitting (libviso2): 5x5 SAD costs of the anchor's small descriptor against the target shifted by
+ * (-2..2)^2, minimum on the border -> fail, least-squares quadric c ~ b0 du^2 + b1 dv^2 + b2 du dv + b3 du +
+ * b4 dv + b5 through the 3x3 costs around the minimum, stationary point -> (ddu, ddv), |.| >= 1 -> fail.
+ * The 9x6 design of libviso2's `refinement` has closed-form normal equations; with integer costs
+ *   6 b0 = B0 = 3 P - 2 R,  6 b1 = B1 = 3 Q - 2 R,  4 b2 = B2,  6 b3 = B3,  6 b4 = B4
+ * (P = sum du^2 c, Q = sum dv^2 c, R = sum c, B2 = sum du dv c, B3 = sum du c, B4 = sum dv c), so
+ *   ddv = NV / D,  ddu = -2 (B4 D + 2 B1 NV) / (3 B2 D),   D = 9 B2^2 - 16 B0 B1,  NV = 8 B0 B4 - 6 B2 B3
+ * are ratios of integers: one IEEE double division each, rounded to float -- the same bits on any machine.
+ * libviso2's tests |divisor| < 1e-8, |b2| < 1e-8 become D == 0, B2 == 0. */
+static int parabolic_fit(const uint8_t* du1, const uint8_t* dv1, const uint8_t* du2, const uint8_t* dv2, int32_t w,
+                         int32_t h, float u1, float v1, float* u2, float* v2) {
+  const int32_t margin = 7;  /* src/matcher.cpp:38 */
+  if (*u2 - 2 < margin || *u2 + 2 > w - 1 - margin || *v2 - 2 < margin || *v2 + 2 > h - 1 - margin) return 0;
+  uint8_t d1[16], d2[16];
+  small_descriptor(du1, dv1, w, (int32_t)u1, (int32_t)v1, d1);
+  int32_t cost[25], min_ind = 0;
+  for (int32_t b = 0; b < 5; b++)
+    for (int32_t a = 0; a < 5; a++) {
+      small_descriptor(du2, dv2, w, (int32_t)*u2 + a - 2, (int32_t)*v2 + b - 2, d2);
+      int32_t s = 0;
+      for (int i = 0; i < 16; i++) s += abs((int32_t)d1[i] - (int32_t)d2[i]);
+      cost[b * 5 + a] = s;
+    }
+  for (int32_t i = 1; i < 25; i++) if (cost[i] < cost[min_ind]) min_ind = i;
+  const int32_t a0 = min_ind % 5, b0 = min_ind / 5;
+  if (a0 == 0 || a0 == 4 || b0 == 0 || b0 == 4) return 0;
+  int64_t P = 0, Q = 0, R = 0, B2 = 0, B3 = 0, B4 = 0;
+  for (int32_t i = -1; i <= 1; i++)
+    for (int32_t j = -1; j <= 1; j++) {
+      const int64_t c = cost[(b0 + i) * 5 + (a0 + j)];
+      P += j * j * c; Q += i * i * c; R += c; B2 += i * j * c; B3 += j * c; B4 += i * c;
+    }
+  const int64_t B0 = 3 * P - 2 * R, B1 = 3 * Q - 2 * R;
+  const int64_t D = 9 * B2 * B2 - 16 * B0 * B1, NV = 8 * B0 * B4 - 6 * B2 * B3;
+  if (D == 0 || B2 == 0) return 0;
+  const float ddv = (float)((double)NV / (double)D);
+  const float ddu = (float)((double)(-2 * (B4 * D + 2 * B1 * NV)) / (double)(3 * B2 * D));
+  if (fabsf(ddu) >= 1.0f || fabsf(ddv) >= 1.0f) return 0;
+  *u2 = (float)((double)*u2 + ((double)(a0 - 2) + (double)ddu));
+  *v2 = (float)((double)*v2 + ((double)(b0 - 2) + (double)ddv));
+  return 1;
+}
+
+/* refinement(p_matched, method) with param.refinement == 2 (libviso2): the current left feature is the anchor;
+ * 1p (flow), then -- quad lists only, i.e. u2c >= 0 -- 2c and 2p are refined against it; a match any fit
+ * rejects is dropped.  In place, order preserved.  img_2p / img_2c may be NULL for flow lists. */
+void vo_oracle_refine(const vo_oracle_geom* g, const uint8_t* img_1p, const uint8_t* img_2p, const uint8_t* img_1c,
+                      const uint8_t* img_2c, vo_oracle_match* list, int32_t* n) {
+  const int32_t w = g->width, h = g->height;
+  const uint8_t* imgs[4] = {img_1p, img_2p, img_1c, img_2c};
+  uint8_t* du[4] = {0, 0, 0, 0};
+  uint8_t* dv[4] = {0, 0, 0, 0};
+  for (int i = 0; i < 4; i++)
+    if (imgs[i]) {
+      du[i] = (uint8_t*)malloc((size_t)w * h); dv[i] = (uint8_t*)malloc((size_t)w * h);
+      vo_oracle_sobel5x5(imgs[i], w, h, g->pitch, du[i], dv[i]);
+    }
+  int32_t kept = 0;
+  for (int32_t i = 0; i < *n; i++) {
+    vo_oracle_match m = list[i];
+    int ok = parabolic_fit(du[2], dv[2], du[0], dv[0], w, h, m.u1c, m.v1c, &m.u1p, &m.v1p);
+    if (ok && m.u2c >= 0.f && du[3] && du[1]) {
+      ok = parabolic_fit(du[2], dv[2], du[3], dv[3], w, h, m.u1c, m.v1c, &m.u2c, &m.v2c) &&
+           parabolic_fit(du[2], dv[2], du[1], dv[1], w, h, m.u1c, m.v1c, &m.u2p, &m.v2p);
+    }
+    if (ok) list[kept++] = m;
+  }
+  *n = kept;
+  for (int i = 0; i < 4; i++) { free(du[i]); free(dv[i]); }
 }
