@@ -56,8 +56,13 @@ EXPORTS = [
     "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
     "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
-    "vo_pipeline_process", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
+    "vo_pipeline_process", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
 ]
+
+class VoStereoParams(C.Structure):  # vo_stereo_params: /root/reference/src/viso_stereo.h:31-43
+    _fields_ = [("f", C.c_double), ("cu", C.c_double), ("cv", C.c_double), ("base", C.c_double),
+                ("ransac_iters", C.c_int32), ("reweighting", C.c_int32), ("inlier_threshold", C.c_double)]
+
 
 class VoMonoParams(C.Structure):  # vo_mono_params: /root/reference/src/viso_mono.h:32-46, src/viso.h:56-64
     _fields_ = [("f", C.c_double), ("cu", C.c_double), ("cv", C.c_double), ("height", C.c_double), ("pitch", C.c_double),
@@ -129,6 +134,7 @@ def load_library() -> C.CDLL:
         "vo_pipeline_create": [vp, C.POINTER(VoMonoParams), i32, f32, f32, i32, C.POINTER(vp)],
         "vo_pipeline_destroy": [vp],
         "vo_pipeline_process": [vp, i32, vp, i64, i32, vp, vp, vp, vp, vp, i64],
+        "vo_estimate_motion_stereo": [vp, vp, i32, C.POINTER(VoStereoParams), C.POINTER(C.c_double), C.POINTER(i32)],
         "vo_batch_match_quad": [vp, i32, vp, vp, vp, vp, i32, i32, i32, f32, f32],
         "vo_batch_refine": [vp, i32],
         "vo_refine_matches": [vp],
@@ -466,6 +472,26 @@ class Egomotion:
 
     def rand(self) -> int:
         return int(self.lib.vo_egomotion_rand(self.h))
+
+
+class EgomotionStereo(Egomotion):
+    """vo_estimate_motion_stereo: VisualOdometryStereo::estimateMotion, /root/reference/src/viso_stereo.cpp:54-157,
+    on quad match lists; same sample stream handle as the monocular stage."""
+
+    def __init__(self, f=1.0, cu=0.0, cv=0.0, base=1.0, ransac_iters=200, inlier_threshold=2.0, reweighting=True,
+                 seed: int = 0):
+        super().__init__(seed=seed)
+        self.sprm = VoStereoParams(f=f, cu=cu, cv=cv, base=base, ransac_iters=ransac_iters, reweighting=int(reweighting),
+                                   inlier_threshold=inlier_threshold)
+
+    def estimate(self, matches: np.ndarray):
+        m = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)
+        tr = (C.c_double * 6)()
+        ok = C.c_int32(0)
+        st = self.lib.vo_estimate_motion_stereo(self.h, _ptr(m) if len(m) else None, len(m), C.byref(self.sprm), tr, C.byref(ok))
+        if st != VO_OK:
+            raise VoError(st, "vo_estimate_motion_stereo")
+        return np.array(tr[:], dtype=np.float64) if ok.value else None
 
 
 def transformation_vector_to_matrix(tr) -> np.ndarray:

@@ -533,3 +533,209 @@ void vo_transformation_vector_to_matrix(const double tr[6], double Tr[16]) {
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// Stereo egomotion: VisualOdometryStereo::estimateMotion, src/viso_stereo.cpp:54-157 -- 3-point RANSAC over a
+// Gauss-Newton minimisation of the reprojection error of the previous frame's triangulated points into the
+// current left/right images, then a refit on the inliers.  A host stage like the monocular one (sequential,
+// 6x6 systems).  Operation order follows the reference statement by statement (sums, Gauss-Jordan pivoting), and
+// the library is compiled without FMA contraction, so results agree with the compiled reference to rounding.
+// =================================================================================================
+namespace {
+
+enum GnResult { GN_UPDATED, GN_FAILED, GN_CONVERGED };  // src/viso_stereo.h:69
+
+struct StereoWork {
+  const vo_p_match* m;
+  int32_t N;
+  vo_stereo_params prm;
+  std::vector<double> X, Y, Z, J, predict, observe, residual;
+};
+
+// Matrix::solve (Gauss-Jordan, full pivoting, eps = 1e-20): src/matrix.cpp:417-503, for a 6x6 system with one RHS
+bool solve6(double A[6][6], double B[6]) {
+  int indxc[6], indxr[6], ipiv[6] = {0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < 6; i++) {
+    double big = 0.0;
+    int irow = 0, icol = 0;
+    for (int j = 0; j < 6; j++)
+      if (ipiv[j] != 1)
+        for (int k = 0; k < 6; k++)
+          if (ipiv[k] == 0 && std::fabs(A[j][k]) >= big) { big = std::fabs(A[j][k]); irow = j; icol = k; }
+    ++ipiv[icol];
+    if (irow != icol) {
+      for (int l = 0; l < 6; l++) std::swap(A[irow][l], A[icol][l]);
+      std::swap(B[irow], B[icol]);
+    }
+    indxr[i] = irow; indxc[i] = icol;
+    if (std::fabs(A[icol][icol]) < 1e-20) return false;
+    const double pivinv = 1.0 / A[icol][icol];
+    A[icol][icol] = 1.0;
+    for (int l = 0; l < 6; l++) A[icol][l] *= pivinv;
+    B[icol] *= pivinv;
+    for (int ll = 0; ll < 6; ll++)
+      if (ll != icol) {
+        const double dum = A[ll][icol];
+        A[ll][icol] = 0.0;
+        for (int l = 0; l < 6; l++) A[ll][l] -= A[icol][l] * dum;
+        B[ll] -= B[icol] * dum;
+      }
+  }
+  (void)indxr; (void)indxc;  // the column unscrambling only touches A, which is not read afterwards
+  return true;
+}
+
+// computeObservations + computeResidualsAndJacobian: src/viso_stereo.cpp:222-327
+void residuals_and_jacobian(StereoWork& w, const double tr[6], const int32_t* active, int32_t na) {
+  for (int32_t i = 0; i < na; i++) {
+    const vo_p_match& q = w.m[active[i]];
+    w.observe[4 * i + 0] = q.u1c; w.observe[4 * i + 1] = q.v1c; w.observe[4 * i + 2] = q.u2c; w.observe[4 * i + 3] = q.v2c;
+  }
+  const double rx = tr[0], ry = tr[1], rz = tr[2], tx = tr[3], ty = tr[4], tz = tr[5];
+  const double sx = std::sin(rx), cx = std::cos(rx), sy = std::sin(ry), cy = std::cos(ry), sz = std::sin(rz), cz = std::cos(rz);
+  const double r00 = +cy * cz, r01 = -cy * sz, r02 = +sy;
+  const double r10 = +sx * sy * cz + cx * sz, r11 = -sx * sy * sz + cx * cz, r12 = -sx * cy;
+  const double r20 = -cx * sy * cz + sx * sz, r21 = +cx * sy * sz + sx * cz, r22 = +cx * cy;
+  const double rdrx10 = +cx * sy * cz - sx * sz, rdrx11 = -cx * sy * sz - sx * cz, rdrx12 = -cx * cy;
+  const double rdrx20 = +sx * sy * cz + cx * sz, rdrx21 = -sx * sy * sz + cx * cz, rdrx22 = -sx * cy;
+  const double rdry00 = -sy * cz, rdry01 = +sy * sz, rdry02 = +cy;
+  const double rdry10 = +sx * cy * cz, rdry11 = -sx * cy * sz, rdry12 = +sx * sy;
+  const double rdry20 = -cx * cy * cz, rdry21 = +cx * cy * sz, rdry22 = -cx * sy;
+  const double rdrz00 = -cy * sz, rdrz01 = -cy * cz;
+  const double rdrz10 = -sx * sy * sz + cx * cz, rdrz11 = -sx * sy * cz - cx * sz;
+  const double rdrz20 = +cx * sy * sz + sx * cz, rdrz21 = +cx * sy * cz - sx * sz;
+  const double f = w.prm.f, cu = w.prm.cu, cv = w.prm.cv, base = w.prm.base;
+  for (int32_t i = 0; i < na; i++) {
+    const double X1p = w.X[active[i]], Y1p = w.Y[active[i]], Z1p = w.Z[active[i]];
+    const double X1c = r00 * X1p + r01 * Y1p + r02 * Z1p + tx;
+    const double Y1c = r10 * X1p + r11 * Y1p + r12 * Z1p + ty;
+    const double Z1c = r20 * X1p + r21 * Y1p + r22 * Z1p + tz;
+    double weight = 1.0;
+    if (w.prm.reweighting) weight = 1.0 / (std::fabs(w.observe[4 * i + 0] - cu) / std::fabs(cu) + 0.05);
+    const double X2c = X1c - base;
+    for (int j = 0; j < 6; j++) {
+      double X1cd = 0, Y1cd = 0, Z1cd = 0;
+      switch (j) {
+        case 0: X1cd = 0; Y1cd = rdrx10 * X1p + rdrx11 * Y1p + rdrx12 * Z1p; Z1cd = rdrx20 * X1p + rdrx21 * Y1p + rdrx22 * Z1p; break;
+        case 1: X1cd = rdry00 * X1p + rdry01 * Y1p + rdry02 * Z1p; Y1cd = rdry10 * X1p + rdry11 * Y1p + rdry12 * Z1p;
+                Z1cd = rdry20 * X1p + rdry21 * Y1p + rdry22 * Z1p; break;
+        case 2: X1cd = rdrz00 * X1p + rdrz01 * Y1p; Y1cd = rdrz10 * X1p + rdrz11 * Y1p; Z1cd = rdrz20 * X1p + rdrz21 * Y1p; break;
+        case 3: X1cd = 1; Y1cd = 0; Z1cd = 0; break;
+        case 4: X1cd = 0; Y1cd = 1; Z1cd = 0; break;
+        case 5: X1cd = 0; Y1cd = 0; Z1cd = 1; break;
+      }
+      w.J[(4 * i + 0) * 6 + j] = weight * f * (X1cd * Z1c - X1c * Z1cd) / (Z1c * Z1c);
+      w.J[(4 * i + 1) * 6 + j] = weight * f * (Y1cd * Z1c - Y1c * Z1cd) / (Z1c * Z1c);
+      w.J[(4 * i + 2) * 6 + j] = weight * f * (X1cd * Z1c - X2c * Z1cd) / (Z1c * Z1c);
+      w.J[(4 * i + 3) * 6 + j] = weight * f * (Y1cd * Z1c - Y1c * Z1cd) / (Z1c * Z1c);
+    }
+    w.predict[4 * i + 0] = f * X1c / Z1c + cu;
+    w.predict[4 * i + 1] = f * Y1c / Z1c + cv;
+    w.predict[4 * i + 2] = f * X2c / Z1c + cu;
+    w.predict[4 * i + 3] = f * Y1c / Z1c + cv;
+    for (int k = 0; k < 4; k++) w.residual[4 * i + k] = weight * (w.observe[4 * i + k] - w.predict[4 * i + k]);
+  }
+}
+
+// updateParameters: src/viso_stereo.cpp:178-220
+GnResult update_parameters(StereoWork& w, const int32_t* active, int32_t na, double tr[6], double step_size, double eps) {
+  if (na < 3) return GN_FAILED;
+  residuals_and_jacobian(w, tr, active, na);
+  double A[6][6], B[6];
+  for (int m = 0; m < 6; m++) {
+    for (int n = 0; n < 6; n++) {
+      double a = 0;
+      for (int32_t i = 0; i < 4 * na; i++) a += w.J[i * 6 + m] * w.J[i * 6 + n];
+      A[m][n] = a;
+    }
+    double b = 0;
+    for (int32_t i = 0; i < 4 * na; i++) b += w.J[i * 6 + m] * w.residual[i];
+    B[m] = b;
+  }
+  if (!solve6(A, B)) return GN_FAILED;
+  bool converged = true;
+  for (int m = 0; m < 6; m++) {
+    tr[m] += step_size * B[m];
+    if (std::fabs(B[m]) > eps) converged = false;
+  }
+  return converged ? GN_CONVERGED : GN_UPDATED;
+}
+
+// getInlier: src/viso_stereo.cpp:159-176
+void stereo_inliers(StereoWork& w, const double tr[6], const std::vector<int32_t>& all, std::vector<int32_t>& out) {
+  residuals_and_jacobian(w, tr, all.data(), w.N);
+  out.clear();
+  const double thr2 = w.prm.inlier_threshold * w.prm.inlier_threshold;
+  for (int32_t i = 0; i < w.N; i++) {
+    const double d0 = w.observe[4 * i + 0] - w.predict[4 * i + 0], d1 = w.observe[4 * i + 1] - w.predict[4 * i + 1];
+    const double d2 = w.observe[4 * i + 2] - w.predict[4 * i + 2], d3 = w.observe[4 * i + 3] - w.predict[4 * i + 3];
+    if (d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 < thr2) out.push_back(i);
+  }
+}
+
+}  // namespace
+
+extern "C" vo_status vo_estimate_motion_stereo(vo_egomotion* eg, const vo_p_match* matches, int32_t n,
+                                               const vo_stereo_params* prm, double tr_delta[6], int32_t* ok) {
+  if (!eg || !prm || !tr_delta || !ok || n < 0 || (n > 0 && !matches)) return VO_ERR_INVALID;
+  *ok = 0;
+  eg->inliers.clear();
+  for (int k = 0; k < 6; k++) tr_delta[k] = 0.0;
+  if (n < 6) return VO_OK;  // src/viso_stereo.cpp:69-70 (before any rand() is consumed)
+  StereoWork w;
+  w.m = matches; w.N = n; w.prm = *prm;
+  w.X.resize(n); w.Y.resize(n); w.Z.resize(n);
+  w.J.resize((size_t)4 * n * 6); w.predict.resize((size_t)4 * n); w.observe.resize((size_t)4 * n); w.residual.resize((size_t)4 * n);
+  for (int32_t i = 0; i < n; i++) {  // project matches of the previous image into 3d: src/viso_stereo.cpp:82-87
+    const double d = std::max(matches[i].u1p - matches[i].u2p, 0.0001f);
+    w.X[i] = (matches[i].u1p - prm->cu) * prm->base / d;
+    w.Y[i] = (matches[i].v1p - prm->cv) * prm->base / d;
+    w.Z[i] = prm->f * prm->base / d;
+  }
+  std::vector<int32_t> all(n), pool, inl_curr, best_inl;
+  for (int32_t i = 0; i < n; i++) all[i] = i;
+  double best_tr[6] = {0, 0, 0, 0, 0, 0};
+  bool have_tr = false;
+  for (int32_t k = 0; k < prm->ransac_iters; k++) {
+    int32_t active[3];  // getRandomSample(N, 3): src/viso.cpp:86-106
+    pool = all;
+    for (int i = 0; i < 3; i++) {
+      const int32_t j = (int32_t)(eg->rng.next() % (uint32_t)pool.size());
+      active[i] = pool[j];
+      pool.erase(pool.begin() + j);
+    }
+    double tr[6] = {0, 0, 0, 0, 0, 0};
+    GnResult result = GN_UPDATED;
+    int iter = 0;
+    while (result == GN_UPDATED) {
+      result = update_parameters(w, active, 3, tr, 1, 1e-6);
+      if (iter++ > 20 || result == GN_CONVERGED) break;
+    }
+    if (result != GN_FAILED) {
+      stereo_inliers(w, tr, all, inl_curr);
+      if (inl_curr.size() > best_inl.size()) {
+        best_inl = inl_curr;
+        for (int q = 0; q < 6; q++) best_tr[q] = tr[q];
+        have_tr = true;
+      }
+    }
+  }
+  bool success = true;
+  if (best_inl.size() >= 6 && have_tr) {  // final optimisation on the inliers: src/viso_stereo.cpp:126-139
+    int iter = 0;
+    GnResult result = GN_UPDATED;
+    while (result == GN_UPDATED) {
+      result = update_parameters(w, best_inl.data(), (int32_t)best_inl.size(), best_tr, 1, 1e-8);
+      if (iter++ > 100 || result == GN_CONVERGED) break;
+    }
+    if (result != GN_CONVERGED) success = false;
+  } else {
+    success = false;
+  }
+  eg->inliers = best_inl;
+  if (success) {
+    for (int q = 0; q < 6; q++) tr_delta[q] = best_tr[q];
+    *ok = 1;
+  }
+  return VO_OK;
+}

@@ -88,12 +88,14 @@ def _rot(rx, ry, rz):
 
 
 def make_scene_matches(n_lists: int, seed: int = 0, width: int = 1241, height: int = 376, n_points: int = 320,
-                       step: float = 0.9, outlier_frac: float = 0.05, calib=None, cam_height: float = KITTI_HEIGHT):
+                       step: float = 0.9, outlier_frac: float = 0.05, calib=None, cam_height: float = KITTI_HEIGHT,
+                       base: float = 0.0):
     """n_lists match lists (structured arrays with fields u1p,v1p,u1c,v1c,... like Matcher::p_match) of a camera
     driving forward `step` metres per frame with a small yaw/pitch wobble through a static scene: a ground
     plane cam_height below the camera plus random structure on both sides.  Coordinates are rounded to integer
     pixels like the matcher's output; outlier_frac of the matches get a random wrong partner.
-    Returns (lists, true_motions[n_lists, 6]) with motion = (rx,ry,rz,tx,ty,tz) of Tr_delta (prev -> curr)."""
+    base > 0 adds the right camera of a rectified rig (u2 = u1 - f*base/Z, v2 = v1): quad match lists for the stereo
+    egomotion.  Returns (lists, true_motions[n_lists, 6]) with motion = (rx,ry,rz,tx,ty,tz) of Tr_delta (prev -> curr)."""
     from .api import P_MATCH_DTYPE
     calib = calib or KITTI_CALIB
     f, cu, cv = calib["f"], calib["cu"], calib["cv"]
@@ -130,6 +132,9 @@ def make_scene_matches(n_lists: int, seed: int = 0, width: int = 1241, height: i
             m["v1c"][bad] = np.rint(rng.uniform(9, height - 9, n_out))
         for fld in ("u2p", "v2p", "u2c", "v2c"):
             m[fld] = -1.0
+        if base > 0:
+            m["u2p"], m["v2p"] = np.rint(up[idx] - f * base / pts[idx, 2]), m["v1p"]
+            m["u2c"], m["v2c"] = np.rint(uc[idx] - f * base / pc[idx, 2]), m["v1c"]
         for fld in ("i1p", "i2p", "i1c", "i2c"):
             m[fld] = -1
         lists.append(m)

@@ -265,6 +265,20 @@ vo_status vo_estimate_motion_mono_samples(const vo_p_match* matches, int32_t n, 
                                           const int32_t* samples, int32_t n_iters, int32_t threads,
                                           double tr_delta[6], int32_t* ok, int32_t* inliers,
                                           int32_t inliers_cap, int32_t* n_inliers);
+/* VisualOdometryStereo::parameters, src/viso_stereo.h:31-43 + VisualOdometry::calibration, src/viso.h:56-64 */
+typedef struct vo_stereo_params {
+  double f, cu, cv;          /* calibration */
+  double base;               /* baseline (m); reference default 1.0 */
+  int32_t ransac_iters;      /* 200 */
+  int32_t reweighting;       /* 1: lower weights towards the image border */
+  double inlier_threshold;   /* 2.0 (pixels) */
+} vo_stereo_params;
+/* VisualOdometryStereo::estimateMotion(p_matched): src/viso_stereo.cpp:54-157 -- 3-point RANSAC over Gauss-Newton on
+ * the reprojection error into the current left/right images, refit on the inliers.  Needs quad matches (u2p, u2c,
+ * v2c filled).  Draws its samples from the handle's stream (3 per iteration, none for n < 6).  *ok = 0 where the
+ * reference returns an empty vector. */
+vo_status vo_estimate_motion_stereo(vo_egomotion* eg, const vo_p_match* matches, int32_t n,
+                                    const vo_stereo_params* prm, double tr_delta[6], int32_t* ok);
 /* VisualOdometry::getInlierIndices / getNumberOfInliers: src/viso.h:96-99 (out may be NULL) */
 vo_status vo_egomotion_inliers(const vo_egomotion* eg, int32_t* out, int32_t cap, int32_t* n);
 /* next value of the handle's sample stream (== glibc rand()); test hook */

@@ -170,3 +170,17 @@ def mono_motion_seq(ref: "RefLib", lists, f, cu, cv, height=1.0, pitch=0.0, rans
     ninl = np.zeros(len(lists), dtype=np.int32)
     ref.lib.ref_mono_motion_seq(_p(flat), _p(counts), C.c_int32(len(lists)), _p(prm), _p(tr), _p(ok), _p(ninl))
     return tr, ok, ninl
+
+
+def stereo_motion_seq(ref: "RefLib", lists, f, cu, cv, base=1.0, ransac_iters=200, inlier_threshold=2.0, reweighting=True):
+    """VisualOdometryStereo::estimateMotion (/root/reference/src/viso_stereo.cpp:54) on a sequence of quad match lists
+    processed by ONE reference object.  Returns (tr[n,6], ok[n], n_inliers[n])."""
+    lists = [np.ascontiguousarray(m, dtype=P_MATCH_DTYPE) for m in lists]
+    counts = np.array([len(m) for m in lists], dtype=np.int32)
+    flat = np.concatenate(lists) if lists else np.zeros(0, dtype=P_MATCH_DTYPE)
+    prm = np.array([f, cu, cv, base, ransac_iters, inlier_threshold, 1.0 if reweighting else 0.0], dtype=np.float64)
+    tr = np.zeros((len(lists), 6), dtype=np.float64)
+    ok = np.zeros(len(lists), dtype=np.int32)
+    ninl = np.zeros(len(lists), dtype=np.int32)
+    ref.lib.ref_stereo_motion_seq(_p(flat), _p(counts), C.c_int32(len(lists)), _p(prm), _p(tr), _p(ok), _p(ninl))
+    return tr, ok, ninl

@@ -13,6 +13,7 @@
 //   removeOutliers      /root/reference/src/remove_outliers.cpp:4
 //   Matcher::*          /root/reference/src/matcher.cpp:32-187
 //   VisualOdometryMono::estimateMotion   /root/reference/src/viso_mono.cpp:41  (row F2, host egomotion)
+//   VisualOdometryStereo::estimateMotion /root/reference/src/viso_stereo.cpp:54 (row F3, stereo egomotion)
 // The reference keeps multi-megabyte arrays on the stack, so every call is executed on a
 // helper thread with a 1 GiB stack; std::cout chatter of the reference is muted.
 
@@ -20,6 +21,7 @@
 #define protected public
 #include "matcher.h"
 #include "viso_mono.h"
+#include "viso_stereo.h"
 #undef private
 #undef protected
 
@@ -166,6 +168,28 @@ void ref_mono_motion_seq(const void* lists, const int32_t* counts, int32_t n_lis
     p.height = prm[3]; p.pitch = prm[4];
     p.ransac_iters = (int32_t)prm[5]; p.inlier_threshold = prm[6]; p.motion_threshold = prm[7];
     VisualOdometryMono vo(p);
+    const Matcher::p_match* cur = (const Matcher::p_match*)lists;
+    for (int32_t i = 0; i < n_lists; i++) {
+      std::vector<Matcher::p_match> v(cur, cur + counts[i]);
+      cur += counts[i];
+      std::vector<double> tr = vo.estimateMotion(v);
+      ok[i] = tr.size() == 6 ? 1 : 0;
+      for (int k = 0; k < 6; k++) tr_out[6 * i + k] = ok[i] ? tr[k] : 0.0;
+      n_inliers[i] = (int32_t)vo.inliers.size();
+    }
+  });
+}
+
+// ---- stereo egomotion (the egomotion half IS in the reference, src/viso_stereo.cpp:54-157) ----
+// One VisualOdometryStereo object (srand(0) in its base constructor) processes the lists in order.
+// prm = {f, cu, cv, base, ransac_iters, inlier_threshold, reweighting}
+void ref_stereo_motion_seq(const void* lists, const int32_t* counts, int32_t n_lists, const double* prm,
+                           double* tr_out, int32_t* ok, int32_t* n_inliers) {
+  on_big_stack([&] {
+    VisualOdometryStereo::parameters p;
+    p.calib.f = prm[0]; p.calib.cu = prm[1]; p.calib.cv = prm[2];
+    p.base = prm[3]; p.ransac_iters = (int32_t)prm[4]; p.inlier_threshold = prm[5]; p.reweighting = prm[6] != 0.0;
+    VisualOdometryStereo vo(p);
     const Matcher::p_match* cur = (const Matcher::p_match*)lists;
     for (int32_t i = 0; i < n_lists; i++) {
       std::vector<Matcher::p_match> v(cur, cur + counts[i]);
