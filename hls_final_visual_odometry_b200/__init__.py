@@ -5,8 +5,8 @@ mirror of the reference's Matcher interface plus the synthetic-frame generator u
 bench.py.  No CPU implementation of the hot path lives here.
 """
 from .api import (Engine, Matcher, VoError, P_MATCH_DTYPE, load_library, pinned_empty, Egomotion,  # noqa: F401
-                  VisualOdometryMono, transformation_vector_to_matrix, Pipeline, EgomotionStereo)
+                  VisualOdometryMono, transformation_vector_to_matrix, Pipeline, EgomotionStereo, VisualOdometryStereo)
 from . import synth  # noqa: F401
 
 __all__ = ["Engine", "Matcher", "VoError", "P_MATCH_DTYPE", "load_library", "pinned_empty", "synth", "Egomotion",
-           "VisualOdometryMono", "transformation_vector_to_matrix", "Pipeline", "EgomotionStereo"]
+           "VisualOdometryMono", "transformation_vector_to_matrix", "Pipeline", "EgomotionStereo", "VisualOdometryStereo"]

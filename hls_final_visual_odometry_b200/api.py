@@ -400,9 +400,13 @@ class Matcher:
             self.refinement = 0
             self.f = self.cu = self.cv = self.base = 0.0
 
-    def __init__(self, width: int, height: int, param: "Matcher.parameters | None" = None, device: int = 0):
+    def __init__(self, width: int, height: int, param: "Matcher.parameters | None" = None, device: int = 0,
+                 stereo: bool = False):
+        """stereo=True (EXTENSION, absent from the reference): pushBack keeps I2, matchFeatures(2) is the quad matcher;
+        param.refinement == 2 adds the sub-pixel stage.  Defaults = the reference's behaviour (I2/method ignored)."""
         self.param = param or Matcher.parameters()
-        self.engine = Engine(width, height, device=device)
+        self.engine = Engine(width, height, device=device, stereo=stereo,
+                             match_disp_tolerance=self.param.match_disp_tolerance if stereo else 0)
 
     def setIntrinsics(self, f, cu, cv, base):
         self.param.f, self.param.cu, self.param.cv, self.param.base = f, cu, cv, base
@@ -413,12 +417,14 @@ class Matcher:
             import sys
             print("ERROR: Image dimension mismatch!", file=sys.stderr)  # src/matcher.cpp:59-62: message, return
             return
-        self.engine.push_back(I1, replace)
+        self.engine.push_back(I1, replace, img2=I2)
 
     def matchFeatures(self, method=0, Tr_delta=None):
         # src/matcher.cpp:93-111: myMatching, then the host-side removeOutliers
         self.engine.match_features(method)
         self.engine.remove_outliers()
+        if self.param.refinement == 2:
+            self.engine.refine_matches()
 
     def bucketFeatures(self, max_features, bucket_width, bucket_height):
         self.engine.bucket_features(max_features, bucket_width, bucket_height)
@@ -536,6 +542,69 @@ class VisualOdometryMono:
         return self.updateMotion()
 
     def updateMotion(self) -> bool:  # src/viso.cpp:42-57
+        tr = self.ego.estimate(self.p_matched)
+        if tr is None:
+            return False
+        self.Tr_delta = transformation_vector_to_matrix(tr)
+        self.Tr_valid = True
+        return True
+
+    def getMotion(self):
+        return self.Tr_delta
+
+    def getMatches(self):
+        return self.matcher.getMatches()
+
+    def getNumberOfMatches(self):
+        return len(self.p_matched)
+
+    def getNumberOfInliers(self):
+        return len(self.ego.inliers())
+
+    def getInlierIndices(self):
+        return self.ego.inliers()
+
+
+class VisualOdometryStereo:
+    """Python mirror of /root/reference/src/viso_stereo.h:27-96: process(I1, I2) = pushBack -> [bootstrap while no valid
+    motion] -> matchFeatures(2) -> bucketFeatures -> getMatches -> updateMotion (src/viso_stereo.cpp:33-52).  The
+    matching half is the quad-matching EXTENSION (the reference's matcher is flow-only, so its own class cannot work);
+    the egomotion half is the reference's, bit for bit (vo_estimate_motion_stereo)."""
+
+    class parameters:
+        def __init__(self):
+            self.match = Matcher.parameters()
+            self.max_features, self.bucket_width, self.bucket_height = 2, 50.0, 50.0   # src/viso.h:43-53
+            self.f, self.cu, self.cv = 1.0, 0.0, 0.0                                   # src/viso.h:56-64
+            self.base, self.ransac_iters, self.inlier_threshold, self.reweighting = 1.0, 200, 2.0, True
+
+    def __init__(self, width: int, height: int, param: "VisualOdometryStereo.parameters | None" = None, device: int = 0):
+        self.param = param or VisualOdometryStereo.parameters()
+        p = self.param
+        self.matcher = Matcher(width, height, p.match, device=device, stereo=True)
+        self.matcher.setIntrinsics(p.f, p.cu, p.cv, p.base)
+        self.ego = EgomotionStereo(p.f, p.cu, p.cv, p.base, p.ransac_iters, p.inlier_threshold, p.reweighting)
+        self.Tr_delta = np.eye(4)
+        self.Tr_valid = False
+        self.p_matched = np.zeros(0, dtype=P_MATCH_DTYPE)
+
+    def _match(self):
+        self.matcher.matchFeatures(2, self.Tr_delta if self.Tr_valid else None)
+        self.matcher.bucketFeatures(self.param.max_features, self.param.bucket_width, self.param.bucket_height)
+        self.p_matched = self.matcher.getMatches()
+
+    def process(self, I1, I2=None, dims=None, replace=False) -> bool:
+        if isinstance(I1, np.ndarray) and I1.dtype == P_MATCH_DTYPE:    # process(p_matched): src/viso.h:75-78
+            self.p_matched = I1
+            return self.updateMotion()
+        self.matcher.pushBack(I1, dims, replace, I2=I2)
+        if not self.Tr_valid:                                           # bootstrap: src/viso_stereo.cpp:39-44
+            self._match()
+            self.updateMotion()
+        self._match()
+        return self.updateMotion()
+
+    def updateMotion(self) -> bool:
         tr = self.ego.estimate(self.p_matched)
         if tr is None:
             return False

@@ -8,7 +8,42 @@
 #include <string>
 #include <vector>
 
+#include <cstring>
+
 #include "viso_mono.h"
+#include "viso_stereo.h"
+
+// stereo variant of the loop (src/demo.cpp reads I1_/I2_ pairs the same way): vo_demo <dir> w h n f cu cv --stereo <base>
+static int run_stereo(const std::string& dir, int32_t width, int32_t height, int32_t n, double f, double cu, double cv, double base) {
+  VisualOdometryStereo::parameters param;
+  param.calib.f = f; param.calib.cu = cu; param.calib.cv = cv; param.base = base;
+  VisualOdometryStereo viso(param);
+  Matrix pose = Matrix::eye(4);
+  std::vector<uint8_t> left((size_t)width * height), right((size_t)width * height);
+  for (int32_t i = 0; i < n; i++) {
+    char name[256];
+    snprintf(name, sizeof(name), "/I1_%06d.dat", i);
+    std::ifstream l((dir + name).c_str(), std::ifstream::binary | std::ifstream::in);
+    snprintf(name, sizeof(name), "/I2_%06d.dat", i);
+    std::ifstream r((dir + name).c_str(), std::ifstream::binary | std::ifstream::in);
+    if (!l.read((char*)left.data(), left.size()) || !r.read((char*)right.data(), right.size())) {
+      std::cerr << "ERROR: Couldn't read input files!" << std::endl;
+      return 1;
+    }
+    int32_t dims[] = {width, height, width};
+    const bool ok = viso.process(left.data(), right.data(), dims);
+    if (viso.getMatcher()->lastStatus() != 0) return 2;
+    std::cout << "Processing: Frame: " << i << ", Matches: " << viso.getNumberOfMatches();
+    if (ok) {
+      pose = pose * Matrix::inv(viso.getMotion());
+      std::cout << ", Inliers: " << 100.0 * viso.getNumberOfInliers() / viso.getNumberOfMatches() << " %" << std::endl << pose << std::endl;
+    } else {
+      std::cout << " ... failed!" << std::endl;
+    }
+  }
+  std::cout << "Demo complete! Exiting ..." << std::endl;
+  return 0;
+}
 
 int main(int argc, char** argv) {
   if (argc < 5) {
@@ -17,6 +52,8 @@ int main(int argc, char** argv) {
   }
   const std::string dir = argv[1];
   const int32_t width = atoi(argv[2]), height = atoi(argv[3]), n = atoi(argv[4]);
+  if (argc > 9 && !strcmp(argv[8], "--stereo"))
+    return run_stereo(dir, width, height, n, atof(argv[5]), atof(argv[6]), atof(argv[7]), atof(argv[9]));
   VisualOdometryMono::parameters param;
   param.calib.f = argc > 5 ? atof(argv[5]) : 491.543832;   // calibration of the reference demo: src/demo.cpp:60-65
   param.calib.cu = argc > 6 ? atof(argv[6]) : 484.474328;

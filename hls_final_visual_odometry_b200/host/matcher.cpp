@@ -6,7 +6,8 @@
 
 static_assert(sizeof(Matcher::p_match) == sizeof(vo_p_match), "p_match must stay the 48-byte wire format");
 
-Matcher::Matcher(parameters param, int device) : param(param), device(device), eng(nullptr), last_status(0) {}
+Matcher::Matcher(parameters param, int device, bool stereo)
+    : param(param), device(device), stereo(stereo), eng(nullptr), last_status(0) {}
 
 Matcher::~Matcher() {
   if (eng) vo_engine_destroy(eng);
@@ -20,6 +21,8 @@ bool Matcher::ensureEngine(int32_t width, int32_t height) {
   cfg.width = width;
   cfg.height = height;
   cfg.nms_tau = param.nms_tau;
+  cfg.stereo = stereo ? 1 : 0;
+  cfg.match_disp_tolerance = param.match_disp_tolerance;
   last_status = vo_engine_create(&cfg, device, nullptr, &eng);
   if (last_status != VO_OK) {
     std::cerr << "ERROR: " << vo_last_error() << std::endl;
@@ -54,6 +57,7 @@ void Matcher::matchFeatures(int32_t method, Matrix* /*Tr_delta*/) {
   } else {
     last_status = vo_remove_outliers(eng);  // removeOutliers(p_matched_2, p_matched_2_cnt), src/matcher.cpp:108
   }
+  if (last_status == VO_OK && param.refinement == 2) last_status = vo_refine_matches(eng);  // extension (matcher.h)
   if (last_status != VO_OK) std::cerr << "ERROR: " << vo_last_error() << std::endl;
 }
 

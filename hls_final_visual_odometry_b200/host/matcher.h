@@ -9,7 +9,11 @@
 //  * matchFeatures() runs the GPU circular matcher and then, as the reference does inside
 //    matchFeatures (src/matcher.cpp:108), the host-side Delaunay support filter
 //    (vo_remove_outliers, csrc/vo_outliers.cpp); setOutlierFilter() can replace that stage;
-//  * frame 0 yields zero matches instead of matching against uninitialised counts.
+//  * frame 0 yields zero matches instead of matching against uninitialised counts;
+//  * EXTENSION (absent from the reference): a Matcher constructed with stereo = true keeps the
+//    right images pushBack receives and runs the quad matcher for matchFeatures(2); parameters::refinement == 2
+//    (dead in the reference, default 0) adds the sub-pixel stage after removeOutliers.  With the defaults the
+//    behaviour is the reference's: I2, `method` and `refinement` are ignored.
 #ifndef VO_B200_HOST_MATCHER_H
 #define VO_B200_HOST_MATCHER_H
 
@@ -57,7 +61,7 @@ class Matcher {
           u2c(u2c), v2c(v2c), i2c(i2c) {}
   };
 
-  explicit Matcher(parameters param, int device = 0);
+  explicit Matcher(parameters param, int device = 0, bool stereo = false);
   ~Matcher();
   Matcher(const Matcher&) = delete;
   Matcher& operator=(const Matcher&) = delete;
@@ -66,11 +70,11 @@ class Matcher {
     param.f = f; param.cu = cu; param.cv = cv; param.base = base;
   }
 
-  // src/matcher.cpp:51-91.  dims = {width, height, bytes per line}; I2 is ignored as in the reference.
+  // src/matcher.cpp:51-91.  dims = {width, height, bytes per line}; I2 is ignored as in the reference (unless stereo).
   void pushBack(uint8_t* I1, uint8_t* I2, int32_t* dims, const bool replace);
   void pushBack(uint8_t* I1, int32_t* dims, const bool replace) { pushBack(I1, 0, dims, replace); }
 
-  // src/matcher.cpp:93-111.  method and Tr_delta are accepted and ignored, as in the reference.
+  // src/matcher.cpp:93-111.  method and Tr_delta are accepted and ignored, as in the reference (unless stereo: method 2).
   void matchFeatures(int32_t method, Matrix* Tr_delta = 0);
 
   // src/matcher.cpp:140-187
@@ -92,6 +96,7 @@ class Matcher {
   bool ensureEngine(int32_t width, int32_t height);
   parameters param;
   int device;
+  bool stereo;
   vo_engine* eng;
   int last_status;
   std::function<void(std::vector<Matcher::p_match>&)> outlier_filter;

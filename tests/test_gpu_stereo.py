@@ -187,3 +187,55 @@ def test_refinement_matcher_level_and_state_errors():
         assert ei.value.status == VO_ERR_STATE
     finally:
         eng.close()
+
+
+def test_stereo_process_loop_on_a_rendered_rig(tmp_path):
+    """VisualOdometryStereo::process (/root/reference/src/viso_stereo.cpp:33-52) over a rendered 3-D corridor seen by a
+    rectified rig: bucketed quad lists == oracle quad matching -> removeOutliers -> bucketing (unpinned extension),
+    motion == the compiled reference's estimateMotion on those lists within 1e-6 (pinned half), and it is the rendered
+    motion in metres (the baseline fixes the scale).  The C++ shim (vo_demo --stereo) must report the same counts."""
+    import re
+    import subprocess
+    from hls_final_visual_odometry_b200 import VisualOdometryStereo, build
+    from hls_final_visual_odometry_b200.api import remove_outliers_host
+    from hls_final_visual_odometry_b200.synth import KITTI_CALIB, make_corridor_sequence
+    from oracle.ref_lib import RefLib, have_ref, stereo_motion_seq
+    w, h, n, base = 1241, 376, 4, 0.54
+    left, poses = make_corridor_sequence(w, h, n_frames=n, seed=1)
+    right, _ = make_corridor_sequence(w, h, n_frames=n, seed=1, cam_offset_x=base)
+    p = VisualOdometryStereo.parameters()
+    p.f, p.cu, p.cv, p.base = KITTI_CALIB["f"], KITTI_CALIB["cu"], KITTI_CALIB["cv"], base
+    vo = VisualOdometryStereo(w, h, p)
+    orc = Oracle(w, h)
+    fl = [_feats(orc, f) for f in left]
+    fr = [_feats(orc, f) for f in right]
+    lists, got_tr, counts = [], [], []
+    for k in range(n):
+        ok = vo.process(left[k], right[k])
+        counts.append(vo.getNumberOfMatches())
+        if k == 0:
+            assert not ok and vo.getNumberOfMatches() == 0
+            continue
+        want = orc.bucket_features(remove_outliers_host(orc.quad_matching(fl[k - 1], fr[k - 1], fl[k], fr[k], 2)), 2, 50.0, 50.0)
+        assert matches_digest(vo.p_matched) == matches_digest(want) and len(want) > 100
+        assert ok
+        lists.append(want)
+        got_tr.append(np.array(vo.getMotion()))
+        rel = np.linalg.inv(poses[k]) @ poses[k - 1]                    # rendered motion prev -> curr: 0.6 m forward
+        assert np.abs(vo.getMotion()[:3, 3] - rel[:3, 3]).max() < 0.05 and np.abs(vo.getMotion()[:3, :3] - rel[:3, :3]).max() < 5e-3
+    if have_ref("native"):
+        # the reference object sees list 1 twice (bootstrap + regular pass of the first valid frame)
+        from hls_final_visual_odometry_b200 import transformation_vector_to_matrix
+        tr_ref, ok_ref, _ = stereo_motion_seq(RefLib("native"), [lists[0]] + lists, base=base, **KITTI_CALIB)
+        for k in range(1, n):
+            assert ok_ref[k] == 1
+            assert np.abs(got_tr[k - 1] - transformation_vector_to_matrix(tr_ref[k])).max() <= 1e-6
+    # C++ drop-in
+    build.build_all()
+    for k in range(n):
+        left[k].tofile(str(tmp_path / f"I1_{k:06d}.dat"))
+        right[k].tofile(str(tmp_path / f"I2_{k:06d}.dat"))
+    out = subprocess.run([build.DEMO, str(tmp_path), str(w), str(h), str(n), str(p.f), str(p.cu), str(p.cv), "--stereo", str(base)],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    assert [int(re.search(r"Matches: (\d+)", l).group(1)) for l in out.stdout.splitlines() if "Matches:" in l] == counts
