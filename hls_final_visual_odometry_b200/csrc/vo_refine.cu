@@ -9,9 +9,10 @@
 // double division per offset), so the two agree bit for bit.
 //
 // One WARP per match.  The frames are still resident in their slots, so nothing but 13x13-byte patches is read:
-// per target (1p, and for quad lists 2c and 2p) the warp pulls the patch into shared memory, evaluates du/dv on
-// the 9x9 pixels the 25 shifted descriptors touch, lanes 0..24 each take one shift's SAD, a warp min picks the first
-// minimum in raster order, and lane 0 solves the fit.  k5_compact then drops rejected matches, order preserved.
+// per target (1p, and for quad lists 2c and 2p) the warp pulls the patch into shared memory as aligned words, 27 lanes
+// evaluate du/dv on the 9x9 pixels the 25 shifted descriptors touch (column x 3-row segment each, separable, in
+// registers), lanes 0..24 each take one shift's SAD (one VABSDIFF4 per byte against the anchor descriptor held in
+// registers), a warp min picks the first minimum in raster order, and the fit is exact double arithmetic.  k5_compact then drops rejected matches, order preserved.
 #include "vo_common.cuh"
 
 namespace vo {
@@ -21,82 +22,100 @@ constexpr int kPatch = 13;   // 2*(2 shift + 2 sample + 2 sobel) + 1
 constexpr int kResp = 9;     // 2*(2 shift + 2 sample) + 1
 
 struct K5Warp {
-  uint8_t patch[kPatch * 16];
+  __align__(16) uint8_t patch[kPatch * 16];  // row stride 16 bytes; a row starts at the 4-byte boundary below its first pixel
   uint8_t du[kResp * kResp + 3];
   uint8_t dv[kResp * kResp + 3];
-  uint8_t d1[16];
 };
 
 // computeSmallDescriptor sample offsets (src/matcher.cpp:527-542): 12 du then 4 dv
 __constant__ int8_t c_small_dx[16] = {0, -2, 0, 2, -1, 0, 0, 1, -2, 0, 2, 0, 0, -1, 1, 0};
 __constant__ int8_t c_small_dy[16] = {-2, -1, -1, -1, 0, 0, 0, 0, 1, 1, 1, 2, -1, 0, 0, 1};
 
-__device__ __forceinline__ uint8_t sobel_u8(int acc) {  // src/myComputeFeature.cpp:84-106
-  const int q = acc / 128 + 128;
-  return (uint8_t)min(max(q, 0), 255);
-}
+// acc/128 (C truncation toward zero) + 128; the reference's clamp to [0,255] cannot fire (|acc| <= 12240):
+// src/myComputeFeature.cpp:84-106
+__device__ __forceinline__ uint8_t sobel_u8(int acc) { return (uint8_t)(((acc + ((acc >> 31) & 127)) >> 7) + 128); }
 
-// du/dv on the (2R+1)^2 pixels around (cx, cy) of one frame; R = 2 (anchor) or 4 (target)
-__device__ __forceinline__ void responses(K5Warp& w, const uint8_t* __restrict__ img, int pitch, int cx, int cy, int R,
-                                          int lane) {
-  const int P = 2 * R + 5, S = 2 * R + 1;
+// du/dv on the (2R+1)^2 pixels around (cx, cy) of one frame; R = 2 (anchor) or 4 (target).
+// Patch rows arrive as aligned 32-bit words (<= 4 per row).  A lane owns one output column and a segment of three
+// output rows: it walks the 7 patch rows under them once, keeping the horizontal 5-tap sums of the last five rows in
+// registers (the separable form of the reference's dense 5x5 sums -- same integers).
+template <int R>
+__device__ __forceinline__ void responses(K5Warp& w, const uint8_t* __restrict__ img, int pitch, int cx, int cy, int lane) {
+  constexpr int P = 2 * R + 5, S = 2 * R + 1, NSEG = (S + 2) / 3, WPR = (P + 3 + 3) / 4;  // words per row
+  const int x0 = cx - R - 2, off = x0 & 3;
+  const uint8_t* src = img + (int64_t)(cy - R - 2) * pitch + (x0 - off);
   __syncwarp();
-  for (int i = lane; i < P * P; i += 32) {
-    const int r = i / P, c = i - r * P;
-    w.patch[r * 16 + c] = img[(int64_t)(cy - R - 2 + r) * pitch + (cx - R - 2 + c)];
+  for (int i = lane; i < P * WPR; i += 32) {
+    const int r = i / WPR, j = i - r * WPR;
+    *reinterpret_cast<uint32_t*>(&w.patch[r * 16 + 4 * j]) = *reinterpret_cast<const uint32_t*>(src + (int64_t)r * pitch + 4 * j);
   }
   __syncwarp();
-  for (int i = lane; i < S * S; i += 32) {
-    const int r = i / S, c = i - r * S;
-    int h[5], s[5];  // per patch row: derivative [1 2 0 -2 -1] and smoothing [1 4 6 4 1] along x
+  if (lane < S * NSEG) {
+    const int seg = lane / S, c = lane - seg * S, r0 = 3 * seg;
+    int h[7], sm[7];  // per patch row: derivative [1 2 0 -2 -1] and smoothing [1 4 6 4 1] along x
 #pragma unroll
-    for (int k = 0; k < 5; k++) {
-      const uint8_t* p = &w.patch[(r + k) * 16 + c];
+    for (int k = 0; k < 7; k++) {
+      const uint8_t* p = &w.patch[min(r0 + k, P - 1) * 16 + off + c];
       const int a = p[0], b = p[1], m = p[2], d = p[3], e = p[4];
       h[k] = a + 2 * b - 2 * d - e;
-      s[k] = a + 4 * b + 6 * m + 4 * d + e;
+      sm[k] = a + 4 * b + 6 * m + 4 * d + e;
     }
-    w.du[i] = sobel_u8(h[0] + 4 * h[1] + 6 * h[2] + 4 * h[3] + h[4]);   // v_weight, src/myComputeFeature.cpp:59-65
-    w.dv[i] = sobel_u8(s[0] + 2 * s[1] - 2 * s[3] - s[4]);              // h_weight, src/myComputeFeature.cpp:66-72
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+      if (r0 + k < S) {
+        w.du[(r0 + k) * S + c] = sobel_u8(h[k] + 4 * h[k + 1] + 6 * h[k + 2] + 4 * h[k + 3] + h[k + 4]);  // v_weight, src/myComputeFeature.cpp:59-65
+        w.dv[(r0 + k) * S + c] = sobel_u8(sm[k] + 2 * sm[k + 1] - 2 * sm[k + 3] - sm[k + 4]);             // h_weight, src/myComputeFeature.cpp:66-72
+      }
   }
   __syncwarp();
 }
 
-// one parabolicFitting call: anchor descriptor in w.d1, target frame `img`, (u2, v2) updated by lane 0's result
-__device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const uint8_t* __restrict__ img, float& u2, float& v2,
-                                           int lane) {
+// |a - b| + acc on zero-extended bytes: one VABSDIFF4
+__device__ __forceinline__ uint32_t absdiff_acc(uint32_t a, uint32_t b, uint32_t acc) {
+  uint32_t d;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
+  return d;
+}
+
+// one parabolicFitting call: anchor descriptor in d1[] (registers), target frame `img`, (u2, v2) updated
+__device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const uint8_t* __restrict__ img, const uint32_t (&d1)[16],
+                                           float& u2, float& v2, int lane) {
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   const float margin = 7.f;  // src/matcher.cpp:38
   if (u2 - 2.f < margin || u2 + 2.f > (float)(g.W - 1) - margin || v2 - 2.f < margin || v2 + 2.f > (float)(g.H - 1) - margin)
     return false;
-  responses(w, img, g.pitch, (int)u2, (int)v2, 4, lane);
+  responses<4>(w, img, g.pitch, (int)u2, (int)v2, lane);
   int cost = 0x7FFFFF;
   if (lane < 25) {
     const int a = lane % 5, b = lane / 5;
-    cost = 0;
+    const uint8_t* pu = &w.du[(2 + b) * kResp + (2 + a)];
+    const uint8_t* pv = &w.dv[(2 + b) * kResp + (2 + a)];
+    uint32_t c = 0;
 #pragma unroll
     for (int s = 0; s < 16; s++) {
-      const int idx = (4 + b - 2 + c_small_dy[s]) * kResp + (4 + a - 2 + c_small_dx[s]);
-      const int val = (s < 12) ? w.du[idx] : w.dv[idx];
-      cost += abs((int)w.d1[s] - val);
+      const int idx = c_small_dy[s] * kResp + c_small_dx[s];
+      c = absdiff_acc(d1[s], (s < 12) ? pu[idx] : pv[idx], c);
     }
+    cost = (int)c;
   }
   const int best = __reduce_min_sync(FULL, cost * 32 + lane);  // first minimum in raster order
   const int mi = best & 31, a0 = mi % 5, b0 = mi / 5;
   if (a0 == 0 || a0 == 4 || b0 == 0 || b0 == 4) return false;
-  long long P = 0, Q = 0, R = 0, B2 = 0, B3 = 0, B4 = 0;
+  // every intermediate below is an integer of magnitude < 2^53, so double arithmetic is exact (see the oracle for the bounds)
+  int P = 0, Q = 0, R = 0, B2 = 0, B3 = 0, B4 = 0;
 #pragma unroll
   for (int i = -1; i <= 1; i++)
 #pragma unroll
     for (int j = -1; j <= 1; j++) {
-      const long long c = __shfl_sync(FULL, cost, (b0 + i) * 5 + (a0 + j));
+      const int c = __shfl_sync(FULL, cost, (b0 + i) * 5 + (a0 + j));
       P += j * j * c; Q += i * i * c; R += c; B2 += i * j * c; B3 += j * c; B4 += i * c;
     }
-  const long long B0 = 3 * P - 2 * R, B1 = 3 * Q - 2 * R;
-  const long long D = 9 * B2 * B2 - 16 * B0 * B1, NV = 8 * B0 * B4 - 6 * B2 * B3;
-  if (D == 0 || B2 == 0) return false;
-  const float ddv = (float)__ddiv_rn((double)NV, (double)D);
-  const float ddu = (float)__ddiv_rn((double)(-2 * (B4 * D + 2 * B1 * NV)), (double)(3 * B2 * D));
+  if (B2 == 0) return false;
+  const double b0d = (double)(3 * P - 2 * R), b1d = (double)(3 * Q - 2 * R), b2d = (double)B2, b3d = (double)B3, b4d = (double)B4;
+  const double D = 9.0 * b2d * b2d - 16.0 * b0d * b1d, NV = 8.0 * b0d * b4d - 6.0 * b2d * b3d;
+  if (D == 0.0) return false;
+  const float ddv = (float)__ddiv_rn(NV, D);
+  const float ddu = (float)__ddiv_rn(-2.0 * (b4d * D + 2.0 * b1d * NV), 3.0 * b2d * D);
   if (fabsf(ddu) >= 1.0f || fabsf(ddv) >= 1.0f) return false;
   u2 = (float)__dadd_rn((double)u2, __dadd_rn((double)(a0 - 2), (double)ddu));
   v2 = (float)__dadd_rn((double)v2, __dadd_rn((double)(b0 - 2), (double)ddv));
@@ -104,7 +123,7 @@ __device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const uint8
 }
 
 // quads[item] = {1p, 2p, 1c, 2c} slots (2p/2c = -1 for flow lists)
-__global__ void __launch_bounds__(K5_WARPS * 32)
+__global__ void __launch_bounds__(K5_WARPS * 32, 3)
 k5_refine(Geom g, FrameArrays fa, const int4* __restrict__ quads, float* __restrict__ lists, int64_t stride_matches,
           const int32_t* __restrict__ n_list, uint8_t* __restrict__ keep) {
   __shared__ K5Warp sw[K5_WARPS];
@@ -121,16 +140,17 @@ k5_refine(Geom g, FrameArrays fa, const int4* __restrict__ quads, float* __restr
     const int cx = (int)u1c, cy = (int)v1c;
     bool ok = cx >= 4 && cy >= 4 && cx <= g.W - 5 && cy <= g.H - 5;  // the anchor's descriptor must lie inside the image
     if (ok) {
-      responses(w, fa.img + (int64_t)qd.z * fa.img_stride, g.pitch, cx, cy, 2, lane);
-      if (lane < 16) {
-        const int idx = (2 + c_small_dy[lane]) * 5 + (2 + c_small_dx[lane]);
-        w.d1[lane] = (lane < 12) ? w.du[idx] : w.dv[idx];
+      responses<2>(w, fa.img + (int64_t)qd.z * fa.img_stride, g.pitch, cx, cy, lane);
+      uint32_t d1[16];  // the anchor's small descriptor, zero-extended bytes (every lane holds all 16)
+#pragma unroll
+      for (int s = 0; s < 16; s++) {
+        const int idx = (2 + c_small_dy[s]) * 5 + (2 + c_small_dx[s]);
+        d1[s] = (s < 12) ? w.du[idx] : w.dv[idx];
       }
-      __syncwarp();
-      ok = fit_target(w, g, fa.img + (int64_t)qd.x * fa.img_stride, u1p, v1p, lane);
+      ok = fit_target(w, g, fa.img + (int64_t)qd.x * fa.img_stride, d1, u1p, v1p, lane);
       if (ok && u2c >= 0.f && qd.y >= 0 && qd.w >= 0)
-        ok = fit_target(w, g, fa.img + (int64_t)qd.w * fa.img_stride, u2c, v2c, lane) &&
-             fit_target(w, g, fa.img + (int64_t)qd.y * fa.img_stride, u2p, v2p, lane);
+        ok = fit_target(w, g, fa.img + (int64_t)qd.w * fa.img_stride, d1, u2c, v2c, lane) &&
+             fit_target(w, g, fa.img + (int64_t)qd.y * fa.img_stride, d1, u2p, v2p, lane);
     }
     __syncwarp();
     if (lane == 0) {
