@@ -283,15 +283,29 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int smin = max(__reduce_min_sync(FULL, valid ? v : kBig), ra);
         const int smax = min(__reduce_max_sync(FULL, valid ? v : -1), rb - 1);
         uint32_t k1 = kNone;
-        for (int r = smin; r <= smax; r++) {
-          const int p1 = t.segOff[r][jown + 1];
-          for (int p = t.segOff[r][jown]; p < p1; p += 4) {  // bin lists are padded to 4
-            const uint4 qq = Q4[p >> 2];
-            const uint32_t ka = (uint32_t)sadq(qa, qq.x) * 0x100000u + (uint32_t)p;
-            const uint32_t kb = (uint32_t)sadq(qa, qq.y) * 0x100000u + (uint32_t)(p + 1);
-            const uint32_t kc = (uint32_t)sadq(qa, qq.z) * 0x100000u + (uint32_t)(p + 2);
-            const uint32_t kd = (uint32_t)sadq(qa, qq.w) * 0x100000u + (uint32_t)(p + 3);
-            k1 = min(k1, min(min(ka, kb), min(kc, kd)));
+        if (reach >= kMaxV) {  // flow edge: the +-135-row window admits practically every candidate of the own bin
+          for (int r = smin; r <= smax; r++) {
+            const int p1 = t.segOff[r][jown + 1];
+            for (int p = t.segOff[r][jown]; p < p1; p += 4) {  // bin lists are padded to 4
+              const uint4 qq = Q4[p >> 2];
+              const uint32_t ka = (uint32_t)sadq(qa, qq.x) * 0x100000u + (uint32_t)p;
+              const uint32_t kb = (uint32_t)sadq(qa, qq.y) * 0x100000u + (uint32_t)(p + 1);
+              const uint32_t kc = (uint32_t)sadq(qa, qq.z) * 0x100000u + (uint32_t)(p + 2);
+              const uint32_t kd = (uint32_t)sadq(qa, qq.w) * 0x100000u + (uint32_t)(p + 3);
+              k1 = min(k1, min(min(ka, kb), min(kc, kd)));
+            }
+          }
+        } else {  // narrow (left<->right) edge: only candidates inside the +-rad_v rows can seed; a disparity may cross
+                  // into the neighbouring bins, so the own row's bins jown-1 .. jown+1 are searched
+          const int ja = max(jown - 1, j0), jb = min(jown + 2, j1);
+          for (int r = smin; r <= smax; r++) {
+            const int p1 = t.segOff[r][jb];
+            for (int p = t.segOff[r][ja]; p < p1; p++) {
+              const uint32_t x = S.xr[p].x;
+              const uint32_t t1 = x - lo_p, t2 = x - hi_p;
+              const uint32_t kq = (uint32_t)sadq(qa, S.q[p]) * 0x100000u + (uint32_t)p;
+              k1 = min(k1, (((t1 & ~t2) & 0x80008000u) == 0x80008000u) ? kq : kNone);
+            }
           }
         }
         if (k1 != kNone && vlo < vhi) {
