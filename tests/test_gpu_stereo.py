@@ -239,3 +239,46 @@ def test_stereo_process_loop_on_a_rendered_rig(tmp_path):
                          capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr
     assert [int(re.search(r"Matches: (\d+)", l).group(1)) for l in out.stdout.splitlines() if "Matches:" in l] == counts
+
+
+@pytest.mark.parametrize("name", ["holes", "periodic", "dense", "dead_zone_only", "tiny_patch", "low_contrast", "big_motion", "flat"])
+@pytest.mark.parametrize("size", [(1024, 284), (500, 150)])
+def test_quad_adversarial_vs_oracle(name, size):
+    """the mono path's adversarial frame pairs (tests/cases.py: lagging v_bin, first-wins ties, dead column/row, '<5 -> 0',
+    chunked windows) as the left camera of a rig whose right camera sees the same scene 11 px to the left, one row down"""
+    from cases import CASES
+    w, h = size
+    prev, curr = CASES[name](w, h, seed=2)
+    shift = lambda img: np.ascontiguousarray(np.roll(np.roll(img, -11, axis=1), 1, axis=0))
+    frames = [prev, shift(prev), curr, shift(curr)]                       # slots 1p, 2p, 1c, 2c
+    orc = Oracle(w, h)
+    f = [_feats(orc, x) for x in frames]
+    want = orc.quad_matching(f[0], f[1], f[2], f[3], 2)
+    eng = Engine(w, h, max_frames=4, max_pairs=1, stereo=True)
+    try:
+        eng.batch_extract_host(0, np.stack(frames))
+        eng.batch_match_quad([0], [1], [2], [3], disp_tolerance=2, refinement=0, max_features=2)
+        got = eng.batch_get_matches(0, 0)
+        assert len(got) == len(want) and matches_digest(got) == matches_digest(want)
+        assert matches_digest(eng.batch_get_matches(0, 1)) == matches_digest(orc.bucket_features(want, 2, 50.0, 50.0))
+        eng.batch_refine(1)
+        wr = orc.refine(want, frames[0], frames[2], frames[1], frames[3])
+        assert eng.batch_get_matches(0, 0).tobytes() == wr.tobytes()
+    finally:
+        eng.close()
+
+
+def test_quad_tall_frames_row_groups():
+    """2048x1024 (V = 23: origin rows are split into groups of 8 per CTA, windows staged in chunks) on a dense texture"""
+    w, h = 2048, 1024
+    left, right, orc, fl, fr = _quad_case(w, h, 1, 21, n=2, blur_passes=4)
+    eng = Engine(w, h, max_frames=4, max_pairs=1, stereo=True)
+    try:
+        eng.batch_extract_host(0, left)
+        eng.batch_extract_host(2, right)
+        eng.batch_match_quad([0], [2], [1], [3], disp_tolerance=2, refinement=2)
+        want = orc.refine(orc.quad_matching(fl[0], fr[0], fl[1], fr[1], 2, cap=1 << 19), left[0], left[1], right[0], right[1])
+        got = eng.batch_get_matches(0, 0)
+        assert len(want) > 50000 and got.tobytes() == want.tobytes()
+    finally:
+        eng.close()
