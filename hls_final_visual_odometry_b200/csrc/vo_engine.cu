@@ -92,6 +92,14 @@ struct vo_engine {
   int4* h_edges = nullptr;              // pinned
   int4* d_quads = nullptr;              // [n_pairbuf] {1p, 2p, 1c, 2c} slots of the last match call (2p = 2c = -1: flow)
   int4* h_quads = nullptr;              // pinned
+  // The three pinned tables above are read by ASYNCHRONOUS copies, and a pipelined caller (bench.py's e2e loop) fills
+  // the next call's tables while the previous copy has not run yet: they rotate through kStageGens generations, each
+  // guarded by an event recorded after its copies (stage_begin / stage_end).
+  static constexpr int kStageGens = 4;
+  int2* h_pairs_base = nullptr; int4* h_edges_base = nullptr; int4* h_quads_base = nullptr;
+  cudaEvent_t stage_done[kStageGens] = {nullptr, nullptr, nullptr, nullptr};
+  bool stage_used[kStageGens] = {false, false, false, false};
+  int stage_gen = 0;
   uint32_t* d_qxy = nullptr;            // stereo engines: partner coordinates per current-left feature (k3q_flags)
   uint8_t* d_keep = nullptr;            // refinement: keep flag per match
   std::vector<uint8_t> slot_has_image;  // frame bytes resident in the slot (not when extraction read caller memory in place)
@@ -276,7 +284,25 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
   return VO_OK;
 }
 
+// next generation of the pinned pair/edge/quad tables; blocks only if the host runs kStageGens calls ahead of the GPU
+vo_status stage_begin(vo_engine* e) {
+  e->stage_gen = (e->stage_gen + 1) % vo_engine::kStageGens;
+  const int gi = e->stage_gen;
+  if (e->stage_used[gi]) CU_TRY(cudaEventSynchronize(e->stage_done[gi]));
+  e->h_pairs = e->h_pairs_base + (int64_t)gi * e->n_pairbuf;
+  e->h_edges = e->h_edges_base + (int64_t)gi * e->n_pairbuf * e->epi;
+  e->h_quads = e->h_quads_base + (int64_t)gi * e->n_pairbuf;
+  return VO_OK;
+}
+vo_status stage_end(vo_engine* e) {
+  CU_TRY(cudaEventRecord(e->stage_done[e->stage_gen], e->stream));
+  e->stage_used[e->stage_gen] = true;
+  return VO_OK;
+}
+
 vo_status set_pairs(vo_engine* e, int pair0, int n, const int32_t* prev, const int32_t* curr) {
+  vo_status sb = stage_begin(e);
+  if (sb != VO_OK) return sb;
   for (int i = 0; i < n; i++) {
     if (prev[i] < 0 || prev[i] >= e->n_slots || curr[i] < 0 || curr[i] >= e->n_slots)
       return fail(VO_ERR_INVALID, "pair %d: slot out of range", i);
@@ -290,7 +316,7 @@ vo_status set_pairs(vo_engine* e, int pair0, int n, const int32_t* prev, const i
   CU_TRY(cudaMemcpyAsync(e->d_edges + 2 * pair0, e->h_edges + 2 * pair0, sizeof(int4) * 2 * n, cudaMemcpyHostToDevice, e->stream));
   CU_TRY(cudaMemcpyAsync(e->d_quads + pair0, e->h_quads + pair0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->stream));
   e->last_was_quad = false;
-  return VO_OK;
+  return stage_end(e);
 }
 
 // EXTENSION (row F3): sub-pixel refinement of the raw lists of items [item0, item0 + n) in place
@@ -299,8 +325,8 @@ vo_status do_refine(vo_engine* e, int item0, int n_items, int32_t max_n) {
     const int4 q = e->h_quads[item0 + i];
     for (int s : {q.x, q.y, q.z, q.w})
       if (s >= 0 && !e->slot_has_image[s])
-        return fail(VO_ERR_STATE, "refinement needs the frame of slot %d resident in the engine (it was extracted in place "
-                    "from caller memory by vo_batch_extract_device)", s);
+        return fail(VO_ERR_STATE, "refinement needs the frame of slot %d resident in the engine (the slot was never filled, or "
+                    "it was extracted in place from caller memory by vo_batch_extract_device)", s);
   }
   if (!e->d_keep) {
     cudaError_t ce = cudaMalloc((void**)&e->d_keep, (size_t)e->n_pairbuf * e->cfg.max_matches);
@@ -356,6 +382,8 @@ vo_status set_quads(vo_engine* e, int item0, int n, const int32_t* s1p, const in
                     const int32_t* s2c, int disp_tolerance) {
   if (e->epi != 4) return fail(VO_ERR_STATE, "quad matching needs an engine created with vo_config.stereo = 1");
   if (disp_tolerance < 0 || disp_tolerance > 16) return fail(VO_ERR_INVALID, "match_disp_tolerance %d outside [0,16]", disp_tolerance);
+  vo_status sb = stage_begin(e);
+  if (sb != VO_OK) return sb;
   for (int i = 0; i < n; i++) {
     for (int s : {s1p[i], s2p[i], s1c[i], s2c[i]})
       if (s < 0 || s >= e->n_slots) return fail(VO_ERR_INVALID, "item %d: slot out of range", i);
@@ -371,7 +399,7 @@ vo_status set_quads(vo_engine* e, int item0, int n, const int32_t* s1p, const in
   CU_TRY(cudaMemcpyAsync(e->d_edges + 4 * item0, e->h_edges + 4 * item0, sizeof(int4) * 4 * n, cudaMemcpyHostToDevice, e->stream));
   CU_TRY(cudaMemcpyAsync(e->d_quads + item0, e->h_quads + item0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->stream));
   e->last_was_quad = true;
-  return VO_OK;
+  return stage_end(e);
 }
 
 vo_status ensure(int32_t** p, size_t* have, size_t need) {
@@ -515,13 +543,20 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
       return fail(VO_ERR_CUDA, "lfsr upload");
     }
   }
-  if (cudaMallocHost((void**)&e->h_edges, sizeof(int4) * P * e->epi) != cudaSuccess ||
-      cudaMallocHost((void**)&e->h_quads, sizeof(int4) * P) != cudaSuccess ||
-      cudaMallocHost((void**)&e->h_pairs, sizeof(int2) * P) != cudaSuccess ||
+  {
+    bool ok = true;
+    for (auto& ev : e->stage_done) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "staging event create"); }
+  }
+  if (cudaMallocHost((void**)&e->h_edges_base, sizeof(int4) * P * e->epi * vo_engine::kStageGens) != cudaSuccess ||
+      cudaMallocHost((void**)&e->h_quads_base, sizeof(int4) * P * vo_engine::kStageGens) != cudaSuccess ||
+      cudaMallocHost((void**)&e->h_pairs_base, sizeof(int2) * P * vo_engine::kStageGens) != cudaSuccess ||
       cudaMallocHost((void**)&e->h_counts, sizeof(int32_t) * (2 * P + 4)) != cudaSuccess) {
     vo_engine_destroy(e);
     return fail(VO_ERR_CUDA, "pinned alloc");
   }
+  e->h_pairs = e->h_pairs_base; e->h_edges = e->h_edges_base; e->h_quads = e->h_quads_base;
+  for (int64_t i = 0; i < P * vo_engine::kStageGens; i++) e->h_quads_base[i] = make_int4(-1, -1, -1, -1);
   vo_status s = make_tmap(&e->tmap_slots, e->fa.img, g.W, g.H, (int)S, g.pitch, e->fa.img_stride);
   if (s != VO_OK) { vo_engine_destroy(e); return s; }
   if (cudaStreamSynchronize(e->stream) != cudaSuccess) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "init sync"); }
@@ -543,9 +578,10 @@ void vo_engine_destroy(vo_engine* e) {
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
   cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);
   cudaFree(e->d_edges); cudaFree(e->d_quads); cudaFree(e->d_qxy); cudaFree(e->d_keep);
-  if (e->h_edges) cudaFreeHost(e->h_edges);
-  if (e->h_quads) cudaFreeHost(e->h_quads);
-  if (e->h_pairs) cudaFreeHost(e->h_pairs);
+  if (e->h_edges_base) cudaFreeHost(e->h_edges_base);
+  if (e->h_quads_base) cudaFreeHost(e->h_quads_base);
+  if (e->h_pairs_base) cudaFreeHost(e->h_pairs_base);
+  for (auto& ev : e->stage_done) if (ev) cudaEventDestroy(ev);
   if (e->h_counts) cudaFreeHost(e->h_counts);
   for (auto& ev : e->evs) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
   if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);

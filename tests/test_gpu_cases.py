@@ -236,3 +236,31 @@ def test_engine_remove_outliers_with_real_outliers():
         assert_matches_equal(eng.get_matches(), want, "bucketed after removeOutliers")
     finally:
         eng.close()
+
+
+def test_back_to_back_async_batches_keep_their_own_pair_tables():
+    """A pipelined caller (bench.py's e2e loop) enqueues the next batch while the previous one has not started: the pinned
+    pair/edge tables behind the asynchronous copies must not be shared between calls in flight."""
+    from hls_final_visual_odometry_b200 import pinned_empty
+    w, h, n = 500, 150, 4
+    seq = make_sequence(w, h, n, seed=12)
+    seq[3] = seq[3][::-1].copy()                             # an unrelated frame: pairs (0,1) and (2,3) give different counts
+    eng = Engine(w, h, max_frames=n, max_pairs=1)
+    try:
+        eng.batch_extract_host(0, seq)
+        want = {}
+        for pr in ((0, 1), (2, 3)):
+            eng.batch_match([pr[0]], [pr[1]])
+            want[pr] = int(eng.batch_counts(1)[0][0])
+        assert want[(0, 1)] != want[(2, 3)]
+        counts = pinned_empty((16, 2), np.int32)
+        counts[:] = -1
+        eng.synchronize()
+        for it in range(16):                                 # no host synchronisation between the calls
+            pr = (0, 1) if it % 2 == 0 else (2, 3)
+            eng.batch_match([pr[0]], [pr[1]])
+            eng.batch_download_async(1, 0, counts[it], None, 0, 0)
+        eng.synchronize()
+        assert [int(c) for c in counts[:, 0]] == [want[(0, 1)] if it % 2 == 0 else want[(2, 3)] for it in range(16)]
+    finally:
+        eng.close()
