@@ -7,6 +7,7 @@
 #include <cuda.h>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -92,17 +93,29 @@ struct vo_engine {
   int4* h_edges = nullptr;              // pinned
   int4* d_quads = nullptr;              // [n_pairbuf] {1p, 2p, 1c, 2c} slots of the last match call (2p = 2c = -1: flow)
   int4* h_quads = nullptr;              // pinned
-  // The three pinned tables above are read by ASYNCHRONOUS copies, and a pipelined caller (bench.py's e2e loop) fills
-  // the next call's tables while the previous copy has not run yet: they rotate through kStageGens generations, each
-  // guarded by an event recorded after its copies (stage_begin / stage_end).
+  // The pair/edge/quad tables (pinned host copy + device copy) rotate through kStageGens generations.  Host side: they
+  // are read by ASYNCHRONOUS copies, and a pipelined caller (bench.py's e2e loop) fills the next call's tables while the
+  // previous copy has not run yet.  Device side: the copies travel on the UPLOAD stream, behind the frame upload of the
+  // same step -- on the compute stream they would queue on the H2D copy engine behind the next step's 60 MB upload and
+  // stall the kernels for a millisecond (measured: e2e 64k -> 47k pairs/s) -- so a generation's device table may only
+  // be rewritten once the kernels that read it are done (stage_begin / stage_end).
   static constexpr int kStageGens = 4;
   int2* h_pairs_base = nullptr; int4* h_edges_base = nullptr; int4* h_quads_base = nullptr;
-  cudaEvent_t stage_done[kStageGens] = {nullptr, nullptr, nullptr, nullptr};
+  int2* d_pairs_base = nullptr; int4* d_edges_base = nullptr; int4* d_quads_base = nullptr;
+  cudaEvent_t stage_done[kStageGens] = {nullptr, nullptr, nullptr, nullptr};   // copies of the generation done (upload stream)
+  cudaEvent_t stage_idle[kStageGens] = {nullptr, nullptr, nullptr, nullptr};   // kernels reading the generation enqueued up to here
   bool stage_used[kStageGens] = {false, false, false, false};
   int stage_gen = 0;
   uint32_t* d_qxy = nullptr;            // stereo engines: partner coordinates per current-left feature (k3q_flags)
   uint8_t* d_keep = nullptr;            // refinement: keep flag per match
   std::vector<uint8_t> slot_has_image;  // frame bytes resident in the slot (not when extraction read caller memory in place)
+  // Kernels that read slot IMAGES (K1 always, K5 for the frames of its items): an upload on the copy stream into a slot
+  // waits for exactly the recent readers of that slot, so uploads into other slots overlap them.  A record pushed out of
+  // the ring makes the copy stream wait for it unconditionally (the copy stream is FIFO, so that holds for good).
+  struct ImgReader { cudaEvent_t ev = nullptr; std::vector<uint8_t> slots; bool used = false; };
+  static constexpr int kReaders = 8;
+  ImgReader readers[kReaders];
+  int reader_next = 0;
   int ring_r_prev = 2, ring_r_curr = 3; // stereo engines: right-image ring
   int right_pushed = 0;
   bool last_was_quad = false;
@@ -218,6 +231,19 @@ vo_status check_device_status(vo_engine* e) {
   return VO_OK;
 }
 
+// registers a kernel just launched on the compute stream as a reader of the images of the slots `mark` flags
+template <class Mark>
+vo_status note_image_reader(vo_engine* e, Mark mark) {
+  vo_engine::ImgReader& r = e->readers[e->reader_next];
+  e->reader_next = (e->reader_next + 1) % vo_engine::kReaders;
+  if (r.used) CU_TRY(cudaStreamWaitEvent(e->h2d_stream, r.ev, 0));
+  r.slots.assign((size_t)e->n_slots, 0);
+  mark(r.slots);
+  CU_TRY(cudaEventRecord(r.ev, e->stream));
+  r.used = true;
+  return VO_OK;
+}
+
 vo_status do_extract(vo_engine* e, const CUtensorMap& tm, int first_slot, int z_base, int n) {
   const vo::Geom& g = e->g;
   // v-bins the reference never flushes read as empty: clear all counts of the target slots
@@ -228,7 +254,8 @@ vo_status do_extract(vo_engine* e, const CUtensorMap& tm, int first_slot, int z_
     CU_TRY(vo::launch_k1(tm, g, e->fa, first_slot, z_base, n, e->stream));
     e->launches += 1;
   }
-  CU_TRY(cudaEventRecord(e->ev_k1_done, e->stream));  // the image slots may be overwritten from here on
+  if (&tm == &e->tmap_slots)  // (an extraction through a tensor map of caller memory reads no slot image)
+    return note_image_reader(e, [&](std::vector<uint8_t>& sl) { for (int i = 0; i < n; i++) sl[first_slot + i] = 1; });
   return VO_OK;
 }
 
@@ -286,16 +313,25 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
 
 // next generation of the pinned pair/edge/quad tables; blocks only if the host runs kStageGens calls ahead of the GPU
 vo_status stage_begin(vo_engine* e) {
+  CU_TRY(cudaEventRecord(e->stage_idle[e->stage_gen], e->stream));  // every kernel that reads the current tables is enqueued
   e->stage_gen = (e->stage_gen + 1) % vo_engine::kStageGens;
   const int gi = e->stage_gen;
-  if (e->stage_used[gi]) CU_TRY(cudaEventSynchronize(e->stage_done[gi]));
+  if (e->stage_used[gi]) {
+    CU_TRY(cudaEventSynchronize(e->stage_done[gi]));                 // host table: its last copy has run
+    CU_TRY(cudaStreamWaitEvent(e->h2d_stream, e->stage_idle[gi], 0));  // device table: its last readers are done
+  }
   e->h_pairs = e->h_pairs_base + (int64_t)gi * e->n_pairbuf;
   e->h_edges = e->h_edges_base + (int64_t)gi * e->n_pairbuf * e->epi;
   e->h_quads = e->h_quads_base + (int64_t)gi * e->n_pairbuf;
+  e->d_pairs = e->d_pairs_base + (int64_t)gi * e->n_pairbuf;
+  e->d_edges = e->d_edges_base + (int64_t)gi * e->n_pairbuf * e->epi;
+  e->d_quads = e->d_quads_base + (int64_t)gi * e->n_pairbuf;
   return VO_OK;
 }
+// after the table copies have been enqueued on the upload stream
 vo_status stage_end(vo_engine* e) {
-  CU_TRY(cudaEventRecord(e->stage_done[e->stage_gen], e->stream));
+  CU_TRY(cudaEventRecord(e->stage_done[e->stage_gen], e->h2d_stream));
+  CU_TRY(cudaStreamWaitEvent(e->stream, e->stage_done[e->stage_gen], 0));
   e->stage_used[e->stage_gen] = true;
   return VO_OK;
 }
@@ -312,9 +348,9 @@ vo_status set_pairs(vo_engine* e, int pair0, int n, const int32_t* prev, const i
     e->h_edges[2 * (pair0 + i) + 1] = make_int4(prev[i], curr[i], e->g.rad_v, kFlowReach);
     e->h_quads[pair0 + i] = make_int4(prev[i], -1, curr[i], -1);
   }
-  CU_TRY(cudaMemcpyAsync(e->d_pairs + pair0, e->h_pairs + pair0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemcpyAsync(e->d_edges + 2 * pair0, e->h_edges + 2 * pair0, sizeof(int4) * 2 * n, cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemcpyAsync(e->d_quads + pair0, e->h_quads + pair0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_pairs + pair0, e->h_pairs + pair0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->h2d_stream));
+  CU_TRY(cudaMemcpyAsync(e->d_edges + 2 * pair0, e->h_edges + 2 * pair0, sizeof(int4) * 2 * n, cudaMemcpyHostToDevice, e->h2d_stream));
+  CU_TRY(cudaMemcpyAsync(e->d_quads + pair0, e->h_quads + pair0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->h2d_stream));
   e->last_was_quad = false;
   return stage_end(e);
 }
@@ -337,7 +373,12 @@ vo_status do_refine(vo_engine* e, int item0, int n_items, int32_t max_n) {
                        e->cfg.max_matches, max_n, e->d_n_raw + item0, e->d_keep + (int64_t)item0 * e->cfg.max_matches,
                        e->stream));
   e->launches += 2;
-  return VO_OK;
+  return note_image_reader(e, [&](std::vector<uint8_t>& sl) {
+    for (int i = 0; i < n_items; i++) {
+      const int4 q = e->h_quads[item0 + i];
+      for (int s : {q.x, q.y, q.z, q.w}) if (s >= 0) sl[s] = 1;
+    }
+  });
 }
 
 // EXTENSION (row F3): quad matching of items [item0, item0 + n): four K2 edges, cycle + emit, optional refinement
@@ -395,9 +436,9 @@ vo_status set_quads(vo_engine* e, int item0, int n, const int32_t* s1p, const in
     e->h_edges[4 * k + 2] = make_int4(s2p[i], s2c[i], e->g.rad_v, kFlowReach);  // flow   2p -> 2c
     e->h_edges[4 * k + 3] = make_int4(s2c[i], s1c[i], disp_tolerance, 1);       // stereo 2c -> 1c
   }
-  CU_TRY(cudaMemcpyAsync(e->d_pairs + item0, e->h_pairs + item0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemcpyAsync(e->d_edges + 4 * item0, e->h_edges + 4 * item0, sizeof(int4) * 4 * n, cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemcpyAsync(e->d_quads + item0, e->h_quads + item0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_pairs + item0, e->h_pairs + item0, sizeof(int2) * n, cudaMemcpyHostToDevice, e->h2d_stream));
+  CU_TRY(cudaMemcpyAsync(e->d_edges + 4 * item0, e->h_edges + 4 * item0, sizeof(int4) * 4 * n, cudaMemcpyHostToDevice, e->h2d_stream));
+  CU_TRY(cudaMemcpyAsync(e->d_quads + item0, e->h_quads + item0, sizeof(int4) * n, cudaMemcpyHostToDevice, e->h2d_stream));
   e->last_was_quad = true;
   return stage_end(e);
 }
@@ -491,6 +532,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
               cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking) == cudaSuccess;
     cudaEvent_t* evs[4] = {&e->ev_h2d_done, &e->ev_k1_done, &e->ev_compute_done, &e->ev_d2h_done};
     for (auto ev : evs) ok = ok && cudaEventCreateWithFlags(ev, cudaEventDisableTiming) == cudaSuccess;
+    for (auto& r : e->readers) ok = ok && cudaEventCreateWithFlags(&r.ev, cudaEventDisableTiming) == cudaSuccess;
     for (auto& f : e->fences) ok = ok && cudaEventCreateWithFlags(&f, cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "pipeline stream/event create"); }
   }
@@ -514,10 +556,11 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   cudaMemsetAsync(e->fa.cnt, 0, sizeof(int32_t) * S * e->fa.cnt_stride, e->stream);
   cudaMemsetAsync(e->fa.img, 0, (size_t)(S * e->fa.img_stride + 256), e->stream);
   const int64_t lists = (int64_t)g.U * 4 * g.col_cap;
-  ALLOC(e->d_pairs, sizeof(int2) * P);
+  ALLOC(e->d_pairs_base, sizeof(int2) * P * vo_engine::kStageGens);
   ALLOC(e->d_best, sizeof(uint32_t) * P * e->epi * lists);
-  ALLOC(e->d_edges, sizeof(int4) * P * e->epi);
-  ALLOC(e->d_quads, sizeof(int4) * P);
+  ALLOC(e->d_edges_base, sizeof(int4) * P * e->epi * vo_engine::kStageGens);
+  ALLOC(e->d_quads_base, sizeof(int4) * P * vo_engine::kStageGens);
+  e->d_pairs = e->d_pairs_base; e->d_edges = e->d_edges_base; e->d_quads = e->d_quads_base;
   if (cfg.stereo) ALLOC(e->d_qxy, sizeof(uint32_t) * 3 * P * lists);
   ALLOC(e->d_flags, (size_t)(P * lists));
   ALLOC(e->d_list_cnt, sizeof(int32_t) * P * g.U * 4);
@@ -546,6 +589,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   {
     bool ok = true;
     for (auto& ev : e->stage_done) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+    for (auto& ev : e->stage_idle) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "staging event create"); }
   }
   if (cudaMallocHost((void**)&e->h_edges_base, sizeof(int4) * P * e->epi * vo_engine::kStageGens) != cudaSuccess ||
@@ -573,15 +617,17 @@ void vo_engine_destroy(vo_engine* e) {
   if (e->d2h_stream) { cudaStreamSynchronize(e->d2h_stream); cudaStreamDestroy(e->d2h_stream); }
   for (cudaEvent_t ev : {e->ev_h2d_done, e->ev_k1_done, e->ev_compute_done, e->ev_d2h_done}) if (ev) cudaEventDestroy(ev);
   for (auto& f : e->fences) if (f) cudaEventDestroy(f);
+  for (auto& r : e->readers) if (r.ev) cudaEventDestroy(r.ev);
   cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc); cudaFree(e->fa.q);
-  cudaFree(e->d_pairs); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
+  cudaFree(e->d_pairs_base); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
   cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);
-  cudaFree(e->d_edges); cudaFree(e->d_quads); cudaFree(e->d_qxy); cudaFree(e->d_keep);
+  cudaFree(e->d_edges_base); cudaFree(e->d_quads_base); cudaFree(e->d_qxy); cudaFree(e->d_keep);
   if (e->h_edges_base) cudaFreeHost(e->h_edges_base);
   if (e->h_quads_base) cudaFreeHost(e->h_quads_base);
   if (e->h_pairs_base) cudaFreeHost(e->h_pairs_base);
   for (auto& ev : e->stage_done) if (ev) cudaEventDestroy(ev);
+  for (auto& ev : e->stage_idle) if (ev) cudaEventDestroy(ev);
   if (e->h_counts) cudaFreeHost(e->h_counts);
   for (auto& ev : e->evs) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
   if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
@@ -888,7 +934,13 @@ vo_status vo_batch_extract_host(vo_engine* e, int32_t first_slot, int32_t n, con
   CU_TRY(cudaSetDevice(e->device));
   // upload on the copy stream: it only has to wait for the last extraction that read the image
   // slots, so it overlaps the matching kernels of the previous batch
-  CU_TRY(cudaStreamWaitEvent(e->h2d_stream, e->ev_k1_done, 0));
+  for (const vo_engine::ImgReader& r : e->readers) {
+    if (!r.used) continue;
+    static const bool conservative = getenv("VO_CONSERVATIVE_UPLOAD") != nullptr;  // debugging aid: wait for every reader
+    bool hit = conservative;
+    for (int i = 0; i < n && !hit; i++) hit = r.slots[first_slot + i] != 0;
+    if (hit) CU_TRY(cudaStreamWaitEvent(e->h2d_stream, r.ev, 0));
+  }
   vo_status s = upload_images(e, first_slot, n, images, frame_stride_bytes, pitch_bytes, cudaMemcpyHostToDevice,
                               e->h2d_stream);
   if (s != VO_OK) return s;

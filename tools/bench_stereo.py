@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--refinement", type=int, default=2)
     ap.add_argument("--disparity", type=int, default=14)
     ap.add_argument("--cpu-pairs", type=int, default=2)
+    ap.add_argument("--no-profile", action="store_true", help="no per-kernel CUDA events in the timed loop")
     args = ap.parse_args()
     from hls_final_visual_odometry_b200 import Engine, pinned_empty
     from hls_final_visual_odometry_b200.synth import make_stereo_sequence
@@ -42,9 +43,11 @@ def main():
     hs = pinned_empty((pool // B, 2 * B, H, pitch), np.uint8)
     hs[:, :B, :, :W] = left.reshape(pool // B, B, H, W)
     hs[:, B:, :, :W] = right.reshape(pool // B, B, H, W)
-    # slots: step s fills half (s % 2) = slots [h*2B, h*2B + 2B): B left frames then B right frames; the H2D copy of step
-    # s+1 (upload stream) overlaps the kernels of step s, and the D2H of step s (download stream) those of step s+1
-    eng = Engine(W, H, max_frames=4 * B, max_pairs=B, stereo=True)
+    # slots: step s fills bank (s % 3) = slots [b*2B, b*2B + 2B): B left frames then B right frames.  Three banks, because
+    # step s still reads bank (s-1) % 3 (previous frame of its first item; the refinement reads its image): the H2D copy
+    # of step s+1 (upload stream) then touches nothing step s reads and overlaps all of its kernels; the D2H of step s
+    # (download stream) overlaps the kernels of step s+1
+    eng = Engine(W, H, max_frames=6 * B, max_pairs=B, stereo=True)
     cap = 512
     counts = [pinned_empty((2 * B,), np.int32) for _ in range(2)]
     lists = [pinned_empty((B, cap), eng.get_matches().dtype) for _ in range(2)]
@@ -55,27 +58,27 @@ def main():
         kept[0] += int(counts[buf][B:].sum())
 
     def step(sidx, first):
-        h, buf = sidx % 2, sidx % 2
-        lc = h * 2 * B + np.arange(B)                        # left current slots; the right ones are B further
+        bank, buf = sidx % 3, sidx % 2
+        lc = bank * 2 * B + np.arange(B)                     # left current slots; the right ones are B further
         lp = lc - 1
-        lp[0] = (1 - h) * 2 * B + B - 1                      # previous of the first frame: last left frame of the other half
+        lp[0] = ((sidx - 1) % 3) * 2 * B + B - 1             # previous of the first frame: last left frame of the previous bank
         blk = (sidx * B % pool) // B
-        eng.batch_extract_host(h * 2 * B, hs.ctypes.data + blk * 2 * B * H * pitch, 2 * B, H * pitch, pitch)
+        eng.batch_extract_host(bank * 2 * B, hs.ctypes.data + blk * 2 * B * H * pitch, 2 * B, H * pitch, pitch)
         eng.batch_match_quad(lp, lp + B, lc, lc + B, 2, args.refinement, 2, 50.0, 50.0)
         eng.batch_download_async(B, 1, counts[buf], lists[buf], cap, cap)
         eng.fence_record(buf)
         if sidx > first:
             consume(1 - buf)
 
-    # fill the other half first, so the very first pair has a resident previous frame
-    eng.batch_extract_host(2 * B, hs.ctypes.data + (pool // B - 1) * 2 * B * H * pitch, 2 * B, H * pitch, pitch)
+    # fill the bank before the first one, so the very first pair has a resident previous frame
+    eng.batch_extract_host(2 * 2 * B, hs.ctypes.data + (pool // B - 1) * 2 * B * H * pitch, 2 * B, H * pitch, pitch)
     nw = max(args.warmup, 3)
     for i in range(nw):
         step(i, 0)
     consume((nw - 1) % 2)
     eng.synchronize()
     raw_n, bk_n = eng.batch_counts(B)
-    eng.profile_enable(True)
+    eng.profile_enable(not args.no_profile)
     launches0 = eng.launch_count()
     t0 = time.perf_counter()
     for i in range(nw, nw + args.steps):
