@@ -7,7 +7,7 @@
 //   meta  u32 [bin_num][cap]             "twin": lower-class feature on the same pixel
 //                                        (class<<16 | index in its list) or 0xFFFFFFFF
 //   desc  uint4[bin_num][cap][2]         the 32 descriptor bytes in reference byte order
-//   q     u32 [bin_num][cap]             4 coded group sums of the descriptor (SAD lower bound, K2)
+//   q     uint2[bin_num][cap]            2 x 4 coded group sums of the descriptor (SAD lower bound, K2)
 // This is the reference's max2/max2_num (src/size.h:17-20) as padded SoA; vo_dump_features
 // converts back to the 12 x int32 AoS records for parity.
 #pragma once
@@ -37,7 +37,7 @@ struct FrameArrays {   // base pointers of slot 0; slot s is at + s * stride
   uint32_t* xy;   int64_t rec_stride;    // elements (bin_num*cap) -- shared by xy/meta
   uint32_t* meta;
   uint4* desc;                            // 2 * rec_stride uint4 per slot
-  uint32_t* q;                            // rec_stride u32 per slot: lower-bound signature (desc_q)
+  uint2* q;                               // rec_stride uint2 per slot: lower-bound signature (desc_q)
 };
 
 // destination v-bin of block-row origin j (see oracle/vo_oracle.c dest_v_bin;
@@ -48,28 +48,29 @@ __host__ __device__ inline int32_t dest_v_bin(const Geom& g, int32_t j) {
   return (flush_row <= g.j_last) ? r : g.v_rem;
 }
 
-// Lower-bound signature of a descriptor.  The 32 bytes are (du,dv) pairs of 16 sample points; the
-// four groups {du of samples 0..7}, {dv of 0..7}, {du of 8..15}, {dv of 8..15} partition them, so by
-// the triangle inequality  SAD(a,b) >= sum_g |S_g(a) - S_g(b)|  with S_g the group sums (<= 2040).
-// Each sum is coded into one byte by a monotone integer map f with f(S+1)-f(S) in {0,1} (unit steps
-// inside 1020 +- 64, where Sobel responses of real textures live; one step per 16 outside), so
-// |f(x) - f(y)| <= |x - y| and
-//   SAD(a,b) >= Q(a,b),   Q = sum_g |f(S_g(a)) - f(S_g(b))|  = ONE VABSDIFF4, no slack term.
+// Lower-bound signature of a descriptor: two 32-bit words, one per 16-byte half.  The 32 bytes are (du,dv) pairs of 16
+// sample points; the eight groups {du of samples 4h..4h+3}, {dv of samples 4h..4h+3}, h = 0..3, partition them, so by the
+// triangle inequality  SAD(a,b) >= sum_g |S_g(a) - S_g(b)|  with S_g the group sums (<= 1020).  Each sum is coded into
+// one byte by a monotone integer map f with f(S+1)-f(S) in {0,1} (unit steps inside [410, 610], where sums of four
+// Sobel responses live; one step per 16 outside), so |f(x) - f(y)| <= |x - y| and
+//   SAD(a,b) >= Q(a,b) = Q0 + Q1,   Q_h = sum over the 4 groups of half h of |f(S_g(a)) - f(S_g(b))| = ONE VABSDIFF4 each,
+// with no slack term; Q0 alone is a (weaker) bound as well.  K2 filters with Q0 and confirms with Q0 + Q1.
+// (r1c used four groups of 8 bytes in one word: on frames that are not bit-identical translations of each other --
+// sensor noise -- that bound let 11 % of the candidates through, this one 1.7 %; tools/noise_probe.py.)
 __host__ __device__ inline uint32_t sum_code(uint32_t s) {
-  const uint32_t lo = (s < 956u ? s : 956u) >> 4;                      // 0..59
-  const uint32_t mid = (s < 956u ? 956u : (s > 1084u ? 1084u : s)) - 956u;  // 0..128
-  const uint32_t hi = ((s > 1084u ? s : 1084u) - 1084u) >> 4;          // 0..59
-  return lo + mid + hi;                                                 // 0..246
+  const uint32_t lo = (s < 410u ? s : 410u) >> 4;                          // 0..25
+  const uint32_t mid = (s < 410u ? 410u : (s > 610u ? 610u : s)) - 410u;   // 0..200
+  const uint32_t hi = ((s > 610u ? s : 610u) - 610u) >> 4;                 // 0..25
+  return lo + mid + hi;                                                    // 0..250
 }
-// sums of the even (sh = 0: du) or odd (sh = 8: dv) bytes of four descriptor words
-__host__ __device__ inline uint32_t group_q(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, int sh) {
-  const uint32_t x = ((w0 >> sh) & 0x00FF00FFu) + ((w1 >> sh) & 0x00FF00FFu) + ((w2 >> sh) & 0x00FF00FFu) +
-                     ((w3 >> sh) & 0x00FF00FFu);
+// sums of the even (sh = 0: du) or odd (sh = 8: dv) bytes of two descriptor words
+__host__ __device__ inline uint32_t group_q(uint32_t w0, uint32_t w1, int sh) {
+  const uint32_t x = ((w0 >> sh) & 0x00FF00FFu) + ((w1 >> sh) & 0x00FF00FFu);
   return sum_code((x + (x >> 16)) & 0xFFFFu);
 }
-__host__ __device__ inline uint32_t desc_q(const uint4& a, const uint4& b) {
-  return group_q(a.x, a.y, a.z, a.w, 0) | (group_q(a.x, a.y, a.z, a.w, 8) << 8) | (group_q(b.x, b.y, b.z, b.w, 0) << 16) |
-         (group_q(b.x, b.y, b.z, b.w, 8) << 24);
+__host__ __device__ inline uint32_t half_q(const uint4& a) {
+  return group_q(a.x, a.y, 0) | (group_q(a.x, a.y, 8) << 8) | (group_q(a.z, a.w, 0) << 16) | (group_q(a.z, a.w, 8) << 24);
 }
+__host__ __device__ inline uint2 desc_q(const uint4& a, const uint4& b) { return make_uint2(half_q(a), half_q(b)); }
 
 }  // namespace vo

@@ -224,7 +224,7 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
   uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride;
   uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride;
   uint4* desc = fa.desc + (int64_t)slot * fa.rec_stride * 2;
-  uint32_t* qsig = fa.q + (int64_t)slot * fa.rec_stride;
+  uint2* qsig = fa.q + (int64_t)slot * fa.rec_stride;
   constexpr int sdx[16] = {-3, -3, -1, -1, 3, 3, 1, 1, -1, -1, 1, 1, -5, -5, 5, 5};
   constexpr int sdy[16] = {-1, 1, -1, 1, -1, 1, -1, 1, -5, 5, -5, 5, -3, 3, -3, 3};
   const int e1 = total[0], e2 = e1 + total[1], e3 = e2 + total[2], e4 = e3 + total[3];
@@ -284,7 +284,7 @@ __global__ void k_load_features(Geom g, FrameArrays fa, int slot, const int32_t*
   uint32_t* xy = fa.xy + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
   uint32_t* meta = fa.meta + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
   uint4* desc = fa.desc + ((int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap) * 2;
-  uint32_t* qsig = fa.q + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
+  uint2* qsig = fa.q + (int64_t)slot * fa.rec_stride + (int64_t)bin * g.cap;
   const int c = bin & 3;
   for (int k = threadIdx.x; k < n; k += blockDim.x) {
     const int32_t* rec = max2 + ((int64_t)bin * cap_stride + k) * 12;

@@ -18,6 +18,14 @@
 // "strict <, first candidate in (u_bin asc, col_idx asc) order wins".  The threshold is seeded
 // from the bins the origins themselves sit in (zero-flow prior).  Pruning is conservative, so the
 // result is identical to evaluating every SAD (PRUNE=false does that, for the tests).
+// The bound has two words (one per descriptor half, desc_q).  A warp whose origins found exact partners
+// (bit-identical patches: rendered or noise-free frames) filters with the first word only; a warp whose
+// seeds carry non-zero bounds (sensor noise) filters with both words -- twice the shared-memory reads, six
+// times fewer false hits -- and keeps its poorly seeded origins on the lane path.  Queued groups are
+// re-tested candidate by candidate with both words against the owner's CURRENT bound before an exact SAD
+// is spent.  Origins without a usable seed go to a warp-per-origin pass whose survivors are compacted
+// through the warp's queue so that exact SADs run 32 at a time (tools/noise_probe.py: 1.3-1.7x over the
+// one-word filter on noisy frames, -4 % on noise-free ones).
 // SAD is not a contraction: no tensor cores here by design.
 //
 // K3 (k3_flags, k3_emit): closed-cycle test, same-pixel dedupe (lowest class wins, via the twin
@@ -39,11 +47,13 @@ constexpr int kMaxCols = kOC + 5;  // staged target columns: [ub0-3, ub_last+3) 
 constexpr int kSegW = kMaxCols + 1;
 constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
 constexpr int kMaxWarps = 16;
+constexpr int kTwoWordVotes = 24;  // lanes with a non-zero seed bound that switch a warp's filter to both signature words
 constexpr int kQueue = 64;      // deferred exact evaluations per warp
 constexpr int kBig = 1 << 20;
 static_assert(kCandCap <= 2048, "k2 hard pass packs the staged position into 11 bits");
 constexpr int kHardCap = 2048;  // origins per chunk handed to the warp-per-origin pass
-constexpr int kHitBudget = 4;   // filter hits (groups of 4) a lane may queue before its origin is handed over
+constexpr int kSeedGood = 128;  // an origin whose seed SAD is above this has no partner worth a lane-per-origin walk: warp-per-origin pass
+constexpr int kHitBudget = 4;   // default of vo_config.match_hit_budget: filter hits (groups of 4) a lane may queue before its origin is handed over
 
 struct K2Tables {
   int32_t cntT[kMaxV][kSegW];         // target counts (row, staged column)
@@ -65,8 +75,10 @@ struct __align__(128) K2Smem {
   __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
   uint4 hi[kCandCap];                 // descriptor bytes 16..31
   uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
-  __align__(16) uint32_t q[kCandCap]; // 4 coded group sums (lower-bound filter); read four at a time
+  __align__(16) uint32_t q[kCandCap];  // signature word 0: 4 coded group sums of bytes 0..15 (first-level filter); read four at a time
+  __align__(16) uint32_t q1[kCandCap]; // signature word 1: bytes 16..31 (second level: Q0 + Q1)
 };
+static_assert(sizeof(K2Smem) <= 113 * 1024, "two K2 CTAs per SM need <= 113 KB each (227 KB minus the per-CTA reserve)");
 
 // acc + sum of |a_i - b_i| over the four packed bytes: one VABSDIFF4.U8.ACC
 __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) {
@@ -116,7 +128,7 @@ __device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 template <bool PRUNE, int THREADS>
 __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
                                            uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
-                                           int rows_per_group, int rad_v, int reach) {
+                                           int rows_per_group, int rad_v, int reach, int hit_budget) {
   constexpr int NW = THREADS / 32;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   K2Tables& t = S.t;
@@ -187,11 +199,12 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 
   const uint32_t* xy_from = fa.xy + (int64_t)from_slot * fa.rec_stride;
   const uint4* desc_from = fa.desc + (int64_t)from_slot * fa.rec_stride * 2;
-  const uint32_t* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
+  const uint2* q_from = fa.q + (int64_t)from_slot * fa.rec_stride;
   const uint32_t* xy_to = fa.xy + (int64_t)to_slot * fa.rec_stride;
   const uint4* desc_to = fa.desc + (int64_t)to_slot * fa.rec_stride * 2;
-  const uint32_t* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
+  const uint2* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
   const uint4* Q4 = reinterpret_cast<const uint4*>(S.q);
+  const uint4* Q14 = reinterpret_cast<const uint4*>(S.q1);
   uint32_t* sbest = S.sbest[warp];
   uint32_t* queue = S.queue[warp];
   const uint32_t lt_mask = (1u << lane) - 1u, lane16 = (uint32_t)lane << 16;
@@ -228,12 +241,15 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           S.lo[dst + k] = d0;
           S.hi[dst + k] = d1;
           S.xr[dst + k] = make_uint2(xy_to[src + k] + 0x80008000u, rank0 + (uint32_t)k);
-          S.q[dst + k] = q_to[src + k];
+          const uint2 qv = q_to[src + k];
+          S.q[dst + k] = qv.x;
+          S.q1[dst + k] = qv.y;
         } else {
           S.lo[dst + k] = make_uint4(0, 0, 0, 0);
           S.hi[dst + k] = make_uint4(0, 0, 0, 0);
           S.xr[dst + k] = make_uint2(kNone, kNone);
           S.q[dst + k] = kNone;
+          S.q1[dst + k] = kNone;
         }
       }
     }
@@ -253,7 +269,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       int v = r0, vlo = kBig, vhi = 0;
       uint32_t oxy = 0;
       uint4 a = make_uint4(0, 0, 0, 0), b = a;
-      uint32_t qa = 0;
+      uint32_t qa = 0, qb = 0;
       uint32_t bestk = kNone;
       if (valid) {
         while (t.prefO[cc][v + 1] <= o) v++;
@@ -261,7 +277,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         oxy = __ldg(&xy_from[rec]);
         a = __ldg(&desc_from[2 * rec]);
         b = __ldg(&desc_from[2 * rec + 1]);
-        qa = __ldg(&q_from[rec]);
+        const uint2 qo = __ldg(&q_from[rec]);
+        qa = qo.x; qb = qo.y;
         // lagging v_bin (src/myMatch.cpp:153-158): only the first origins after empty bins
         const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
         const int lo_r = max(max(max(vb - 3, 0), ra), v - reach);  // src/myMatch.cpp:92-93,99
@@ -283,27 +300,29 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int smin = max(__reduce_min_sync(FULL, valid ? v : kBig), ra);
         const int smax = min(__reduce_max_sync(FULL, valid ? v : -1), rb - 1);
         uint32_t k1 = kNone;
+        int sa = jown, sb = jown + 1;  // seed bins of the own rows
         if (reach >= kMaxV) {  // flow edge: the +-135-row window admits practically every candidate of the own bin
           for (int r = smin; r <= smax; r++) {
             const int p1 = t.segOff[r][jown + 1];
             for (int p = t.segOff[r][jown]; p < p1; p += 4) {  // bin lists are padded to 4
-              const uint4 qq = Q4[p >> 2];
-              const uint32_t ka = (uint32_t)sadq(qa, qq.x) * 0x100000u + (uint32_t)p;
-              const uint32_t kb = (uint32_t)sadq(qa, qq.y) * 0x100000u + (uint32_t)(p + 1);
-              const uint32_t kc = (uint32_t)sadq(qa, qq.z) * 0x100000u + (uint32_t)(p + 2);
-              const uint32_t kd = (uint32_t)sadq(qa, qq.w) * 0x100000u + (uint32_t)(p + 3);
+              const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
+              const uint32_t ka = sad4(qb, q1.x, sad4(qa, qq.x, 0u)) * 0x100000u + (uint32_t)p;
+              const uint32_t kb = sad4(qb, q1.y, sad4(qa, qq.y, 0u)) * 0x100000u + (uint32_t)(p + 1);
+              const uint32_t kc = sad4(qb, q1.z, sad4(qa, qq.z, 0u)) * 0x100000u + (uint32_t)(p + 2);
+              const uint32_t kd = sad4(qb, q1.w, sad4(qa, qq.w, 0u)) * 0x100000u + (uint32_t)(p + 3);
               k1 = min(k1, min(min(ka, kb), min(kc, kd)));
             }
           }
         } else {  // narrow (left<->right) edge: only candidates inside the +-rad_v rows can seed; a disparity may cross
                   // into the neighbouring bins, so the own row's bins jown-1 .. jown+1 are searched
           const int ja = max(jown - 1, j0), jb = min(jown + 2, j1);
+          sa = ja; sb = jb;
           for (int r = smin; r <= smax; r++) {
             const int p1 = t.segOff[r][jb];
             for (int p = t.segOff[r][ja]; p < p1; p++) {
               const uint32_t x = S.xr[p].x;
               const uint32_t t1 = x - lo_p, t2 = x - hi_p;
-              const uint32_t kq = (uint32_t)sadq(qa, S.q[p]) * 0x100000u + (uint32_t)p;
+              const uint32_t kq = sad4(qb, S.q1[p], sad4(qa, S.q[p], 0u)) * 0x100000u + (uint32_t)p;
               k1 = min(k1, (((t1 & ~t2) & 0x80008000u) == 0x80008000u) ? kq : kNone);
             }
           }
@@ -322,12 +341,13 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       bool handed = false;
       // An origin the filter cannot prune (no near-exact match: every candidate may still win) would
       // flood the queue; it leaves the lane-per-origin walk and is matched by a whole warp after the
-      // tasks of this chunk (k2_hard_origins).  It is matched from scratch there.
+      // tasks of this chunk.  It takes the best key found so far along (through best[]) as its starting bound.
       auto hand_over = [&]() {
         const int hs = atomicAdd(&S.hard_n, 1);
         hits = -kBig;  // once per task (if the list is full the origin stays on the queue path)
         if (hs < kHardCap) {
           S.hard[hs] = (uint16_t)((cc << 15) | o);
+          bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
           vlo = kBig; vhi = 0;
           handed = true;
           return true;
@@ -335,10 +355,15 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         return false;
       };
       K2STAT(0, valid ? 1 : 0);
-      K2STAT(1, (valid && vlo < vhi) ? 1 : 0);
       K2STAT(2, (valid && vlo < vhi && bestk == kNone) ? 1 : 0);
       K2STAT(3, (valid && vlo < vhi && bestk != kNone && (bestk >> 19) == 0) ? 1 : 0);
-      if (PRUNE && vlo < vhi && bestk == kNone) hand_over();  // no seed: every group would hit
+      // Filter width, chosen per warp: on clean frames most origins find an exact partner (bound 0) and the first
+      // signature word alone prunes everything; once sensor noise leaves the seeds with non-zero bounds the filter
+      // tests both words (twice the shared-memory reads, ~6x fewer false hits) and can afford to keep poorly seeded
+      // origins on the lane path.
+      const bool two = PRUNE && __popc(__ballot_sync(FULL, vlo < vhi && tq > 0)) > kTwoWordVotes;
+      K2STAT(1, (valid && two) ? 1 : 0);
+      if (PRUNE && vlo < vhi && (two ? bestk == kNone : tq > kSeedGood)) hand_over();  // no seed or a poor one: nearly every group would hit
 
       // exact SAD + window test of up to 32 queued (origin, group of 4 candidates) entries, one per
       // lane; the origin's record comes from its owner lane by shuffle, the result goes back
@@ -355,11 +380,16 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         ob.x = __shfl_sync(FULL, b.x, owner); ob.y = __shfl_sync(FULL, b.y, owner);
         ob.z = __shfl_sync(FULL, b.z, owner); ob.w = __shfl_sync(FULL, b.w, owner);
         const uint32_t olo = __shfl_sync(FULL, lo_p, owner), ohi = __shfl_sync(FULL, hi_p, owner);
+        const uint32_t oq = __shfl_sync(FULL, qa, owner), oq1 = __shfl_sync(FULL, qb, owner);
+        const int otq = __shfl_sync(FULL, tq, owner);  // the owner's bound NOW (it may have dropped since the group was queued)
         if (on) {
-          uint32_t k = cand_key(S, p, oa, ob, olo, ohi);
-          k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
-          k = min(k, cand_key(S, p + 2, oa, ob, olo, ohi));
-          k = min(k, cand_key(S, p + 3, oa, ob, olo, ohi));
+          // a group was queued because ONE of its four candidates may win: re-test each against the bound first
+          const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
+          uint32_t k = kNone;
+          if ((int)sad4(oq1, q1.x, sad4(oq, qq.x, 0u)) <= otq) k = cand_key(S, p, oa, ob, olo, ohi);
+          if ((int)sad4(oq1, q1.y, sad4(oq, qq.y, 0u)) <= otq) k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
+          if ((int)sad4(oq1, q1.z, sad4(oq, qq.z, 0u)) <= otq) k = min(k, cand_key(S, p + 2, oa, ob, olo, ohi));
+          if ((int)sad4(oq1, q1.w, sad4(oq, qq.w, 0u)) <= otq) k = min(k, cand_key(S, p + 3, oa, ob, olo, ohi));
           if (k != kNone) atomicMin(&sbest[owner], k);
         }
         __syncwarp();
@@ -378,7 +408,23 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         while (pg < pg1) {
           const int nb = min(32, pg1 - pg);
           uint32_t m = 0;  // MISS bits while filtering, newest group in bit 0
-          if (PRUNE) {
+          if (PRUNE && two) {
+            const uint4* qp = Q4 + pg;
+            const uint4* rp = Q14 + pg;
+            auto gmin = [&](const uint4& x, const uint4& y) {
+              return (int)min(min(sad4(qb, y.x, sad4(qa, x.x, 0u)), sad4(qb, y.y, sad4(qa, x.y, 0u))),
+                              min(sad4(qb, y.z, sad4(qa, x.z, 0u)), sad4(qb, y.w, sad4(qa, x.w, 0u))));
+            };
+            int i = 0;
+#pragma unroll 2
+            for (; i + 1 < nb; i += 2, qp += 2, rp += 2) {
+              const int ma = gmin(qp[0], rp[0]), mb = gmin(qp[1], rp[1]);
+              m = __funnelshift_l((uint32_t)(tqe - ma), m, 1);
+              m = __funnelshift_l((uint32_t)(tqe - mb), m, 1);
+            }
+            if (i < nb) m = __funnelshift_l((uint32_t)(tqe - gmin(qp[0], rp[0])), m, 1);
+            m = ~m;
+          } else if (PRUNE) {
             const uint4* qp = Q4 + pg;  // one uint4 = the signatures of one group of 4 candidates
             int i = 0;
 #pragma unroll 2
@@ -406,8 +452,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           if (PRUNE) {
             hits += __popc(m);
             K2STAT(4, __popc(m));
-            if (hits > kHitBudget) { K2STAT(6, tq == 0 ? 1 : 0); K2STAT(7, hits); }
-            if (hits > kHitBudget && hand_over()) { m = 0u; act = false; tqe = -1; K2STAT(5, 1); }
+            if (!two && hits > hit_budget && hand_over()) { m = 0u; act = false; tqe = -1; K2STAT(5, 1); }
           }
           const uint32_t gfirst = lane16 + (uint32_t)(pg + nb - 32);  // owner lane << 16 + group of bit 31 (mod 2^32)
           for (;;) {
@@ -447,34 +492,71 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
         const uint32_t oxy = __ldg(&xy_from[rec]);
         const uint4 a = __ldg(&desc_from[2 * rec]), b = __ldg(&desc_from[2 * rec + 1]);
-        const uint32_t qa = __ldg(&q_from[rec]);
+        const uint2 qo = __ldg(&q_from[rec]);
+        const uint32_t qa = qo.x, qb = qo.y;
         const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
         const int lo_r = max(max(max(vb - 3, 0), ra), v - reach), hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
         const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
         const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);
         const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
         uint32_t bk = kNone;
-        if (!first_chunk) {  // result of the earlier chunks
+        {  // the best key the lane-per-origin walk (and the earlier chunks) left in best[]
           const uint32_t prev = bo[o];
           if (prev != kNone) bk = prev + ((uint32_t)j0 << 16);
         }
         int tl = (int)(bk >> 19);  // kNone >> 19 = 8191 > any SAD
-        // one pass, the origin's own row first (zero-flow prior): a candidate is evaluated exactly iff its
-        // lower bound is <= the best SAD known to this lane; the bound is shared warp-wide after every row
+        if (lane == 0) K2STAT(6, 1);
+        // One pass, the origin's own row first (zero-flow prior).  Lanes test the two-word lower bound of 32 candidates at
+        // a time against the best SAD known to the warp and COMPACT the survivors into the warp's queue; exact SADs are
+        // then taken 32 at a time with every lane busy (evaluating in place would run the exact path whenever ANY lane
+        // survives: with a few per cent survivors that is nearly every iteration).
+        int hn = 0;
+        auto drain = [&](int n) {  // exact evaluation of the last n (<= 32) queued candidates
+          hn -= n;
+          if (lane < n) {
+            const uint32_t e2 = queue[hn + lane];
+            K2STAT(7, 1);
+            if ((int)(e2 >> 11) <= tl) bk = min(bk, cand_key(S, (int)(e2 & 0x7FFu), a, b, lo_p, hi_p));  // bound re-tested: tl may have dropped
+          }
+          tl = min(tl, (int)(__reduce_min_sync(FULL, bk) >> 19));
+          __syncwarp();
+        };
         const bool own = (v >= lo_r) && (v < hi_r);
+        const bool dense = tl > kSeedGood;  // no partner in sight: the bound prunes little, most lanes would evaluate anyway
         for (int rr = own ? lo_r - 1 : lo_r; rr < hi_r; rr++) {
           const int r = (rr < lo_r) ? v : rr;
           if (own && rr == v) continue;
           const int p1 = t.segOff[r][j1];
+          if (dense) {
+            // evaluate in place; the bound is lane-private inside a row and shared warp-wide after it
 #pragma unroll 2
-          for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) {
-            if (sadq(qa, S.q[p]) <= tl) {
-              bk = min(bk, cand_key(S, p, a, b, lo_p, hi_p));
-              tl = min(tl, (int)(bk >> 19));
+            for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) {
+              if ((int)sad4(qb, S.q1[p], sad4(qa, S.q[p], 0u)) <= tl) {
+                bk = min(bk, cand_key(S, p, a, b, lo_p, hi_p));
+                tl = min(tl, (int)(bk >> 19));
+              }
             }
+            tl = __reduce_min_sync(FULL, tl);
+            continue;
           }
-          tl = __reduce_min_sync(FULL, tl);
+          // 64 candidates per iteration, two per lane; loads are unconditional (positions past p1 are clamped into the
+          // staging arrays and masked out of the ballots)
+          for (int pb = t.segOff[r][j0]; pb < p1; pb += 64) {
+            const int pA = pb + lane, pB = pA + 32;
+            const int cA = min(pA, kCandCap - 1), cB = min(pB, kCandCap - 1);
+            const int qA = (int)sad4(qb, S.q1[cA], sad4(qa, S.q[cA], 0u));
+            const int qB = (int)sad4(qb, S.q1[cB], sad4(qa, S.q[cB], 0u));
+            const bool hA = (pA < p1) && (qA <= tl), hB = (pB < p1) && (qB <= tl);
+            const uint32_t balA = __ballot_sync(FULL, hA), balB = __ballot_sync(FULL, hB);
+            const int nA = __popc(balA);
+            if (hA) queue[hn + __popc(balA & lt_mask)] = ((uint32_t)qA << 11) | (uint32_t)pA;
+            if (hB) queue[hn + nA + __popc(balB & lt_mask)] = ((uint32_t)qB << 11) | (uint32_t)pB;
+            hn += nA + __popc(balB);
+            while (hn >= 32) { __syncwarp(); drain(32); }
+          }
         }
+        __syncwarp();
+        if (hn > 0) drain(hn);
         bk = __reduce_min_sync(FULL, bk);
         if (lane == 0) bo[o] = (bk == kNone) ? kNone : bk - ((uint32_t)j0 << 16);
       }
@@ -489,7 +571,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 template <bool PRUNE, int THREADS>
 __global__ void __launch_bounds__(THREADS, 2)
 k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best, int rows_per_group,
-         int ngroups) {
+         int ngroups, int hit_budget) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   K2Smem& S = *reinterpret_cast<K2Smem*>(smem_raw);
   const int cg = blockIdx.x / ngroups, grp = blockIdx.x - cg * ngroups;
@@ -503,7 +585,7 @@ k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __res
   // joint pass over both columns; if a row of the shared window does not fit, one pass per column
   for (int it = -1;;) {
     const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
-                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w);
+                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, hit_budget);
     if (it < 0 && ok) break;
     if (++it >= noc) break;
   }
@@ -791,7 +873,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
 
 template <bool PRUNE, int THREADS>
 static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                               int rows_per_group, cudaStream_t st) {
+                               int rows_per_group, int hit_budget, cudaStream_t st) {
   static bool attr_set = false;
   const int bytes = (int)sizeof(K2Smem);
   if (!attr_set) {
@@ -802,16 +884,17 @@ static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4*
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   const int cgroups = (g.U - 1 + kOC - 1) / kOC;
   dim3 grid(cgroups * ngroups, 8, n_edges / 2);  // edges come in twos (mono: curr->prev, prev->curr; quad: four)
-  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups);
+  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups,
+                                                         hit_budget > 0 ? hit_budget : kHitBudget);
   return cudaGetLastError();
 }
 
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                      int rows_per_group, int prune, int threads, cudaStream_t st) {
-  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, st);
-  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, st);
-  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, st);
-  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, st);
+                      int rows_per_group, int prune, int threads, int hit_budget, cudaStream_t st) {
+  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
+  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
+  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
+  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,

@@ -6,7 +6,11 @@ from hls_final_visual_odometry_b200 import Engine
 from hls_final_visual_odometry_b200.build import LIB
 from hls_final_visual_odometry_b200.synth import make_sequence
 W, H, B = 1241, 376, 8
+amp = int(sys.argv[1]) if len(sys.argv) > 1 else 0   # independent sensor noise of +-amp grey levels per frame
 seq = make_sequence(W, H, B + 1, seed=1)
+if amp:
+    rng = np.random.default_rng(100 + amp)
+    seq = np.clip(seq.astype(np.int16) + rng.integers(-amp, amp + 1, seq.shape, dtype=np.int16), 0, 255).astype(np.uint8)
 eng = Engine(W, H, max_frames=B + 1, max_pairs=B)
 lib = ctypes.CDLL(LIB)
 out = (ctypes.c_ulonglong * 8)()
@@ -16,6 +20,8 @@ prev = np.arange(B, dtype=np.int32); curr = prev + 1
 eng.batch_match(prev, curr, 2, 50.0, 50.0)
 eng.synchronize()
 lib.vo_debug_k2_stats(out)
-names = ["origins", "with rows", "seed none", "seed T==0", "filter hits (groups)", "budget handovers", "-", "-"]
+names = ["origins", "lanes in two-word warps", "seed none", "seed T==0", "filter hits (groups)", "budget handovers", "hard pass: origins",
+         "hard pass: queued candidates"]
+print(f"noise +-{amp}")
 for n, v in zip(names, out):
     print(f"{n:24s} {v / B:12.1f} per pair")
