@@ -236,8 +236,12 @@ def run_ours(args):
     canvas = make_canvas(W, H, seed=1 + rank)
     host_pool = pinned_empty((pool_frames, H, pitch), np.uint8)
     host_pool[:] = 0
+    noise_rng = np.random.default_rng(500 + rank) if args.noise > 0 else None
     for f in range(pool_frames):
-        host_pool[f, :, :W] = frame_from_canvas(canvas, W, H, f)
+        frame = frame_from_canvas(canvas, W, H, f)
+        if noise_rng is not None:  # independent sensor noise per frame: no two frames are bit-identical translations any more
+            frame = np.clip(frame.astype(np.int16) + noise_rng.integers(-args.noise, args.noise + 1, frame.shape, dtype=np.int16), 0, 255)
+        host_pool[f, :, :W] = frame
     dev_pool = torch.from_numpy(host_pool).cuda()        # HBM-resident copy, TMA-friendly pitch
     torch.cuda.synchronize()
     # the engine launches on THIS torch stream, so torch.cuda.Event timing brackets our kernels
@@ -394,7 +398,10 @@ def run_ours(args):
                    "pairs_per_step": pairs_per_step, "batch_per_gpu": B, "bucket": "2 per 50x50",
                    "l2": f"inputs larger than L2: pool of {pool_frames} frames ({pool_frames * H * pitch / 1e6:.0f} MB) cycled",
                    "features_per_frame": n_c, "raw_matches_per_pair": n_m, "bucketed_per_pair": n_b,
-                   "sharding": "independent sequences per GPU, no collective"},
+                   "sharding": "independent sequences per GPU, no collective",
+                   "sensor_noise": (f"uniform +-{args.noise} grey levels per frame" if args.noise > 0 else
+                                    "none: frames are exact integer translations of one canvas (best case for K2's exact pruning; "
+                                    "--noise N and profiles/*noise* give the figures with sensor noise)")},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * H * pitch) * world,
                 "d2h_bytes_per_step": int(counts[0].nbytes + B * max_keep * 48) * world,
@@ -423,6 +430,7 @@ def main():
     ap.add_argument("--pool", type=int, default=384, help="distinct frames cycled (keeps inputs larger than L2)")
     ap.add_argument("--rows", type=int, default=0, help="match_rows_per_cta tuning knob (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--noise", type=int, default=0, help="add uniform +-N grey levels of independent noise to every frame (our arm only)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

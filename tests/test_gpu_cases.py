@@ -264,3 +264,52 @@ def test_back_to_back_async_batches_keep_their_own_pair_tables():
         assert [int(c) for c in counts[:, 0]] == [want[(0, 1)] if it % 2 == 0 else want[(2, 3)] for it in range(16)]
     finally:
         eng.close()
+
+
+def _noisy(seq, amp, seed):
+    rng = np.random.default_rng(seed)
+    return np.clip(seq.astype(np.int16) + rng.integers(-amp, amp + 1, seq.shape, dtype=np.int16), 0, 255).astype(np.uint8)
+
+
+@pytest.mark.parametrize("amp", [1, 3, 8, 24])
+@pytest.mark.parametrize("size", [(1241, 376), (640, 200)], ids=lambda s: f"{s[0]}x{s[1]}")
+def test_matching_under_sensor_noise_vs_oracle(size, amp):
+    """Frames that are NOT bit-identical translations: no origin has a zero-SAD partner, the warps of K2 filter with
+    both signature words and keep poorly seeded origins on the lane path (csrc/vo_match.cu).  Bit-exact vs the oracle."""
+    w, h = size
+    seq = _noisy(make_sequence(w, h, 3, seed=21), amp, 1000 + amp)
+    orc = Oracle(w, h)
+    eng = Engine(w, h, max_frames=3, max_pairs=2)
+    try:
+        eng.batch_extract_host(0, seq)
+        eng.batch_match([0, 1], [1, 2], max_features=2, bw=50.0, bh=50.0)
+        f = [orc.compute_features(seq[i])[:2] for i in range(3)]
+        for i in range(2):
+            want, _ = orc.matching(*f[i], *f[i + 1], cap=1 << 18)
+            assert_matches_equal(eng.batch_get_matches(i, 0), want, f"noise {amp} pair {i}")
+            assert_matches_equal(eng.batch_get_matches(i, 1), orc.bucket_features(want, 2, 50.0, 50.0), f"noise {amp} pair {i} bucketed")
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("size", [(1241, 376), (2048, 1024)], ids=lambda s: f"{s[0]}x{s[1]}")
+def test_pruned_equals_exhaustive_on_mixed_noise_batch(size):
+    """One batch whose pairs carry different noise levels (0, 1, 2, 5, 12, 40 grey levels): one- and two-word warps, seed
+    handovers, budget handovers and chunked windows in the same launch; pruned search == every-SAD search."""
+    w, h = size
+    base = make_sequence(w, h, 7, seed=33)
+    amps = [0, 0, 1, 2, 5, 12, 40]
+    seq = np.stack([_noisy(base[i:i + 1], a, 50 + i)[0] if a else base[i] for i, a in enumerate(amps)])
+    prev = np.arange(6, dtype=np.int32)
+    got = []
+    for exhaustive in (False, True):
+        eng = Engine(w, h, max_frames=7, max_pairs=6, match_exhaustive=exhaustive)
+        try:
+            eng.batch_extract_host(0, seq)
+            eng.batch_match(prev, prev + 1, max_features=0)
+            got.append([eng.batch_get_matches(i, 0) for i in range(6)])
+        finally:
+            eng.close()
+    for i in range(6):
+        assert len(got[0][i]) > 100, f"pair {i}"
+        assert matches_digest(got[0][i]) == matches_digest(got[1][i]), f"pair {i} (noise {amps[i]} -> {amps[i + 1]})"

@@ -282,3 +282,30 @@ def test_quad_tall_frames_row_groups():
         assert len(want) > 50000 and got.tobytes() == want.tobytes()
     finally:
         eng.close()
+
+
+@pytest.mark.parametrize("amp", [2, 10])
+def test_quad_matching_under_sensor_noise_vs_oracle(amp):
+    """Independent noise on all four images: K2's two-word filtering on flow AND left<->right edges; refinement on top."""
+    w, h, n = 800, 240, 3
+    left, right = make_stereo_sequence(w, h, n, seed=8, disparity=[9, 10, 11])
+    rng = np.random.default_rng(amp)
+    left = np.clip(left.astype(np.int16) + rng.integers(-amp, amp + 1, left.shape, dtype=np.int16), 0, 255).astype(np.uint8)
+    right = np.clip(right.astype(np.int16) + rng.integers(-amp, amp + 1, right.shape, dtype=np.int16), 0, 255).astype(np.uint8)
+    orc = Oracle(w, h)
+    fl = [_feats(orc, f) for f in left]
+    fr = [_feats(orc, f) for f in right]
+    eng = Engine(w, h, max_frames=2 * n, max_pairs=n - 1, stereo=True)
+    try:
+        eng.batch_extract_host(0, left)
+        eng.batch_extract_host(n, right)
+        k = np.arange(1, n)
+        eng.batch_match_quad(k - 1, n + k - 1, k, n + k, disp_tolerance=2, refinement=2, max_features=0)
+        for i in range(n - 1):
+            want = orc.quad_matching(fl[i], fr[i], fl[i + 1], fr[i + 1], 2)
+            want = orc.refine(want, left[i], left[i + 1], right[i], right[i + 1])
+            got = eng.batch_get_matches(i, 0)
+            assert len(want) > 100
+            assert got.tobytes() == want.tobytes(), f"noise {amp} item {i}"
+    finally:
+        eng.close()

@@ -10,6 +10,7 @@ python bench.py > "$out/${tag}_bench.json" 2> "$out/${tag}_bench.err" || echo "b
 python bench.py --impl reference --steps 3 --warmup 1 > "$out/${tag}_bench_reference.json" 2>> "$out/${tag}_bench.err" || echo "reference arm failed"
 python tools/bench_stereo.py > "$out/${tag}_stereo_bench.json" 2> "$out/${tag}_stereo.err" || echo "stereo bench failed"
 python tools/bench_stereo.py --refinement 0 --cpu-pairs 0 > "$out/${tag}_stereo_bench_norefine.json" 2>> "$out/${tag}_stereo.err"
+VO_PROBE_PARITY=1 python tools/noise_probe.py 0 1 2 4 8 16 > "$out/${tag}_noise_probe.txt" 2>&1 || echo "noise probe failed"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file "$out/${tag}_launches.csv" \
     python bench.py --steps 2 --warmup 3 --no-cpu > "$out/${tag}_ncu_launches.log" 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file "$out/${tag}_stereo_launches.csv" \
