@@ -47,7 +47,7 @@ constexpr int kMaxCols = kOC + 5;  // staged target columns: [ub0-3, ub_last+3) 
 constexpr int kSegW = kMaxCols + 1;
 constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
 constexpr int kMaxWarps = 16;
-constexpr int kTwoWordVotes = 24;  // lanes with a non-zero seed bound that switch a warp's filter to both signature words
+constexpr int kTwoWordVotes = 3;  // a warp filters with both signature words when more than 3/4 of its searching lanes hold a non-zero bound
 constexpr int kQueue = 64;      // deferred exact evaluations per warp
 constexpr int kBig = 1 << 20;
 static_assert(kCandCap <= 2048, "k2 hard pass packs the staged position into 11 bits");
@@ -128,7 +128,7 @@ __device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 template <bool PRUNE, int THREADS>
 __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
                                            uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
-                                           int rows_per_group, int rad_v, int reach, int hit_budget) {
+                                           int rows_per_group, int rad_v, int reach, int hit_budget, bool hinted) {
   constexpr int NW = THREADS / 32;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   K2Tables& t = S.t;
@@ -214,6 +214,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     // ---- chunk = as many whole rows as fit the staging buffer ------------------------------
     int rb = ra, staged = 0;
     while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
+    // hints (see k2_hint_scatter) are only used when the whole window is staged at once; a chunked window searches in full
+    const bool use_hint = hinted && first_chunk && rb >= row_hi;
     __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
     if (tid == THREADS - 1) S.hard_n = 0;
     if (tid <= rb - ra) {
@@ -271,6 +273,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       uint4 a = make_uint4(0, 0, 0, 0), b = a;
       uint32_t qa = 0, qb = 0;
       uint32_t bestk = kNone;
+      uint32_t hint = kNone;
+      bool full = valid;  // this lane runs an unseeded search (seed pass below)
       if (valid) {
         while (t.prefO[cc][v + 1] <= o) v++;
         const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
@@ -284,6 +288,11 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int lo_r = max(max(max(vb - 3, 0), ra), v - reach);  // src/myMatch.cpp:92-93,99
         const int hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
         if (lo_r < hi_r) { vlo = lo_r; vhi = hi_r; }
+        if (use_hint) {
+          hint = bo[o];
+          full = false;
+          if (hint == kNone) { vlo = kBig; vhi = 0; }  // no feature of the other frame points here: the cycle cannot close
+        }
         if (!first_chunk) {
           bestk = bo[o];
           if (bestk != kNone) bestk += (uint32_t)j0 << 16;
@@ -294,7 +303,23 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
       const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
 
-      if (PRUNE) {
+      if (PRUNE && use_hint && vlo < vhi) {
+        // the hinted candidate must be one this origin may legally take (bin ranges are not symmetric between the two
+        // directions): locate it in the staged window and evaluate it; anything unexpected -> plain search
+        const int jr = (int)((hint >> 16) & 7u), kb = (int)(hint & 0xFFFFu), j = j0 + jr;
+        uint32_t k = kNone;
+        if (jr < 6 && j < j1) {
+          for (int r = vlo; r < vhi; r++) {
+            if (kb >= t.colT[j][r] && kb < t.colT[j][r + 1]) {
+              k = cand_key(S, t.segOff[r][j] + kb - t.colT[j][r], a, b, lo_p, hi_p);
+              break;
+            }
+          }
+        }
+        if (k != kNone && k == hint + ((uint32_t)j0 << 16)) bestk = k;
+        else full = true;
+      }
+      if (PRUNE && __any_sync(FULL, full && vlo < vhi)) {
         // seed: the candidate with the smallest lower bound among the bins the origins themselves
         // sit in (zero-flow prior); any legal candidate gives a valid bound
         const int smin = max(__reduce_min_sync(FULL, valid ? v : kBig), ra);
@@ -327,7 +352,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             }
           }
         }
-        if (k1 != kNone && vlo < vhi) {
+        if (k1 != kNone && vlo < vhi && full) {
           const int p = (int)(k1 & 0xFFFFFu);
           if (p >= t.rowStart[vlo] && p < t.rowStart[vhi]) bestk = min(bestk, cand_key(S, p, a, b, lo_p, hi_p));
         }
@@ -361,7 +386,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       // signature word alone prunes everything; once sensor noise leaves the seeds with non-zero bounds the filter
       // tests both words (twice the shared-memory reads, ~6x fewer false hits) and can afford to keep poorly seeded
       // origins on the lane path.
-      const bool two = PRUNE && __popc(__ballot_sync(FULL, vlo < vhi && tq > 0)) > kTwoWordVotes;
+      const uint32_t searching = __ballot_sync(FULL, vlo < vhi);
+      const bool two = PRUNE && __popc(__ballot_sync(FULL, vlo < vhi && tq > 0)) * 4 > __popc(searching) * kTwoWordVotes;
       K2STAT(1, (valid && two) ? 1 : 0);
       if (PRUNE && vlo < vhi && (two ? bestk == kNone : tq > kSeedGood)) hand_over();  // no seed or a poor one: nearly every group would hit
 
@@ -571,12 +597,15 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 template <bool PRUNE, int THREADS>
 __global__ void __launch_bounds__(THREADS, 2)
 k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best, int rows_per_group,
-         int ngroups, int hit_budget) {
+         int ngroups, int hit_budget, int mode) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   K2Smem& S = *reinterpret_cast<K2Smem*>(smem_raw);
   const int cg = blockIdx.x / ngroups, grp = blockIdx.x - cg * ngroups;
-  const int c = blockIdx.y >> 1;
-  const int edge = blockIdx.z * 2 + (blockIdx.y & 1);
+  // mode 0: grid.y = class x {even, odd edge}, every search in full.  Modes 1 and 2 split a mono pair's two directions
+  // over two launches (grid.y = class): 1 = the odd edges (prev -> curr) in full, 2 = the even edges (curr -> prev)
+  // starting from the hints k2_hint_scatter derived from the odd edges' results.
+  const int c = mode ? (int)blockIdx.y : (int)(blockIdx.y >> 1);
+  const int edge = blockIdx.z * 2 + (mode ? (mode == 1 ? 1 : 0) : (int)(blockIdx.y & 1));
   const int4 ed = edges[edge];  // x = origin slot, y = target slot, z = rad_v, w = row reach (MatchEdge)
   const int from_slot = ed.x, to_slot = ed.y;
   const int ub0 = cg * kOC;
@@ -585,9 +614,57 @@ k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __res
   // joint pass over both columns; if a row of the shared window does not fit, one pass per column
   for (int it = -1;;) {
     const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
-                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, hit_budget);
+                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, hit_budget, mode == 2);
     if (it < 0 && ok) break;
     if (++it >= noc) break;
+  }
+}
+
+// ---- hints for the second direction of a mono pair ---------------------------------------------------------------
+// A match is emitted only when the cycle closes: A (curr) -> argmin B (prev) and B -> argmin A (src/myMatch.cpp:160-186).
+// Once the prev -> curr direction is known, the curr -> prev search of A matters only if some B points at A, and it can
+// only close on the pointer with the smallest key; that key is what A's own search would compute for B, so it is a
+// ready-made bound.  k2_hint_clear resets best[curr->prev] of every origin, k2_hint_scatter writes min over the pointers
+// B of key(A, B) = SAD << 19 | (u_bin(B) - first column of A's window) << 16 | col_idx(B) -- or a marker that cannot be
+// validated when B's column lies outside A's (half-open, clipped) column range.  K2 mode 2 validates the hint against
+// the staged window (rows, pixel window, key equality) and falls back to a plain search if anything differs; origins
+// nobody points at are skipped (their result cannot be observed).
+constexpr int KH_THREADS = 256;
+__device__ __forceinline__ int column_total(const Geom& g, const int32_t* __restrict__ cnt, int u, int c) {
+  __shared__ int tot;
+  if (threadIdx.x == 0) tot = 0;
+  __syncthreads();
+  int s = 0;
+  for (int v = threadIdx.x; v < g.V; v += blockDim.x) s += cnt[(v * g.U + u) * 4 + c];
+  if (s) atomicAdd(&tot, s);
+  __syncthreads();
+  return tot;
+}
+
+__global__ void __launch_bounds__(KH_THREADS)
+k2_hint_clear(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best) {
+  const int u = blockIdx.x >> 2, c = blockIdx.x & 3, pair = blockIdx.y;
+  const int4 ed = edges[2 * pair];  // curr -> prev: its origins are the features of ed.x
+  const int n = column_total(g, fa.cnt + (int64_t)ed.x * fa.cnt_stride, u, c);
+  uint32_t* bo = best + ((int64_t)(2 * pair) * g.U * 4 + (u * 4 + c)) * g.col_cap;
+  for (int k = threadIdx.x; k < n; k += KH_THREADS) bo[k] = kNone;
+}
+
+__global__ void __launch_bounds__(KH_THREADS)
+k2_hint_scatter(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best) {
+  const int ub = blockIdx.x >> 2, c = blockIdx.x & 3, pair = blockIdx.y;
+  const int4 ed = edges[2 * pair + 1];  // prev -> curr: origins B are the features of ed.x
+  const int n = column_total(g, fa.cnt + (int64_t)ed.x * fa.cnt_stride, ub, c);
+  const uint32_t* bsrc = best + ((int64_t)(2 * pair + 1) * g.U * 4 + (ub * 4 + c)) * g.col_cap;
+  uint32_t* bdst = best + (int64_t)(2 * pair) * g.U * 4 * g.col_cap;
+  const int a0 = max(ub - 3, 0);
+  for (int k = threadIdx.x; k < n; k += KH_THREADS) {
+    const uint32_t key = bsrc[k];
+    if (key == kNone) continue;
+    const int ua = a0 + (int)((key >> 16) & 7u), ka = (int)(key & 0xFFFFu);
+    const int w0 = max(ua - 3, 0), w1 = min(ua + 3, g.U - 1);  // A's target columns [w0, w1): src/myMatch.cpp:90-91,97
+    const uint32_t low = (ub >= w0 && ub < w1) ? (((uint32_t)(ub - w0) << 16) | (uint32_t)k) : 0x7FFFFu;
+    atomicMin(&bdst[(int64_t)(ua * 4 + c) * g.col_cap + ka], (key & ~0x7FFFFu) | low);
   }
 }
 
@@ -873,7 +950,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
 
 template <bool PRUNE, int THREADS>
 static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                               int rows_per_group, int hit_budget, cudaStream_t st) {
+                               int rows_per_group, int hit_budget, bool split, cudaStream_t st) {
   static bool attr_set = false;
   const int bytes = (int)sizeof(K2Smem);
   if (!attr_set) {
@@ -883,18 +960,28 @@ static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4*
   }
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   const int cgroups = (g.U - 1 + kOC - 1) / kOC;
-  dim3 grid(cgroups * ngroups, 8, n_edges / 2);  // edges come in twos (mono: curr->prev, prev->curr; quad: four)
-  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups,
-                                                         hit_budget > 0 ? hit_budget : kHitBudget);
+  const int budget = hit_budget > 0 ? hit_budget : kHitBudget;
+  if (!split) {
+    dim3 grid(cgroups * ngroups, 8, n_edges / 2);  // edges come in twos (mono: curr->prev, prev->curr; quad: four)
+    k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 0);
+    return cudaGetLastError();
+  }
+  // mono pairs: prev -> curr in full, hints, then curr -> prev from the hints
+  dim3 grid(cgroups * ngroups, 4, n_edges / 2), hgrid((g.U - 1) * 4, n_edges / 2);
+  k2_hint_clear<<<hgrid, KH_THREADS, 0, st>>>(g, fa, edges, best);
+  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 1);
+  k2_hint_scatter<<<hgrid, KH_THREADS, 0, st>>>(g, fa, edges, best);
+  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 2);
   return cudaGetLastError();
 }
 
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                      int rows_per_group, int prune, int threads, int hit_budget, cudaStream_t st) {
-  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
-  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
-  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
-  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, st);
+                      int rows_per_group, int prune, int threads, int hit_budget, int split, cudaStream_t st) {
+  // split != 0: the edges are mono pairs (curr->prev, prev->curr) and may run as two dependent launches
+  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, false, st);
+  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, split, st);
+  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, split, st);
+  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, split, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
