@@ -313,3 +313,13 @@ def test_pruned_equals_exhaustive_on_mixed_noise_batch(size):
     for i in range(6):
         assert len(got[0][i]) > 100, f"pair {i}"
         assert matches_digest(got[0][i]) == matches_digest(got[1][i]), f"pair {i} (noise {amps[i]} -> {amps[i + 1]})"
+
+
+def test_random_stress_pruned_equals_exhaustive():
+    """tools/stress_match.py: random sizes, flows up to the window limits (asymmetric bin ranges between the two
+    directions: K2's hints must be validated), noise levels and densities; pruned + hinted search == every-SAD search."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "tools"))
+    import stress_match
+    rng = np.random.default_rng(2024)
+    assert all([stress_match.run_case(rng, i) for i in range(16)])
