@@ -207,6 +207,25 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
+def _bind_host_to_gpu(torch, local_rank):
+    """Multi-rank runs: pin this process to the CPUs NVML names as local to its GPU BEFORE the pinned frame pool is
+    allocated and first touched, so that the pool lands on the GPU's NUMA node (the e2e leg streams 60 MB per step and rank
+    from it).  Returns a short description for the JSON line, or None if NVML cannot tell."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(local_rank).uuid)
+            h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = nv.nvmlDeviceGetHandleByIndex(local_rank)
+        nv.nvmlDeviceSetCpuAffinity(h)
+        cpus = sorted(os.sched_getaffinity(0))
+        return f"{len(cpus)} cpus local to the GPU ({cpus[0]}..{cpus[-1]}; nvmlDeviceSetCpuAffinity)"
+    except Exception as exc:  # not fatal: the run is valid without it
+        return f"unbound ({type(exc).__name__})"
+
+
 def run_ours(args):
     import torch
 
@@ -220,6 +239,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    host_affinity = _bind_host_to_gpu(torch, local_rank) if world > 1 else None
     dist = None
     if world > 1:
         if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
@@ -400,7 +420,7 @@ def run_ours(args):
                    "pairs_per_step": pairs_per_step, "batch_per_gpu": B, "bucket": "2 per 50x50",
                    "l2": f"inputs larger than L2: pool of {pool_frames} frames ({pool_frames * H * pitch / 1e6:.0f} MB) cycled",
                    "features_per_frame": n_c, "raw_matches_per_pair": n_m, "bucketed_per_pair": n_b,
-                   "sharding": "independent sequences per GPU, no collective",
+                   "sharding": "independent sequences per GPU, no collective", "host_affinity": host_affinity,
                    "sensor_noise": (f"uniform +-{args.noise} grey levels per frame" if args.noise > 0 else
                                     "none: frames are exact integer translations of one canvas (best case for K2's exact pruning; "
                                     "--noise N and profiles/*noise* give the figures with sensor noise)")},
