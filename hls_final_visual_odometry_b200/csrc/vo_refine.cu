@@ -123,7 +123,7 @@ __device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const uint8
 }
 
 // quads[item] = {1p, 2p, 1c, 2c} slots (2p/2c = -1 for flow lists)
-__global__ void __launch_bounds__(K5_WARPS * 32, 3)
+__global__ void __launch_bounds__(K5_WARPS * 32, 4)
 k5_refine(Geom g, FrameArrays fa, const int4* __restrict__ quads, float* __restrict__ lists, int64_t stride_matches,
           const int32_t* __restrict__ n_list, uint8_t* __restrict__ keep) {
   __shared__ K5Warp sw[K5_WARPS];
