@@ -34,13 +34,20 @@ __device__ __forceinline__ float block_max(float v, float* red) {
   return r;
 }
 
+// current-image coordinates of match i: from the 4-byte side array when there is one, else from the record
+__device__ __forceinline__ uint2 k4_coord(const uint32_t* __restrict__ side, const uint4* __restrict__ src, int i) {
+  if (side) { const uint32_t x = side[i]; return make_uint2(__float_as_uint((float)(x & 0xFFFFu)), __float_as_uint((float)(x >> 16))); }
+  const uint4 w1 = src[(int64_t)i * 3 + 1];
+  return make_uint2(w1.z, w1.w);
+}
+
 // in: lists of 48-byte p_match records (3 x uint4), u1c/v1c are words 6/7
 __global__ void __launch_bounds__(K4_THREADS)
 k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t* __restrict__ n_in,
           int32_t max_features, float bucket_w, float bucket_h, const uint32_t* __restrict__ lfsr, int32_t lfsr_len,
           int32_t* __restrict__ scratch, int64_t scratch_stride, int32_t nb_max, int32_t q_cap,
           uint4* __restrict__ out, int64_t out_stride_matches, int32_t out_cap, int32_t* __restrict__ n_out,
-          int32_t* __restrict__ status) {
+          int32_t* __restrict__ status, const uint32_t* __restrict__ side_all) {
   __shared__ float red[K4_WARPS];
   __shared__ int32_t s_carry[2];
   __shared__ int32_t s_scan[K4_WARPS][2];
@@ -48,6 +55,9 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
   const int n = n_in[pair];
   const uint4* src = in + (int64_t)pair * in_stride_matches * 3;
   uint4* dst = out + (int64_t)pair * out_stride_matches * 3;
+  // optional 4-byte (u1c | v1c << 16) per record, written by K3's emit for lists of integer coordinates: the three
+  // passes then stream 4 bytes per match instead of the 48-byte records (r1f: 208 MB of DRAM reads per 128 pairs)
+  const uint32_t* side = side_all ? side_all + (int64_t)pair * in_stride_matches : nullptr;
   int32_t* hist = scratch + (int64_t)pair * scratch_stride;
   int32_t* cnt = hist + (int64_t)nb_max * 32;
   int32_t* soff = cnt + nb_max;
@@ -56,10 +66,13 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
 
   // ---- extent of the current-image coordinates (src/matcher.cpp:143-152) -------------------
   float um = 0.f, vm = 0.f;
-  for (int i = tid; i < n; i += K4_THREADS) {
-    const uint4 w1 = src[(int64_t)i * 3 + 1];
-    um = fmaxf(um, __uint_as_float(w1.z));
-    vm = fmaxf(vm, __uint_as_float(w1.w));
+  // (the passes are latency bound -- one CTA per pair, ~17 matches per thread: four independent loads in flight per thread)
+  for (int i = tid; i < n; i += 4 * K4_THREADS) {
+    uint2 x[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) x[k] = (i + k * K4_THREADS < n) ? k4_coord(side, src, i + k * K4_THREADS) : make_uint2(0u, 0u);
+#pragma unroll
+    for (int k = 0; k < 4; k++) { um = fmaxf(um, __uint_as_float(x[k].x)); vm = fmaxf(vm, __uint_as_float(x[k].y)); }
   }
   um = block_max(um, red);
   vm = block_max(vm, red);
@@ -77,11 +90,18 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
   __syncthreads();
   const int seg_len = (n + K4_WARPS - 1) / K4_WARPS;
   const int seg_lo = min(warp * seg_len, n), seg_hi = min(seg_lo + seg_len, n);
-  for (int i = seg_lo + lane; i < seg_hi; i += 32) {
-    const uint4 w1 = src[(int64_t)i * 3 + 1];
-    const int bu = (int)floorf(__fdiv_rn(__uint_as_float(w1.z), bucket_w));
-    const int bv = (int)floorf(__fdiv_rn(__uint_as_float(w1.w), bucket_h));
-    atomicAdd(&hist[(bv * cols + bu) * 32 + warp], 1);
+  for (int i = seg_lo + lane; i < seg_hi; i += 4 * 32) {
+    uint2 x[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) x[k] = (i + k * 32 < seg_hi) ? k4_coord(side, src, i + k * 32) : make_uint2(0u, 0u);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (i + k * 32 < seg_hi) {
+        const int bu = (int)floorf(__fdiv_rn(__uint_as_float(x[k].x), bucket_w));
+        const int bv = (int)floorf(__fdiv_rn(__uint_as_float(x[k].y), bucket_h));
+        atomicAdd(&hist[(bv * cols + bu) * 32 + warp], 1);
+      }
+    }
   }
   __syncthreads();
   // exclusive scan over the 32 segments of every bucket (warp per bucket)
@@ -136,14 +156,18 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
   }
   __syncthreads();
   // ---- pass 2: stable rank of every match inside its bucket; copy the selected ones -------
+  uint2 xa = (seg_lo + lane < seg_hi) ? k4_coord(side, src, seg_lo + lane) : make_uint2(0u, 0u);
+  uint2 xb = (seg_lo + 32 + lane < seg_hi) ? k4_coord(side, src, seg_lo + 32 + lane) : make_uint2(0u, 0u);
   for (int i0 = seg_lo; i0 < seg_hi; i0 += 32) {
     const int i = i0 + lane;
     const bool act = i < seg_hi;
     const uint32_t amask = __ballot_sync(0xFFFFFFFFu, act);
+    const uint2 xc = xa;  // coordinates of this round; the next two rounds' loads are already in flight
+    xa = xb;
+    xb = (i + 64 < seg_hi) ? k4_coord(side, src, i + 64) : make_uint2(0u, 0u);
     if (act) {
-      const uint4 w0 = src[(int64_t)i * 3], w1 = src[(int64_t)i * 3 + 1], w2 = src[(int64_t)i * 3 + 2];
-      const int bu = (int)floorf(__fdiv_rn(__uint_as_float(w1.z), bucket_w));
-      const int bv = (int)floorf(__fdiv_rn(__uint_as_float(w1.w), bucket_h));
+      const int bu = (int)floorf(__fdiv_rn(__uint_as_float(xc.x), bucket_w));
+      const int bv = (int)floorf(__fdiv_rn(__uint_as_float(xc.y), bucket_h));
       const int b = bv * cols + bu;
       const uint32_t same = __match_any_sync(amask, b);
       const int rank = hist[b * 32 + warp] + __popc(same & ((1u << lane) - 1u));
@@ -151,9 +175,9 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
       if ((same & ((1u << lane) - 1u)) == 0) hist[b * 32 + warp] += __popc(same);
       const int kept = min(cnt[b], keep), o0 = ooff[b];
       for (int t = 0; t < kept; t++)
-        if (q[o0 + t] == rank) {
+        if (q[o0 + t] == rank) {  // the few selected records are the only ones read in full
           uint4* rec = dst + (int64_t)(o0 + t) * 3;
-          rec[0] = w0; rec[1] = w1; rec[2] = w2;
+          rec[0] = src[(int64_t)i * 3]; rec[1] = src[(int64_t)i * 3 + 1]; rec[2] = src[(int64_t)i * 3 + 2];
         }
     }
     __syncwarp();
@@ -166,10 +190,10 @@ int64_t k4_scratch_ints_host(int nb_max, int q_cap) { return k4_scratch_ints(nb_
 cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* n_in, int n_pairs, int32_t max_features,
                       float bw, float bh, const uint32_t* lfsr, int32_t lfsr_len, int32_t* scratch, int64_t scratch_stride,
                       int32_t nb_max, int32_t q_cap, void* out, int64_t out_stride_matches, int32_t out_cap,
-                      int32_t* n_out, int32_t* status, cudaStream_t st) {
+                      int32_t* n_out, int32_t* status, const uint32_t* side, cudaStream_t st) {
   k4_bucket<<<n_pairs, K4_THREADS, 0, st>>>((const uint4*)in, in_stride_matches, n_in, max_features, bw, bh, lfsr,
                                             lfsr_len, scratch, scratch_stride, nb_max, q_cap, (uint4*)out,
-                                            out_stride_matches, out_cap, n_out, status);
+                                            out_stride_matches, out_cap, n_out, status, side);
   return cudaGetLastError();
 }
 

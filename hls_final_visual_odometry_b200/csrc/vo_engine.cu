@@ -26,17 +26,17 @@ cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, i
 cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* quads, const int2* pairs, int n_items,
                            const uint32_t* best, uint8_t* flags, int32_t* list_cnt, uint32_t* qxy, void* out,
                            int64_t out_stride_matches, int32_t max_matches, int32_t* n_raw, int32_t* status,
-                           cudaStream_t st);
+                           uint32_t* side, cudaStream_t st);
 cudaError_t launch_k5(const Geom& g, const FrameArrays& fa, const int4* quads, int n_items, void* lists,
                       int64_t stride_matches, int32_t max_n, int32_t* n_list, uint8_t* keep, cudaStream_t st);
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
                       uint8_t* flags, int32_t* list_cnt, void* out, int64_t out_stride_matches, int32_t max_matches,
-                      int32_t* n_raw, int32_t* status, cudaStream_t st);
+                      int32_t* n_raw, int32_t* status, uint32_t* side, cudaStream_t st);
 int64_t k4_scratch_ints_host(int nb_max, int q_cap);
 cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* n_in, int n_pairs, int32_t max_features,
                       float bw, float bh, const uint32_t* lfsr, int32_t lfsr_len, int32_t* scratch, int64_t scratch_stride,
                       int32_t nb_max, int32_t q_cap, void* out, int64_t out_stride_matches, int32_t out_cap,
-                      int32_t* n_out, int32_t* status, cudaStream_t st);
+                      int32_t* n_out, int32_t* status, const uint32_t* side, cudaStream_t st);
 }  // namespace vo
 
 namespace {
@@ -124,6 +124,7 @@ struct vo_engine {
   uint8_t* d_flags = nullptr;
   int32_t* d_list_cnt = nullptr;
   vo_p_match* d_raw = nullptr;          // [n_pairbuf][max_matches]
+  uint32_t* d_side = nullptr;           // [n_pairbuf][max_matches] (u1c | v1c << 16) of the records K3 emitted last (for K4)
   vo_p_match* d_bucketed = nullptr;     // [n_pairbuf][max_matches]
   int32_t* d_n_raw = nullptr;           // [n_pairbuf]
   int32_t* d_n_bucketed = nullptr;      // [n_pairbuf]
@@ -298,7 +299,7 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
     CU_TRY(vo::launch_k3(g, e->fa, e->d_pairs + pair0, n_pairs, e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap,
                          e->d_flags + (int64_t)pair0 * g.U * 4 * g.col_cap, e->d_list_cnt + (int64_t)pair0 * g.U * 4,
                          e->d_raw + (int64_t)pair0 * e->cfg.max_matches, e->cfg.max_matches, e->cfg.max_matches,
-                         e->d_n_raw + pair0, e->d_status, e->stream));
+                         e->d_n_raw + pair0, e->d_status, e->d_side + (int64_t)pair0 * e->cfg.max_matches, e->stream));
     e->launches += 2;
   }
   if (max_features > 0) {
@@ -306,7 +307,8 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
     CU_TRY(vo::launch_k4(e->d_raw + (int64_t)pair0 * e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + pair0, n_pairs,
                          max_features, bw, bh, e->d_lfsr, kLfsrLen, e->d_scratch + (int64_t)pair0 * e->scratch_stride,
                          e->scratch_stride, kNbMax, kQCap, e->d_bucketed + (int64_t)pair0 * e->cfg.max_matches,
-                         e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + pair0, e->d_status, e->stream));
+                         e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + pair0, e->d_status,
+                         e->d_side + (int64_t)pair0 * e->cfg.max_matches, e->stream));
     e->launches += 1;
   }
   return VO_OK;
@@ -402,7 +404,8 @@ vo_status do_match_quad(vo_engine* e, int item0, int n_items, int refinement, in
     CU_TRY(vo::launch_k3_quad(g, e->fa, e->d_quads + item0, e->d_pairs + item0, n_items, e->d_best + (int64_t)item0 * 4 * lists,
                               e->d_flags + (int64_t)item0 * lists, e->d_list_cnt + (int64_t)item0 * g.U * 4,
                               e->d_qxy + (int64_t)item0 * lists * 3, e->d_raw + (int64_t)item0 * e->cfg.max_matches,
-                              e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + item0, e->d_status, e->stream));
+                              e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + item0, e->d_status,
+                              e->d_side + (int64_t)item0 * e->cfg.max_matches, e->stream));
     e->launches += 2;
   }
   if (refinement == 2) {
@@ -414,7 +417,9 @@ vo_status do_match_quad(vo_engine* e, int item0, int n_items, int refinement, in
     CU_TRY(vo::launch_k4(e->d_raw + (int64_t)item0 * e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + item0, n_items,
                          max_features, bw, bh, e->d_lfsr, kLfsrLen, e->d_scratch + (int64_t)item0 * e->scratch_stride,
                          e->scratch_stride, kNbMax, kQCap, e->d_bucketed + (int64_t)item0 * e->cfg.max_matches,
-                         e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + item0, e->d_status, e->stream));
+                         e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + item0, e->d_status,
+                         // the side array holds the integer coordinates K3 emitted: stale once K5 refined or compacted the list
+                         refinement == 2 ? nullptr : e->d_side + (int64_t)item0 * e->cfg.max_matches, e->stream));
     e->launches += 1;
   }
   return VO_OK;
@@ -567,6 +572,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   ALLOC(e->d_flags, (size_t)(P * lists));
   ALLOC(e->d_list_cnt, sizeof(int32_t) * P * g.U * 4);
   ALLOC(e->d_raw, sizeof(vo_p_match) * P * cfg.max_matches);
+  ALLOC(e->d_side, sizeof(uint32_t) * P * cfg.max_matches);
   ALLOC(e->d_bucketed, sizeof(vo_p_match) * P * cfg.max_matches);
   ALLOC(e->d_n_raw, sizeof(int32_t) * P);
   ALLOC(e->d_n_bucketed, sizeof(int32_t) * P);
@@ -621,7 +627,7 @@ void vo_engine_destroy(vo_engine* e) {
   for (auto& f : e->fences) if (f) cudaEventDestroy(f);
   for (auto& r : e->readers) if (r.ev) cudaEventDestroy(r.ev);
   cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc); cudaFree(e->fa.q);
-  cudaFree(e->d_pairs_base); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw);
+  cudaFree(e->d_pairs_base); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw); cudaFree(e->d_side);
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
   cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);
   cudaFree(e->d_edges_base); cudaFree(e->d_quads_base); cudaFree(e->d_qxy); cudaFree(e->d_keep);
@@ -757,7 +763,7 @@ vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, in
   CU_TRY(vo::launch_k4(e->d_raw + (int64_t)pb * e->cfg.max_matches, e->cfg.max_matches, e->d_n_raw + pb, 1, max_features,
                        bucket_w, bucket_h, e->d_lfsr, kLfsrLen, e->d_scratch + (int64_t)pb * e->scratch_stride,
                        e->scratch_stride, kNbMax, kQCap, e->d_bucketed + (int64_t)pb * e->cfg.max_matches,
-                       e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + pb, e->d_status, e->stream));
+                       e->cfg.max_matches, e->cfg.max_matches, e->d_n_bucketed + pb, e->d_status, nullptr, e->stream));
   e->launches += 1;
   CU_TRY(cudaMemcpyAsync(&e->h_counts[0], e->d_n_bucketed + pb, 4, cudaMemcpyDeviceToHost, e->stream));
   vo_status s = check_device_status(e);
@@ -860,7 +866,7 @@ vo_status vo_bucket_features(vo_engine* e, int32_t max_features, float bucket_w,
   {
     Scope sc(e, F_BUCKET);
     CU_TRY(vo::launch_k4(e->d_raw, M, e->d_n_raw, 1, max_features, bucket_w, bucket_h, e->d_lfsr, kLfsrLen, e->d_scratch,
-                         e->scratch_stride, kNbMax, kQCap, e->d_bucketed, M, (int32_t)M, e->d_n_bucketed, e->d_status,
+                         e->scratch_stride, kNbMax, kQCap, e->d_bucketed, M, (int32_t)M, e->d_n_bucketed, e->d_status, nullptr,
                          e->stream));
     e->launches += 1;
   }
@@ -1039,7 +1045,7 @@ vo_status vo_batch_bucket_host(vo_engine* e, int32_t n_pairs, const vo_p_match* 
     Scope sc(e, F_BUCKET);
     CU_TRY(vo::launch_k4(e->d_raw, e->cfg.max_matches, e->d_n_raw, n_pairs, max_features, bucket_w, bucket_h, e->d_lfsr,
                          kLfsrLen, e->d_scratch, e->scratch_stride, kNbMax, kQCap, e->d_bucketed, e->cfg.max_matches,
-                         e->cfg.max_matches, e->d_n_bucketed, e->d_status, e->stream));
+                         e->cfg.max_matches, e->d_n_bucketed, e->d_status, nullptr, e->stream));
     e->launches += 1;
   }
   e->last_batch_pairs = n_pairs;

@@ -856,7 +856,7 @@ __global__ void __launch_bounds__(K3_THREADS)
 k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* __restrict__ best,
         const uint8_t* __restrict__ flags, const int32_t* __restrict__ list_cnt, const uint32_t* __restrict__ qxy,
         uint4* __restrict__ out, int64_t out_stride_matches, int32_t max_matches, int32_t* __restrict__ n_raw,
-        int32_t* __restrict__ status) {
+        int32_t* __restrict__ status, uint32_t* __restrict__ side) {
   __shared__ int32_t pref[kMaxV + 1];
   __shared__ int32_t warp_tot[K3_THREADS / 32];
   __shared__ int32_t s_off, s_total;
@@ -918,6 +918,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
       const uint32_t m1f = __float_as_uint(-1.0f), m1i = 0xFFFFFFFFu;
       const uint32_t u1c = __float_as_uint((float)(cxy & 0xFFFFu)), v1c = __float_as_uint((float)(cxy >> 16));
       uint4* rec = dst + (int64_t)posn * 3;
+      if (side) side[(int64_t)pair * out_stride_matches + posn] = cxy;  // (u1c, v1c) of every record: all K4 needs to bucket
       if (QUAD) {
         const uint32_t* qq = qxy + (((int64_t)pair * U * 4 + list) * g.col_cap + k) * 3;
         const uint32_t x1p = qq[0], x2p = qq[1], x2c = qq[2];
@@ -986,12 +987,12 @@ cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, i
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
                       uint8_t* flags, int32_t* list_cnt, void* out, int64_t out_stride_matches, int32_t max_matches,
-                      int32_t* n_raw, int32_t* status, cudaStream_t st) {
+                      int32_t* n_raw, int32_t* status, uint32_t* side, cudaStream_t st) {
   k3_flags<<<dim3(g.U, n_pairs), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   k3_emit<false><<<dim3(g.U * 4, n_pairs), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt, nullptr, (uint4*)out,
-                                                                out_stride_matches, max_matches, n_raw, status);
+                                                                out_stride_matches, max_matches, n_raw, status, side);
   return cudaGetLastError();
 }
 
@@ -999,12 +1000,12 @@ cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, i
 cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* quads, const int2* pairs, int n_items,
                            const uint32_t* best, uint8_t* flags, int32_t* list_cnt, uint32_t* qxy, void* out,
                            int64_t out_stride_matches, int32_t max_matches, int32_t* n_raw, int32_t* status,
-                           cudaStream_t st) {
+                           uint32_t* side, cudaStream_t st) {
   k3q_flags<<<dim3(g.U, n_items), K3_THREADS, 0, st>>>(g, fa, quads, best, flags, list_cnt, qxy);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   k3_emit<true><<<dim3(g.U * 4, n_items), K3_THREADS, 0, st>>>(g, fa, pairs, best, flags, list_cnt, qxy, (uint4*)out,
-                                                               out_stride_matches, max_matches, n_raw, status);
+                                                               out_stride_matches, max_matches, n_raw, status, side);
   return cudaGetLastError();
 }
 
