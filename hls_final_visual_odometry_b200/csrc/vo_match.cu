@@ -858,6 +858,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
         uint4* __restrict__ out, int64_t out_stride_matches, int32_t max_matches, int32_t* __restrict__ n_raw,
         int32_t* __restrict__ status, uint32_t* __restrict__ side) {
   __shared__ int32_t pref[kMaxV + 1];
+  __shared__ int32_t ppref[6][kMaxV + 1];
   __shared__ int32_t warp_tot[K3_THREADS / 32];
   __shared__ int32_t s_off, s_total;
   const int list = blockIdx.x, pair = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -881,6 +882,13 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
     int acc = 0;
     pref[0] = 0;
     for (int v = 0; v < V; v++) { acc += cnt[(v * U + u) * 4 + c]; pref[v + 1] = acc; }
+  } else if (!QUAD && tid >= 64 && tid < 70) {
+    // col_idx prefixes of the six previous-frame columns a match of this list can point into
+    const int j = tid - 64, pu = max(u - 3, 0) + j;
+    const int32_t* cnt = fa.cnt + (int64_t)pr.x * fa.cnt_stride;
+    int acc = 0;
+    ppref[j][0] = 0;
+    for (int v = 0; v < V; v++) { acc += (pu < U) ? cnt[(v * U + pu) * 4 + c] : 0; ppref[j][v + 1] = acc; }
   }
   __syncthreads();
   const int total = s_total;
@@ -894,7 +902,6 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
   const uint8_t* fl = flags + ((int64_t)pair * U * 4 + list) * g.col_cap;
   const uint32_t* xy_c = fa.xy + (int64_t)pr.y * fa.rec_stride;
   const uint32_t* xy_p = fa.xy + (int64_t)pr.x * fa.rec_stride;
-  const int32_t* cnt_p = fa.cnt + (int64_t)pr.x * fa.cnt_stride;
   uint4* dst = out + (int64_t)pair * out_stride_matches * 3;
   int running = s_off;
   for (int base = 0; base < n; base += K3_THREADS) {
@@ -930,12 +937,10 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
       } else {
         int pu, pk;
         decode_key(best_cp[(int64_t)list * g.col_cap + k], u, pu, pk);
-        int pv = 0, rem = pk;
-        for (;; pv++) {  // locate the previous feature's (row, slot) from its col_idx
-          const int nn = cnt_p[(pv * U + pu) * 4 + c];
-          if (rem < nn) break;
-          rem -= nn;
-        }
+        const int32_t* pp = ppref[pu - max(u - 3, 0)];  // locate the previous feature's (row, slot) from its col_idx
+        int pv = 0;
+        while (pv < V - 1 && pp[pv + 1] <= pk) pv++;
+        const int rem = pk - pp[pv];
         const uint32_t pxy = xy_p[(int64_t)((pv * U + pu) * 4 + c) * g.cap + rem];
         // p_match(u1p,v1p,-1,-1,-1,-1,u1c,v1c,-1,-1,-1,-1): src/myMatch.cpp:189
         const uint32_t u1p = __float_as_uint((float)(pxy & 0xFFFFu)), v1p = __float_as_uint((float)(pxy >> 16));
