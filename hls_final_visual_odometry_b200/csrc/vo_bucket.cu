@@ -18,6 +18,7 @@ namespace vo {
 
 constexpr int K4_THREADS = 1024;
 constexpr int K4_WARPS = K4_THREADS / 32;
+constexpr int K4_SMEM_BUCKETS = 1024;  // bucket grids up to this size keep the (bucket, segment) histogram in shared memory (128 KB)
 
 // per-pair scratch layout (int32 units): hist[nb_max][32] | cnt[nb_max] | soff[nb_max+1] | ooff[nb_max+1] | q[q_cap]
 __host__ __device__ inline int64_t k4_scratch_ints(int nb_max, int q_cap) {
@@ -48,6 +49,7 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
           int32_t* __restrict__ scratch, int64_t scratch_stride, int32_t nb_max, int32_t q_cap,
           uint4* __restrict__ out, int64_t out_stride_matches, int32_t out_cap, int32_t* __restrict__ n_out,
           int32_t* __restrict__ status, const uint32_t* __restrict__ side_all) {
+  extern __shared__ int32_t sh_hist[];
   __shared__ float red[K4_WARPS];
   __shared__ int32_t s_carry[2];
   __shared__ int32_t s_scan[K4_WARPS][2];
@@ -58,8 +60,8 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
   // optional 4-byte (u1c | v1c << 16) per record, written by K3's emit for lists of integer coordinates: the three
   // passes then stream 4 bytes per match instead of the 48-byte records (r1f: 208 MB of DRAM reads per 128 pairs)
   const uint32_t* side = side_all ? side_all + (int64_t)pair * in_stride_matches : nullptr;
-  int32_t* hist = scratch + (int64_t)pair * scratch_stride;
-  int32_t* cnt = hist + (int64_t)nb_max * 32;
+  int32_t* ghist = scratch + (int64_t)pair * scratch_stride;
+  int32_t* cnt = ghist + (int64_t)nb_max * 32;
   int32_t* soff = cnt + nb_max;
   int32_t* ooff = soff + nb_max + 1;
   int32_t* q = ooff + nb_max + 1;
@@ -85,6 +87,7 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
     return;
   }
 
+  int32_t* hist = (nb <= K4_SMEM_BUCKETS) ? sh_hist : ghist;
   // ---- pass 1: histogram per (bucket, ordered segment) --------------------------------------
   for (int i = tid; i < nb * 32; i += K4_THREADS) hist[i] = 0;
   __syncthreads();
@@ -191,7 +194,14 @@ cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* 
                       float bw, float bh, const uint32_t* lfsr, int32_t lfsr_len, int32_t* scratch, int64_t scratch_stride,
                       int32_t nb_max, int32_t q_cap, void* out, int64_t out_stride_matches, int32_t out_cap,
                       int32_t* n_out, int32_t* status, const uint32_t* side, cudaStream_t st) {
-  k4_bucket<<<n_pairs, K4_THREADS, 0, st>>>((const uint4*)in, in_stride_matches, n_in, max_features, bw, bh, lfsr,
+  static bool attr_set = false;
+  const int smem = K4_SMEM_BUCKETS * 32 * (int)sizeof(int32_t);
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k4_bucket, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  k4_bucket<<<n_pairs, K4_THREADS, smem, st>>>((const uint4*)in, in_stride_matches, n_in, max_features, bw, bh, lfsr,
                                             lfsr_len, scratch, scratch_stride, nb_max, q_cap, (uint4*)out,
                                             out_stride_matches, out_cap, n_out, status, side);
   return cudaGetLastError();
