@@ -410,7 +410,7 @@ def run_ours(args):
     fam = {k: (v[0] / max(v[1], 1)) for k, v in prof.items()}
     roofline = {
         "kernel": "k2_match", "launches": "per step the matching of a batch is k2_match twice (prev->curr in full, curr->prev from "
-                  "hints) + k2_hint_clear + k2_hint_scatter; algorithmic bytes, traffic and avg_launch_ms are for that group",
+                  "hints) + k2_hint_scatter; algorithmic bytes, traffic and avg_launch_ms are for that group",
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": b_match * B, "avg_launch_ms": k2_avg_s * 1e3,

@@ -292,7 +292,7 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
     CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)pair0 * 2, 2 * n_pairs,
                          e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap, e->rows_per_group, e->prune,
                          e->match_threads, e->cfg.match_hit_budget, e->split_match, e->stream));
-    e->launches += (e->prune && e->split_match) ? 4 : 1;
+    e->launches += (e->prune && e->split_match) ? 3 : 1;
   }
   {
     Scope sc(e, F_EMIT);

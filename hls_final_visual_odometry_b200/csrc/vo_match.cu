@@ -128,7 +128,8 @@ __device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 template <bool PRUNE, int THREADS>
 __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
                                            uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
-                                           int rows_per_group, int rad_v, int reach, int hit_budget, bool hinted) {
+                                           int rows_per_group, int rad_v, int reach, int hit_budget, bool hinted,
+                                           uint32_t* __restrict__ clear_dir) {
   constexpr int NW = THREADS / 32;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   K2Tables& t = S.t;
@@ -174,6 +175,15 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     t.lagEnd[cc][v] = le;
   }
 
+  if (clear_dir != nullptr && grp == 0) {
+    // mode 1 (prev -> curr in full): the lists of the TARGET frame in this CTA's own columns are the origins of the hinted
+    // launch that follows; reset their best[] entries here so that k2_hint_scatter can atomicMin into them
+    for (int cc = 0; cc < noc; cc++) {
+      const int j = ub0 + cc - ulo;
+      uint32_t* bc = clear_dir + (int64_t)((ub0 + cc) * 4 + c) * g.col_cap;
+      for (int k = tid, n = t.colT[j][V]; k < n; k += THREADS) bc[k] = kNone;
+    }
+  }
   const int r0 = grp * rows_per_group, r1 = min(r0 + rows_per_group, V);
   int oB0 = 0, nT0 = 0, ntasks = 0, row_lo = V;
 #pragma unroll
@@ -614,7 +624,8 @@ k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __res
   // joint pass over both columns; if a row of the shared window does not fit, one pass per column
   for (int it = -1;;) {
     const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
-                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, hit_budget, mode == 2);
+                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, hit_budget, mode == 2,
+                                               mode == 1 ? best + (int64_t)(edge - 1) * g.U * 4 * g.col_cap : nullptr);
     if (it < 0 && ok) break;
     if (++it >= noc) break;
   }
@@ -624,7 +635,7 @@ k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __res
 // A match is emitted only when the cycle closes: A (curr) -> argmin B (prev) and B -> argmin A (src/myMatch.cpp:160-186).
 // Once the prev -> curr direction is known, the curr -> prev search of A matters only if some B points at A, and it can
 // only close on the pointer with the smallest key; that key is what A's own search would compute for B, so it is a
-// ready-made bound.  k2_hint_clear resets best[curr->prev] of every origin, k2_hint_scatter writes min over the pointers
+// ready-made bound.  The full launch resets best[curr->prev] of every origin on its way, k2_hint_scatter writes min over the pointers
 // B of key(A, B) = SAD << 19 | (u_bin(B) - first column of A's window) << 16 | col_idx(B) -- or a marker that cannot be
 // validated when B's column lies outside A's (half-open, clipped) column range.  K2 mode 2 validates the hint against
 // the staged window (rows, pixel window, key equality) and falls back to a plain search if anything differs; origins
@@ -639,15 +650,6 @@ __device__ __forceinline__ int column_total(const Geom& g, const int32_t* __rest
   if (s) atomicAdd(&tot, s);
   __syncthreads();
   return tot;
-}
-
-__global__ void __launch_bounds__(KH_THREADS)
-k2_hint_clear(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best) {
-  const int u = blockIdx.x >> 2, c = blockIdx.x & 3, pair = blockIdx.y;
-  const int4 ed = edges[2 * pair];  // curr -> prev: its origins are the features of ed.x
-  const int n = column_total(g, fa.cnt + (int64_t)ed.x * fa.cnt_stride, u, c);
-  uint32_t* bo = best + ((int64_t)(2 * pair) * g.U * 4 + (u * 4 + c)) * g.col_cap;
-  for (int k = threadIdx.x; k < n; k += KH_THREADS) bo[k] = kNone;
 }
 
 __global__ void __launch_bounds__(KH_THREADS)
@@ -972,9 +974,8 @@ static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4*
     k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 0);
     return cudaGetLastError();
   }
-  // mono pairs: prev -> curr in full, hints, then curr -> prev from the hints
+  // mono pairs: prev -> curr in full (its CTAs also reset best[curr -> prev]), hints, then curr -> prev from the hints
   dim3 grid(cgroups * ngroups, 4, n_edges / 2), hgrid((g.U - 1) * 4, n_edges / 2);
-  k2_hint_clear<<<hgrid, KH_THREADS, 0, st>>>(g, fa, edges, best);
   k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 1);
   k2_hint_scatter<<<hgrid, KH_THREADS, 0, st>>>(g, fa, edges, best);
   k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 2);
