@@ -323,3 +323,4 @@ def test_random_stress_pruned_equals_exhaustive():
     import stress_match
     rng = np.random.default_rng(2024)
     assert all([stress_match.run_case(rng, i) for i in range(16)])
+
