@@ -324,3 +324,10 @@ def test_random_stress_pruned_equals_exhaustive():
     rng = np.random.default_rng(2024)
     assert all([stress_match.run_case(rng, i) for i in range(16)])
 
+
+def test_bench_json_contract():
+    """bench.py prints ONE JSON line with the keys the driver reads (tools/check_bench_contract.py; small batch, no CPU leg)."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "tools"))
+    import check_bench_contract
+    check_bench_contract.main()
