@@ -190,17 +190,16 @@ k4_bucket(const uint4* __restrict__ in, int64_t in_stride_matches, const int32_t
 
 int64_t k4_scratch_ints_host(int nb_max, int q_cap) { return k4_scratch_ints(nb_max, q_cap); }
 
+// per-device opt-in to K4's dynamic shared memory (see init_k1_device)
+cudaError_t init_k4_device() {
+  return cudaFuncSetAttribute(k4_bucket, cudaFuncAttributeMaxDynamicSharedMemorySize, K4_SMEM_BUCKETS * 32 * (int)sizeof(int32_t));
+}
+
 cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* n_in, int n_pairs, int32_t max_features,
                       float bw, float bh, const uint32_t* lfsr, int32_t lfsr_len, int32_t* scratch, int64_t scratch_stride,
                       int32_t nb_max, int32_t q_cap, void* out, int64_t out_stride_matches, int32_t out_cap,
                       int32_t* n_out, int32_t* status, const uint32_t* side, cudaStream_t st) {
-  static bool attr_set = false;
   const int smem = K4_SMEM_BUCKETS * 32 * (int)sizeof(int32_t);
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k4_bucket, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
   k4_bucket<<<n_pairs, K4_THREADS, smem, st>>>((const uint4*)in, in_stride_matches, n_in, max_features, bw, bh, lfsr,
                                             lfsr_len, scratch, scratch_stride, nb_max, q_cap, (uint4*)out,
                                             out_stride_matches, out_cap, n_out, status, side);

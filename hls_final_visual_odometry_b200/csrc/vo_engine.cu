@@ -15,6 +15,9 @@
 
 namespace vo {
 size_t k1_smem_bytes();
+cudaError_t init_k1_device();
+cudaError_t init_k2_device();
+cudaError_t init_k4_device();
 cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
                       cudaStream_t st);
 cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t* max2, int32_t* max2_num,
@@ -493,6 +496,10 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   cudaDeviceProp prop;
   CU_TRY(cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10) return fail(VO_ERR_CUDA, "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
+  // function attributes are per device: every engine sets them on its own GPU (a process may own engines on several)
+  CU_TRY(vo::init_k1_device());
+  CU_TRY(vo::init_k2_device());
+  CU_TRY(vo::init_k4_device());
 
   vo_engine* e = new (std::nothrow) vo_engine();
   if (!e) return fail(VO_ERR_INVALID, "out of host memory");

@@ -84,7 +84,7 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
         : "memory");
   }
   {
-    uint32_t done = 0;
+    uint32_t done = 0, spins = 0;
     while (!done) {
       asm volatile(
           "{\n\t.reg .pred p;\n\t"
@@ -93,6 +93,7 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
           : "=r"(done)
           : "r"(smem_u32(&s.bar))
           : "memory");
+      if (!done && ++spins > (1u << 24)) __trap();  // a TMA load that never completes fails the launch instead of hanging the GPU
     }
   }
 
@@ -310,14 +311,14 @@ __global__ void k_load_features(Geom g, FrameArrays fa, int slot, const int32_t*
 
 size_t k1_smem_bytes() { return sizeof(K1Smem); }
 
+// The opt-in to more than 48 KB of dynamic shared memory is a per-DEVICE function attribute: vo_engine_create calls this
+// (and its K2 / K4 counterparts) after cudaSetDevice, so a process that owns engines on several GPUs sets it on each.
+cudaError_t init_k1_device() {
+  return cudaFuncSetAttribute(k1_extract, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem));
+}
+
 cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
                       cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k1_extract, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem));
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
   const int rows = g.j_last / BH + 1;  // tile rows that contain at least one block row
   dim3 grid(g.U, rows, n);
   k1_extract<<<grid, K1_THREADS, sizeof(K1Smem), st>>>(tmap, g, fa, first_slot, z_base);

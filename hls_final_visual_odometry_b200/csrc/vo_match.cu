@@ -959,13 +959,7 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
 template <bool PRUNE, int THREADS>
 static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
                                int rows_per_group, int hit_budget, bool split, cudaStream_t st) {
-  static bool attr_set = false;
   const int bytes = (int)sizeof(K2Smem);
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k2_match<PRUNE, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   const int cgroups = (g.U - 1 + kOC - 1) / kOC;
   const int budget = hit_budget > 0 ? hit_budget : kHitBudget;
@@ -980,6 +974,16 @@ static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4*
   k2_hint_scatter<<<hgrid, KH_THREADS, 0, st>>>(g, fa, edges, best);
   k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 2);
   return cudaGetLastError();
+}
+
+// per-device opt-in to K2's dynamic shared memory, every instantiation launch_k2 can pick (see init_k1_device)
+cudaError_t init_k2_device() {
+  const int bytes = (int)sizeof(K2Smem);
+  cudaError_t e = cudaFuncSetAttribute(k2_match<false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 384>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  return e;
 }
 
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,

@@ -72,7 +72,7 @@ def main():
             seq = make_sequence(ref.W, ref.H, 3, seed=seed)
             g["cases"][f"textured_seed{seed}_f01"] = pair_record(ref, seq[0], seq[1], with_post=True)
             g["cases"][f"textured_seed{seed}_f12"] = pair_record(ref, seq[1], seq[2], with_post=True)
-        if tag in ("1024x284", "500x150"):
+        if tag != "native":  # every override geometry, incl. the BASELINE sizes (V = 9: one row group; V = 23: row groups, chunked windows)
             for name in ADVERSARIAL:
                 a, b = cases.CASES[name](ref.W, ref.H, 0)
                 g["cases"][name] = pair_record(ref, a, b, with_post=(name != "dense"))

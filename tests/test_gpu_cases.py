@@ -17,7 +17,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = json.load(open(os.path.join(HERE, "golden", "golden.json")))
 
 
-@pytest.mark.parametrize("size", [(1024, 284), (500, 150)], ids=lambda s: f"{s[0]}x{s[1]}")
+# 1241x376 (V = 9) and 2048x1024 (V = 23: K2 runs in row groups of 8 with chunked windows and the one-column fallback on
+# `dense`) are the BASELINE sizes; 1024x284 is the reference's own geometry
+@pytest.mark.parametrize("size", [(1024, 284), (500, 150), (1241, 376), (2048, 1024)], ids=lambda s: f"{s[0]}x{s[1]}")
 @pytest.mark.parametrize("name", sorted(cases.CASES))
 def test_adversarial_vs_oracle(name, size):
     w, h = size
@@ -36,6 +38,32 @@ def test_adversarial_vs_oracle(name, size):
         assert_matches_equal(eng.batch_get_matches(0, 1), orc.bucket_features(want, 2, 50.0, 50.0), name + " bucketed")
     finally:
         eng.close()
+
+
+def test_engines_on_two_devices_in_one_process():
+    """the > 48 KB shared-memory opt-in of K1/K2/K4 is a per-device attribute: an engine on a second GPU of the same
+    process must work like the first (round-1 bug: a process-wide `static bool attr_set`)"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    w, h = 1241, 376
+    seq = make_sequence(w, h, 2, seed=3)
+    orc = Oracle(w, h)
+    fp = orc.compute_features(seq[0])[:2]
+    fc = orc.compute_features(seq[1])[:2]
+    want, _ = orc.matching(fp[0], fp[1], fc[0], fc[1], cap=1 << 18)
+    engines = [Engine(w, h, max_frames=2, max_pairs=1, device=d) for d in (0, 1)]
+    try:
+        for eng in engines:                       # interleaved: both engines alive, both devices used in turn
+            eng.batch_extract_host(0, seq)
+        for d, eng in enumerate(engines):
+            eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+            assert_features_equal(eng.slot_dump_features(1), fc, f"device {d}")
+            assert_matches_equal(eng.batch_get_matches(0, 0), want, f"device {d}")
+            assert_matches_equal(eng.batch_get_matches(0, 1), orc.bucket_features(want, 2, 50.0, 50.0), f"device {d} bucketed")
+    finally:
+        for eng in engines:
+            eng.close()
 
 
 GOLD_IDS = [(tag, name) for tag, g in GOLD["geometries"].items() if tag != "native" for name in g["cases"]]
