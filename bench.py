@@ -32,8 +32,38 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 
 W_DEFAULT, H_DEFAULT = 1241, 376
-METRIC = "frame_pairs_per_s_1241x376"
 UNIT = "frame-pairs/s"
+NOISE_DEFAULT = 2   # grey levels of uniform sensor noise added independently to every frame of the headline workload
+
+
+def metric_name(width, height):
+    return f"frame_pairs_per_s_{width}x{height}"
+
+
+def workload_name(args):
+    """One string for both arms (the driver compares them)."""
+    cfg = "configs[4]: 8 independent sequences" if args.config == 5 else "configs[1]"
+    return (f"{cfg}: {args.width}x{args.height} frame pairs, extract+match+bucket, synthetic sequence with uniform "
+            f"+-{args.noise} grey levels of sensor noise per frame")
+
+
+def noisy_frame(frame, amp, rng):
+    """frame + independent uniform noise in [-amp, amp], clipped (both arms and every leg use this)."""
+    if amp <= 0:
+        return frame
+    return np.clip(frame.astype(np.int16) + rng.integers(-amp, amp + 1, frame.shape, dtype=np.int16), 0, 255).astype(np.uint8)
+
+
+def source_hash():
+    """sha256 over the kernel sources + ABI header: ties profiles/traffic.json to the build it was captured from."""
+    import hashlib
+    h = hashlib.sha256()
+    base = os.path.join(ROOT, "hls_final_visual_odometry_b200", "csrc")
+    files = sorted(os.path.join(base, f) for f in os.listdir(base) if f.endswith((".cu", ".cuh", ".cpp")))
+    for f in files + [os.path.join(ROOT, "include", "vo_b200.h")]:
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
 
 
 # --------------------------------------------------------------------------------------------
@@ -42,12 +72,14 @@ UNIT = "frame-pairs/s"
 def _cpu_worker(args):
     """Process n consecutive pairs of one synthetic sequence with the reference code; returns
     (pairs, seconds, kind)."""
-    width, height, seed, n_pairs = args
+    width, height, seed, n_pairs, noise = args
     from hls_final_visual_odometry_b200.synth import make_sequence
     from oracle.oracle_lib import Oracle
     from oracle.ref_lib import RefLib, have_ref
 
     seq = make_sequence(width, height, n_pairs + 1, seed=seed)
+    rng = np.random.default_rng(9000 + seed)
+    seq = np.stack([noisy_frame(f, noise, rng) for f in seq])
     tag = f"{width}x{height}"
     orc = Oracle(width, height)
     if have_ref(tag):
@@ -69,21 +101,26 @@ def _cpu_worker(args):
         # bucketing stage of the CPU leg runs through the oracle port
         orc.bucket_features(raw, 2, 50.0, 50.0)
         prev = cur
-    return n_pairs, time.perf_counter() - t0, kind
+    dt = time.perf_counter() - t0
+    # untimed: how many 32-byte SADs the reference's exhaustive search evaluates per pair on these frames (the unit of the
+    # integer-pipe roofline); the oracle port counts them
+    fa, fb = orc.compute_features(seq[0])[:2], orc.compute_features(seq[1])[:2]
+    _, st = orc.matching(fa[0], fa[1], fb[0], fb[1], cap=1 << 19)
+    return n_pairs, dt, kind, int(st[0])
 
 
-def cpu_throughput(width, height, pairs_per_worker, workers):
+def cpu_throughput(width, height, pairs_per_worker, workers, noise):
     """Aggregate pairs/s of `workers` independent single-threaded reference processes."""
     import multiprocessing as mp
     ctx = mp.get_context("fork")
-    jobs = [(width, height, 100 + i, pairs_per_worker) for i in range(workers)]
+    jobs = [(width, height, 100 + i, pairs_per_worker, noise) for i in range(workers)]
     t0 = time.perf_counter()
     with ctx.Pool(workers) as pool:
         res = pool.map(_cpu_worker, jobs)
     wall = time.perf_counter() - t0
     slowest = max(r[1] for r in res)
     total = sum(r[0] for r in res)
-    return total / slowest, res[0][2], wall, total
+    return total / slowest, res[0][2], wall, total, float(np.mean([r[3] for r in res]))
 
 
 def run_reference(args):
@@ -96,22 +133,21 @@ def run_reference(args):
     vals = []
     kind = "reference"
     for s in range(args.warmup + args.steps):
-        v, kind, _, total = cpu_throughput(args.width, args.height, pairs_per_worker, workers)
+        v, kind, _, total, _ = cpu_throughput(args.width, args.height, pairs_per_worker, workers, args.noise)
         if s >= args.warmup:
             vals.append(v)
     value = float(np.mean(vals)) if vals else 0.0
     sample = (f"{workers} single-threaded processes x {pairs_per_worker} consecutive pairs per step of the "
-              f"{args.width}x{args.height} synthetic sequence: myComputeFeatures + myMatching "
+              f"{args.width}x{args.height} synthetic sequence (+-{args.noise} grey levels of sensor noise): myComputeFeatures + myMatching "
               f"({'oracle/_ref, reference sources compiled in place' if kind == 'reference' else 'oracle port'})"
               f" + bucketing (oracle port)")
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": metric_name(args.width, args.height), "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * workers * pairs_per_worker / value if value else None,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "higher_is_better": True, "scaling": "strong" if args.config == 5 else "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": f"configs[1]: {args.width}x{args.height} frame pairs, extract+match+bucket",
-                   "pairs_per_step": workers * pairs_per_worker},
+        "config": {"workload": workload_name(args), "pairs_per_step": workers * pairs_per_worker},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -231,6 +267,7 @@ def run_ours(args):
 
     from hls_final_visual_odometry_b200 import Engine, pinned_empty
     from hls_final_visual_odometry_b200.api import P_MATCH_DTYPE
+    from hls_final_visual_odometry_b200.sharding import assign_sequences, sequence_seed
     from hls_final_visual_odometry_b200.synth import frame_from_canvas, make_canvas
 
     rank = int(os.environ.get("RANK", "0"))
@@ -248,21 +285,40 @@ def run_ours(args):
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist = dist_mod
 
-    W, H, B = args.width, args.height, args.batch
+    W, H = args.width, args.height
     pitch = (W + 15) & ~15
-    pool_frames = max(args.pool, 2 * B)
-    pool_frames = (pool_frames + B - 1) // B * B       # whole steps
-    # ---- synthetic sequence of this rank (independent sequences: seed 1 + rank) ------------
-    canvas = make_canvas(W, H, seed=1 + rank)
-    host_pool = pinned_empty((pool_frames, H, pitch), np.uint8)
-    host_pool[:] = 0
-    noise_rng = np.random.default_rng(500 + rank) if args.noise > 0 else None
-    for f in range(pool_frames):
-        frame = frame_from_canvas(canvas, W, H, f)
-        if noise_rng is not None:  # independent sensor noise per frame: no two frames are bit-identical translations any more
-            frame = np.clip(frame.astype(np.int16) + noise_rng.integers(-args.noise, args.noise + 1, frame.shape, dtype=np.int16), 0, 255)
-        host_pool[f, :, :W] = frame
-    dev_pool = torch.from_numpy(host_pool).cuda()        # HBM-resident copy, TMA-friendly pitch
+    # ---- which sequences this rank owns, and how many new frames of each make one step ------------------------------
+    if args.config == 5:
+        # BASELINE configs[4]: a FIXED job of 8 independent sequences (seeds 1..8), sharded 8/4/2/1 per GPU over 1/2/4/8
+        # GPUs -- strong scaling; one GPU interleaves all eight
+        n_total = args.sequences
+        if n_total % world:
+            raise SystemExit(f"bench.py --config 5: {n_total} sequences do not split evenly over {world} ranks")
+        mine = assign_sequences(n_total, world, rank)
+        bs = args.batch // n_total                        # frames per sequence and step (global step = args.batch pairs)
+        pairs_per_step = bs * n_total
+        scaling = "strong"
+    else:
+        mine = [rank]                                     # independent sequence per rank, seed 1 + rank: weak scaling
+        bs = args.batch
+        pairs_per_step = bs * world
+        scaling = "weak"
+    nq = len(mine)
+    B = bs * nq                                           # pairs per step on THIS rank
+    pool_frames = max(args.pool // nq, 2 * bs)
+    pool_frames = (pool_frames + bs - 1) // bs * bs       # whole steps
+    canvases = [make_canvas(W, H, seed=sequence_seed(q)) for q in mine]
+    host_pools = [pinned_empty((pool_frames, H, pitch), np.uint8) for _ in mine]
+
+    def fill_pools(amp):
+        for qi, q in enumerate(mine):
+            host_pools[qi][:] = 0
+            rng = np.random.default_rng(500 + q)
+            for f in range(pool_frames):
+                host_pools[qi][f, :, :W] = noisy_frame(frame_from_canvas(canvases[qi], W, H, f), amp, rng)
+
+    fill_pools(args.noise)
+    dev_pools = [torch.from_numpy(hp).cuda() for hp in host_pools]   # HBM-resident copies, TMA-friendly pitch
     torch.cuda.synchronize()
     # the engine launches on THIS torch stream, so torch.cuda.Event timing brackets our kernels
     # (torch's default stream has handle 0, which the C ABI reads as "create your own stream")
@@ -277,15 +333,21 @@ def run_ours(args):
     consumed = [0]
 
     def slots_of(step):
-        base = (step % 2) * B
-        curr = (base + np.arange(B)) % (2 * B)
-        prev = (curr - 1) % (2 * B)
-        return base, prev.astype(np.int32), curr.astype(np.int32)
+        """per sequence: first slot of this step's frames; all pairs of the rank: prev/curr slot arrays.  Sequence qi owns
+        the ring of slots [qi * 2 bs, (qi + 1) * 2 bs)."""
+        bases, prev, curr = [], [], []
+        for qi in range(nq):
+            ring0 = qi * 2 * bs
+            base = ring0 + (step % 2) * bs
+            c = ring0 + (base - ring0 + np.arange(bs)) % (2 * bs)
+            bases.append(base); curr.append(c); prev.append(ring0 + (c - ring0 - 1) % (2 * bs))
+        return bases, np.concatenate(prev).astype(np.int32), np.concatenate(curr).astype(np.int32)
 
     def step_device(step):
-        base, prev, curr = slots_of(step)
-        f0 = (step * B) % pool_frames
-        eng.batch_extract_device(base, dev_pool.data_ptr() + f0 * H * pitch, B, H * pitch, pitch)
+        bases, prev, curr = slots_of(step)
+        f0 = (step * bs) % pool_frames
+        for qi in range(nq):
+            eng.batch_extract_device(bases[qi], dev_pools[qi].data_ptr() + f0 * H * pitch, bs, H * pitch, pitch)
         eng.batch_match(prev, curr, 2, 50.0, 50.0)
 
     def consume(buf):
@@ -296,10 +358,11 @@ def run_ours(args):
         # software pipeline, depth 2 (the reference's FPGA host does the same, hls_opencl/host/main2.cpp:449-518):
         # H2D of this step runs on the upload stream while the previous step's kernels run; its D2H runs on
         # the download stream; the host blocks only on the PREVIOUS step's result.
-        base, prev, curr = slots_of(step)
-        f0 = (step * B) % pool_frames
+        bases, prev, curr = slots_of(step)
+        f0 = (step * bs) % pool_frames
         buf = step % 2
-        eng.batch_extract_host(base, host_pool[f0:f0 + B])
+        for qi in range(nq):
+            eng.batch_extract_host(bases[qi], host_pools[qi][f0:f0 + bs])
         eng.batch_match(prev, curr, 2, 50.0, 50.0)
         eng.batch_download_async(B, 1, counts[buf], out_lists[buf], max_keep, max_keep)
         eng.fence_record(buf)
@@ -331,7 +394,7 @@ def run_ours(args):
             ms, wall = float(t[0]), float(t[1]) / 1e3
         return ms, wall
 
-    # ---- warm-up (fills the ring so every timed pair has a real previous frame) ------------
+    # ---- warm-up (fills the rings so every timed pair has a real previous frame) ------------
     for s in range(max(args.warmup, 3)):
         step_device(s)
     step0 = max(args.warmup, 3)
@@ -357,27 +420,31 @@ def run_ours(args):
     e2e_ms = max(e2e_ms, e2e_wall * 1e3)                  # host-visible completion is what counts
     clocks = sampler.stop() if sampler else None
 
-    # ---- the same device-resident step on frames with sensor noise (N=1; reported beside the headline, not in it):
-    #      the bench frames are exact translations of one canvas, the best case for K2's exact pruned search ----------
-    noisy = None
-    if world == 1 and args.noise == 0 and not args.no_noise_leg:
-        amp, n_noisy = 2, min(args.steps, 50)
-        nrng = np.random.default_rng(777)
-        for f in range(pool_frames):
-            fr = host_pool[f, :, :W].astype(np.int16) + nrng.integers(-amp, amp + 1, (H, W), dtype=np.int16)
-            host_pool[f, :, :W] = np.clip(fr, 0, 255)
-        dev_pool.copy_(torch.from_numpy(host_pool))
+    # ---- the same device-resident step at other noise levels (N = 1 only; reported beside the headline, never in it).
+    #      Noise-free frames are exact integer translations of one canvas: K2's exact pruning collapses on them (92 % of the
+    #      origins have a SAD-0 partner), so that figure is a BEST CASE, not the headline. ---------------------------------
+    extra = {}
+    if world == 1 and not args.no_extra_legs:
         nfirst = last + 1
-        for s in range(3):
-            step_device(nfirst + s)
-        noisy_ms, _ = timed(step_device, nfirst + 3, n_steps=n_noisy)
-        nraw, _ = eng.batch_counts(B)
-        noisy = {"value": B * n_noisy / (noisy_ms / 1e3), "unit": UNIT, "steps": n_noisy, "ms_per_step": noisy_ms / n_noisy,
-                 "noise": f"uniform +-{amp} grey levels, independent per frame", "raw_matches_per_pair": float(np.mean(nraw)),
-                 "what": "device-resident step as `value`, same frames plus sensor noise (results stay bit-exact, "
-                         "tests/test_gpu_cases.py::test_matching_under_sensor_noise_vs_oracle)"}
+        for name, amp in (("best_case_noise_free", 0), ("noise_8", 8)):
+            if amp == args.noise:
+                continue
+            n_leg = min(args.steps, 50)
+            fill_pools(amp)
+            for qi in range(nq):
+                dev_pools[qi].copy_(torch.from_numpy(host_pools[qi]))
+            for s in range(3):
+                step_device(nfirst + s)
+            leg_ms, _ = timed(step_device, nfirst + 3, n_steps=n_leg)
+            nraw, _ = eng.batch_counts(B)
+            extra[name] = {"value": B * n_leg / (leg_ms / 1e3), "unit": UNIT, "steps": n_leg, "ms_per_step": leg_ms / n_leg,
+                           "noise": f"uniform +-{amp} grey levels, independent per frame" if amp else
+                                    "none: every frame is an exact integer translation of one canvas",
+                           "raw_matches_per_pair": float(np.mean(nraw)),
+                           "what": "device-resident step as `value`, same sequence at another sensor-noise level (results stay "
+                                   "bit-exact at every level: tests/test_gpu_cases.py::test_matching_under_sensor_noise_vs_oracle)"}
+            nfirst += 3 + n_leg
 
-    pairs_per_step = B * world
     value = pairs_per_step * args.steps / (dev_ms / 1e3)
     e2e_value = pairs_per_step * args.steps / (e2e_ms / 1e3)
     if rank != 0:
@@ -385,7 +452,18 @@ def run_ours(args):
             dist.destroy_process_group()
         return 0
 
-    # ---- roofline of the dominant kernel (k2_match) ----------------------------------------
+    # ---- CPU baseline on this box's host cores (bounded sample, the SAME noisy sequence type) ----------------------------
+    cpu, sads_per_pair = None, None
+    if world == 1 and not args.no_cpu:
+        cores = max(1, min(os.cpu_count() or 1, 64))
+        ppw = 12 if W * H < 1_000_000 else 3
+        v, kind, wall, total, sads_per_pair = cpu_throughput(W, H, ppw, cores, args.noise)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": f"{cores} single-threaded processes x {ppw} consecutive pairs ({total} pairs, {wall:.1f} s wall) of "
+                         f"the same {W}x{H} synthetic sequence type with +-{args.noise} grey levels of sensor noise: "
+                         f"myComputeFeatures+myMatching from oracle/_ref, bucketing via the oracle port"}
+
+    # ---- rooflines of the dominant kernel (k2_match) ----------------------------------------
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     if os.path.exists(peaks_path):
@@ -401,49 +479,72 @@ def run_ours(args):
     k2_avg_s = k2_ms / max(k2_calls, 1) / 1e3
     achieved = b_match * B / k2_avg_s / 1e9 if k2_avg_s > 0 else 0.0
     step_ms = dev_ms / args.steps
-    traffic = None                                        # measured DRAM bytes per K2 launch (ncu --set full capture)
+    # measured DRAM bytes and ALU-pipe utilisation of K2 come from an `ncu --set full` capture of THIS build
+    # (tools/ncu_traffic.py writes profiles/traffic.json with the hash of the kernel sources); a capture of another
+    # build is refused instead of silently reported
+    traffic, alu_pct, traffic_note = None, None, None
+    src_hash = source_hash()
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k2_match"]
-        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["pairs_per_launch"] * B
-    except Exception:
-        pass
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tj.get("source_sha256") == src_hash:
+            k2 = tj["k2_match"]
+            traffic = (k2["dram_bytes_read"] + k2["dram_bytes_write"]) / k2["pairs_per_launch"] * B
+            alu_pct = k2.get("alu_pipe_pct_of_peak")
+            traffic_note = f"{k2.get('capture')} (sources {src_hash})"
+        else:
+            traffic_note = (f"profiles/traffic.json was captured from sources {tj.get('source_sha256')}, this build is {src_hash}: "
+                            "not reported (re-run tools/profile_round.sh)")
+            print("bench.py: " + traffic_note, file=sys.stderr)
+    except Exception as exc:
+        traffic_note = f"profiles/traffic.json unreadable ({type(exc).__name__})"
+    # integer-pipe roofline: a 32-byte SAD is 8 VABSDIFF4 on the ALU pipe; tools/intpipe_bench.cu measured how many the
+    # machine issues (profiles/r2_intpipe.json).  The reference's search evaluates `sads_per_pair` of them per frame pair
+    # (counted by the oracle on the CPU leg's frames); K2's pruning returns the same argmin with fewer, so the figure is
+    # "reference-equivalent SAD32/s" and may exceed the exhaustive peak.
+    int_pipe = None
+    try:
+        ip = json.load(open(os.path.join(ROOT, "profiles", "r2_intpipe.json")))
+        rate = next(r["warp_inst_per_clk_per_sm"] for r in ip["results"] if r["op"] == "vabsdiff4_acc")
+        ghz = (clocks or {}).get("sm_mhz") or ip["sm_clock_max_ghz"] * 1e3
+        peak_sad = rate * 32 / 8 * ip["sms"] * ghz * 1e6
+        int_pipe = {"measured_peak_sad32_per_s": peak_sad, "vabsdiff4_warp_inst_per_clk_per_sm": rate, "sm_mhz": ghz,
+                    "source": "profiles/r2_intpipe.json (tools/intpipe_bench.cu on a B200 of this pool)",
+                    "alu_pipe_pct_of_peak": alu_pct,
+                    "alu_pipe_note": "sm__inst_executed_pipe_alu of the K2 launches in the ncu capture of this build" if alu_pct is not None else traffic_note}
+        if sads_per_pair:
+            eq = sads_per_pair * (B / k2_avg_s) if k2_avg_s > 0 else 0.0
+            int_pipe.update({"reference_sad32_per_pair": sads_per_pair, "sad32_equiv_per_s": eq, "frac": eq / peak_sad,
+                             "what": "SAD32 evaluations of the reference's exhaustive search per second of K2 time / measured VABSDIFF4 peak"})
+    except Exception as exc:
+        int_pipe = {"unavailable": f"profiles/r2_intpipe.json: {type(exc).__name__}"}
     fam = {k: (v[0] / max(v[1], 1)) for k, v in prof.items()}
     roofline = {
         "kernel": "k2_match", "launches": "per step the matching of a batch is k2_match twice (prev->curr in full, curr->prev from "
                   "hints) + k2_hint_scatter; algorithmic bytes, traffic and avg_launch_ms are for that group",
-        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+        # BASELINE.json's metric asks for the HBM fraction, so achieved/peak/frac are the HBM figures; the kernel is bound
+        # by the SM integer (ALU) pipe -- `int_pipe` holds that roofline
+        "bound": "hbm", "binding_resource": "sm_integer_alu_pipe", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": b_match * B, "avg_launch_ms": k2_avg_s * 1e3,
         "share_of_step": (k2_avg_s * 1e3) / step_ms if step_ms else None,
         "kernel_ms_per_step": fam,
         "path": {"bytes_per_pair": b_pair, "achieved": b_pair * value / world / 1e9, "frac": b_pair * value / world / 1e9 / peak},
+        "int_pipe": int_pipe,
         "note": "SAD matching is integer-pipe bound (about 100 int ops per algorithmic byte, SURVEY.md row D3); "
                 "the HBM fraction is reported because BASELINE.json's metric asks for it",
     }
 
-    # ---- CPU baseline on this box's host cores (bounded sample) ----------------------------
-    cpu = None
-    if world == 1 and not args.no_cpu:
-        cores = max(1, min(os.cpu_count() or 1, 64))
-        ppw = 12
-        v, kind, wall, total = cpu_throughput(W, H, ppw, cores)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
-               "sample": f"{cores} single-threaded processes x {ppw} consecutive pairs ({total} pairs, {wall:.1f} s wall) of "
-                         f"the same {W}x{H} synthetic sequence type: myComputeFeatures+myMatching from oracle/_ref, "
-                         f"bucketing via the oracle port"}
-
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "metric": metric_name(W, H), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": step_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": f"configs[1]: {W}x{H} frame pairs, extract+match+bucket, batch of {B} consecutive frames per step per GPU",
-                   "pairs_per_step": pairs_per_step, "batch_per_gpu": B, "bucket": "2 per 50x50",
-                   "l2": f"inputs larger than L2: pool of {pool_frames} frames ({pool_frames * H * pitch / 1e6:.0f} MB) cycled",
+        "config": {"workload": workload_name(args),
+                   "pairs_per_step": pairs_per_step, "batch_per_gpu": B, "sequences_per_gpu": nq, "bucket": "2 per 50x50",
+                   "l2": f"inputs larger than L2: pool of {pool_frames * nq} frames ({pool_frames * nq * H * pitch / 1e6:.0f} MB) cycled",
                    "features_per_frame": n_c, "raw_matches_per_pair": n_m, "bucketed_per_pair": n_b,
-                   "sharding": "independent sequences per GPU, no collective", "host_affinity": host_affinity,
-                   "sensor_noise": (f"uniform +-{args.noise} grey levels per frame" if args.noise > 0 else
-                                    "none: frames are exact integer translations of one canvas (best case for K2's exact pruning; "
-                                    "--noise N and profiles/*noise* give the figures with sensor noise)")},
+                   "sharding": ("8 sequences (seeds 1..8) round-robin over the ranks, no collective" if args.config == 5 else
+                                "independent sequences per GPU, no collective"), "host_affinity": host_affinity,
+                   "sensor_noise": f"uniform +-{args.noise} grey levels, independent per frame (both arms)"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * H * pitch) * world,
                 "d2h_bytes_per_step": int(counts[0].nbytes + B * max_keep * 48) * world,
@@ -453,7 +554,7 @@ def run_ours(args):
         "gpu_launches": int(launches) * world,
         "roofline": roofline,
         "cpu_baseline": cpu,
-        "with_sensor_noise": noisy,
+        "other_noise_levels": extra or None,
     }
     print(json.dumps(line), flush=True)
     if dist is not None:
@@ -467,15 +568,30 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--width", type=int, default=W_DEFAULT)
-    ap.add_argument("--height", type=int, default=H_DEFAULT)
-    ap.add_argument("--batch", type=int, default=128, help="frame pairs per step per GPU")
-    ap.add_argument("--pool", type=int, default=384, help="distinct frames cycled (keeps inputs larger than L2)")
+    ap.add_argument("--config", type=int, default=1, choices=[1, 5],
+                    help="BASELINE.json config: 1 = configs[1], 1241x376 frame pairs (the headline); 5 = configs[4], 8 sequences of 2048x1024")
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--batch", type=int, default=None, help="frame pairs per step: per GPU (config 1), of the whole job (config 5)")
+    ap.add_argument("--sequences", type=int, default=8, help="config 5: independent sequences of the job")
+    ap.add_argument("--pool", type=int, default=None, help="distinct frames cycled per GPU (keeps inputs larger than L2)")
     ap.add_argument("--rows", type=int, default=0, help="match_rows_per_cta tuning knob (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
-    ap.add_argument("--no-noise-leg", action="store_true", help="skip the extra device-resident leg on noisy frames (N=1)")
-    ap.add_argument("--noise", type=int, default=0, help="add uniform +-N grey levels of independent noise to every frame (our arm only)")
+    ap.add_argument("--no-extra-legs", "--no-noise-leg", dest="no_extra_legs", action="store_true",
+                    help="skip the extra device-resident legs at other noise levels (N=1)")
+    ap.add_argument("--noise", type=int, default=NOISE_DEFAULT,
+                    help="uniform +-N grey levels of independent sensor noise on every frame, both arms (0 = best case)")
     args = ap.parse_args()
+    if args.config == 5:
+        args.width, args.height = args.width or 2048, args.height or 1024
+        args.batch = args.batch or 64
+        args.pool = args.pool or 192
+        if args.steps == 200:
+            args.steps = 40
+    else:
+        args.width, args.height = args.width or W_DEFAULT, args.height or H_DEFAULT
+        args.batch = args.batch or 128
+        args.pool = args.pool or 384
     if args.impl == "reference":
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -48,7 +48,8 @@ class VoGeometry(C.Structure):
 EXPORTS = [
     "vo_engine_create", "vo_engine_destroy", "vo_engine_geometry", "vo_engine_synchronize", "vo_remove_outliers_host",
     "vo_remove_outliers", "vo_fence_record",
-    "vo_fence_wait", "vo_last_error", "vo_version", "vo_compute_features", "vo_matching", "vo_bucket_matches", "vo_push_back", "vo_match_features",
+    "vo_fence_wait", "vo_last_error", "vo_version", "vo_compute_features", "vo_matching", "vo_matching_iter",
+    "vo_remove_outliers_bucket", "vo_bucket_matches", "vo_push_back", "vo_match_features",
     "vo_bucket_features", "vo_get_matches", "vo_num_matches", "vo_set_matches", "vo_dump_features",
     "vo_batch_extract_host", "vo_batch_extract_device", "vo_batch_match", "vo_batch_counts",
     "vo_batch_get_matches", "vo_batch_download_async", "vo_slot_dump_features", "vo_slot_feature_count",
@@ -79,11 +80,15 @@ def load_library() -> C.CDLL:
     if _lib is not None:
         return _lib
     path = _build.LIB
-    try:
-        path = _build.build_library()
-    except Exception:
-        if not os.path.exists(path):
-            raise
+    alt = os.environ.get("VO_B200_LIB")  # developer A/B switch: another build of the same sources (tools/ab_build.py)
+    if alt:
+        path = alt
+    else:
+        try:
+            path = _build.build_library()
+        except Exception:
+            if not os.path.exists(path):
+                raise
     lib = C.CDLL(path)
     lib.vo_last_error.restype = C.c_char_p
     lib.vo_version.restype = C.c_char_p
@@ -96,6 +101,8 @@ def load_library() -> C.CDLL:
         "vo_engine_synchronize": [vp],
         "vo_compute_features": [vp, vp, i32, vp, vp, i32],
         "vo_matching": [vp, vp, vp, vp, vp, i32, vp, i32, C.POINTER(i32)],
+        "vo_matching_iter": [vp, vp, vp, vp, vp, i32, vp, i32, C.POINTER(i32), i32],
+        "vo_remove_outliers_bucket": [vp, vp, C.POINTER(i32), vp, i32, C.POINTER(i32)],
         "vo_bucket_matches": [vp, vp, i32, i32, f32, f32, vp, i32, C.POINTER(i32)],
         "vo_push_back": [vp, vp, vp, C.POINTER(i32), i32],
         "vo_match_features": [vp, i32],
@@ -231,6 +238,24 @@ class Engine:
         self._check(self.lib.vo_matching(self.h, _ptr(m1p), _ptr(n1p), _ptr(m1c), _ptr(n1c), m1p.shape[3],
                                          _ptr(out), cap, C.byref(n)))
         return out[: n.value].copy()
+
+    def matching_iter(self, m1p, n1p, m1c, n1c, iter_: int, cap: int | None = None):
+        """myMatching(..., iter) of the FPGA build (hls_opencl/kernel/myMatch.hpp:51-57): iter == 0 -> zero matches"""
+        cap = cap or self.max_matches
+        out = np.zeros(cap, P_MATCH_DTYPE)
+        n = C.c_int32(-1)
+        self._check(self.lib.vo_matching_iter(self.h, _ptr(m1p), _ptr(n1p), _ptr(m1c), _ptr(n1c), m1p.shape[3], _ptr(out), cap,
+                                              C.byref(n), iter_))
+        return out[: n.value].copy()
+
+    def remove_outliers_bucket(self, matches: np.ndarray):
+        """removeOutliers(in, in_cnt, out, out_cnt) of the FPGA build (hls_opencl/kernel/remove_outliers.hpp:9-11): Delaunay
+        filter then bucketing 2 per 50x50.  Returns None when the operator left its outputs untouched (<= 3 matches)."""
+        buf = np.array(matches, dtype=P_MATCH_DTYPE, copy=True)
+        out = np.zeros(max(len(buf), 1), P_MATCH_DTYPE)
+        n_in, n_out = C.c_int32(len(buf)), C.c_int32(-1)
+        self._check(self.lib.vo_remove_outliers_bucket(self.h, _ptr(buf), C.byref(n_in), _ptr(out), len(out), C.byref(n_out)))
+        return None if n_out.value < 0 else out[: n_out.value].copy()
 
     def bucket_matches(self, matches: np.ndarray, max_features=2, bw=50.0, bh=50.0):
         matches = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)

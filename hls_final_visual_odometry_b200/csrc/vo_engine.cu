@@ -343,11 +343,14 @@ vo_status stage_end(vo_engine* e) {
 }
 
 vo_status set_pairs(vo_engine* e, int pair0, int n, const int32_t* prev, const int32_t* curr) {
+  // validate everything BEFORE stage_begin advances the table generation: an error must leave the current tables intact
+  if (pair0 < 0 || n < 0 || pair0 + n > e->n_pairbuf) return fail(VO_ERR_INVALID, "pairs [%d, %d) outside the %d pair buffers", pair0, pair0 + n, e->n_pairbuf);
+  for (int i = 0; i < n; i++)
+    if (prev[i] < 0 || prev[i] >= e->n_slots || curr[i] < 0 || curr[i] >= e->n_slots)
+      return fail(VO_ERR_INVALID, "pair %d: slot out of range", i);
   vo_status sb = stage_begin(e);
   if (sb != VO_OK) return sb;
   for (int i = 0; i < n; i++) {
-    if (prev[i] < 0 || prev[i] >= e->n_slots || curr[i] < 0 || curr[i] >= e->n_slots)
-      return fail(VO_ERR_INVALID, "pair %d: slot out of range", i);
     e->h_pairs[pair0 + i] = make_int2(prev[i], curr[i]);
     // the two searches of myMatching (src/myMatch.cpp:148-176): curr -> prev, prev -> curr, both with the flow window
     e->h_edges[2 * (pair0 + i)] = make_int4(curr[i], prev[i], e->g.rad_v, kFlowReach);
@@ -432,11 +435,13 @@ vo_status set_quads(vo_engine* e, int item0, int n, const int32_t* s1p, const in
                     const int32_t* s2c, int disp_tolerance) {
   if (e->epi != 4) return fail(VO_ERR_STATE, "quad matching needs an engine created with vo_config.stereo = 1");
   if (disp_tolerance < 0 || disp_tolerance > 16) return fail(VO_ERR_INVALID, "match_disp_tolerance %d outside [0,16]", disp_tolerance);
+  if (item0 < 0 || n < 0 || item0 + n > e->n_pairbuf) return fail(VO_ERR_INVALID, "items [%d, %d) outside the %d pair buffers", item0, item0 + n, e->n_pairbuf);
+  for (int i = 0; i < n; i++)  // before stage_begin: an error must leave the current tables intact
+    for (int s : {s1p[i], s2p[i], s1c[i], s2c[i]})
+      if (s < 0 || s >= e->n_slots) return fail(VO_ERR_INVALID, "item %d: slot out of range", i);
   vo_status sb = stage_begin(e);
   if (sb != VO_OK) return sb;
   for (int i = 0; i < n; i++) {
-    for (int s : {s1p[i], s2p[i], s1c[i], s2c[i]})
-      if (s < 0 || s >= e->n_slots) return fail(VO_ERR_INVALID, "item %d: slot out of range", i);
     const int k = item0 + i;
     e->h_quads[k] = make_int4(s1p[i], s2p[i], s1c[i], s2c[i]);
     e->h_pairs[k] = make_int2(s1p[i], s1c[i]);
@@ -784,6 +789,29 @@ vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, in
     CU_TRY(cudaStreamSynchronize(e->stream));
   }
   return VO_OK;
+}
+
+// the reference's FPGA operator signatures, 1:1 (hls_opencl/kernel/myMatch.hpp:51-57, remove_outliers.hpp:9-11)
+vo_status vo_matching_iter(vo_engine* e, const int32_t* m1p, const int32_t* n1p, const int32_t* m1c, const int32_t* n1c,
+                           int32_t cap_stride, vo_p_match* p_matched, int32_t p_matched_cap, int32_t* p_matched_num, int32_t iter) {
+  if (iter == 0) {  // frame 0 has no previous features: hls_opencl/kernel/myMatch.cpp:221-224
+    if (!p_matched_num) return fail(VO_ERR_INVALID, "null argument");
+    *p_matched_num = 0;
+    return VO_OK;
+  }
+  return vo_matching(e, m1p, n1p, m1c, n1c, cap_stride, p_matched, p_matched_cap, p_matched_num);
+}
+
+vo_status vo_remove_outliers_bucket(vo_engine* e, const vo_p_match* in, const int32_t* in_cnt, vo_p_match* out, int32_t out_cap,
+                                    int32_t* out_cnt) {
+  if (!e || !in_cnt || !out_cnt || (!in && *in_cnt > 0)) return fail(VO_ERR_INVALID, "null argument");
+  int32_t n = *in_cnt;
+  if (n <= 3) return VO_OK;  // hls_opencl/kernel/remove_outliers.cpp:20-21: returns with the outputs untouched
+  if (n > e->cfg.max_matches) return fail(VO_ERR_CAPACITY, "%d matches > engine capacity %d", n, e->cfg.max_matches);
+  std::vector<vo_p_match> tmp(in, in + n);
+  vo_status s = vo_remove_outliers_host(tmp.data(), &n);  // Delaunay support filter (host stage), then ...
+  if (s != VO_OK) return s;
+  return vo_bucket_matches(e, tmp.data(), n, 2, 50.f, 50.f, out, out_cap, out_cnt);  // ... bucketing 2 per 50x50: .cpp:107-109
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -48,10 +48,19 @@ constexpr int kSegW = kMaxCols + 1;
 constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
 constexpr int kMaxWarps = 16;
 constexpr int kTwoWordVotes = 3;  // a warp filters with both signature words when more than 3/4 of its searching lanes hold a non-zero bound
-constexpr int kQueue = 64;      // deferred exact evaluations per warp
+constexpr int kQueue = 128;     // deferred exact evaluations per warp: < 32 left over + up to kAppend per lane and pass
+#ifndef VO_K2_APPEND
+#define VO_K2_APPEND 3
+#endif
+#ifndef VO_K2_FLOOD
+#define VO_K2_FLOOD 20
+#endif
+constexpr int kAppend = VO_K2_APPEND;  // queue entries a lane contributes per compaction pass (1..3: the count travels in two ballots)
+constexpr int kFlood = VO_K2_FLOOD;    // a lane with at least this many filter hits in a chunk of 32 groups is expanded by the whole warp
 constexpr int kBig = 1 << 20;
 static_assert(kCandCap <= 2048, "k2 hard pass packs the staged position into 11 bits");
-constexpr int kHardCap = 2048;  // origins per chunk handed to the warp-per-origin pass
+static_assert(kAppend >= 1 && kAppend <= 3 && 31 + 32 * kAppend <= kQueue, "a compaction pass must fit the queue");
+constexpr int kHardCap = 1024;  // origins per chunk handed to the warp-per-origin pass
 constexpr int kSeedGood = 128;  // an origin whose seed SAD is above this has no partner worth a lane-per-origin walk: warp-per-origin pass
 constexpr int kHitBudget = 4;   // default of vo_config.match_hit_budget: filter hits (groups of 4) a lane may queue before its origin is handed over
 
@@ -69,7 +78,7 @@ struct K2Tables {
 struct __align__(128) K2Smem {
   K2Tables t;
   uint32_t sbest[kMaxWarps][32];      // running best key of the 32 origins of a warp's task
-  uint32_t queue[kMaxWarps][kQueue + 32];  // deferred exact evaluations: owner lane << 16 | candidate group (+32 dump slots)
+  uint32_t queue[kMaxWarps][kQueue];  // deferred exact evaluations: owner lane << 16 | candidate group
   int32_t hard_n;                     // origins handed to the warp-per-origin pass in this chunk
   uint16_t hard[kHardCap];            // origin column (bit 15) | col_idx
   __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
@@ -366,6 +375,23 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           const int p = (int)(k1 & 0xFFFFFu);
           if (p >= t.rowStart[vlo] && p < t.rowStart[vhi]) bestk = min(bestk, cand_key(S, p, a, b, lo_p, hi_p));
         }
+#ifdef VO_K2_SEEDX
+        if (reach >= kMaxV) {  // second look at the own bins: every candidate the first seed's SAD cannot exclude, exactly
+          int tqs = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
+          const bool me = full && vlo < vhi;
+          const int pa = me ? t.rowStart[vlo] : 0, pb = me ? t.rowStart[vhi] : 0;
+          for (int r = smin; r <= smax; r++) {
+            const int p1 = t.segOff[r][jown + 1];
+            for (int p = t.segOff[r][jown]; p < p1; p++) {
+              const int q = (int)sad4(qb, S.q1[p], sad4(qa, S.q[p], 0u));
+              if (p >= pa && p < pb && q <= tqs) {
+                bestk = min(bestk, cand_key(S, p, a, b, lo_p, hi_p));
+                tqs = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
+              }
+            }
+          }
+        }
+#endif
       }
       sbest[lane] = bestk;
       __syncwarp();
@@ -433,7 +459,41 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
       };
 
-      for (int r = rlo; r < rhi; r++) {
+      // The set bits of lane L's hit mask, evaluated by the whole warp at once: lane j takes the group of bit 31 - j
+      // (group g0 + j), re-tests its four candidates against L's bound and evaluates the survivors exactly.
+      auto expand = [&](int L, uint32_t mine, int g0) {
+        const uint32_t mL = __shfl_sync(FULL, mine, L);
+        uint4 oa, ob;
+        oa.x = __shfl_sync(FULL, a.x, L); oa.y = __shfl_sync(FULL, a.y, L);
+        oa.z = __shfl_sync(FULL, a.z, L); oa.w = __shfl_sync(FULL, a.w, L);
+        ob.x = __shfl_sync(FULL, b.x, L); ob.y = __shfl_sync(FULL, b.y, L);
+        ob.z = __shfl_sync(FULL, b.z, L); ob.w = __shfl_sync(FULL, b.w, L);
+        const uint32_t olo = __shfl_sync(FULL, lo_p, L), ohi = __shfl_sync(FULL, hi_p, L);
+        const uint32_t oq = __shfl_sync(FULL, qa, L), oq1 = __shfl_sync(FULL, qb, L);
+        const int otq = __shfl_sync(FULL, tq, L);
+        uint32_t k = kNone;
+        if ((mL << lane) & 0x80000000u) {
+          const int p = (g0 + lane) << 2;
+          const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
+          if ((int)sad4(oq1, q1.x, sad4(oq, qq.x, 0u)) <= otq) k = cand_key(S, p, oa, ob, olo, ohi);
+          if ((int)sad4(oq1, q1.y, sad4(oq, qq.y, 0u)) <= otq) k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
+          if ((int)sad4(oq1, q1.z, sad4(oq, qq.z, 0u)) <= otq) k = min(k, cand_key(S, p + 2, oa, ob, olo, ohi));
+          if ((int)sad4(oq1, q1.w, sad4(oq, qq.w, 0u)) <= otq) k = min(k, cand_key(S, p + 3, oa, ob, olo, ohi));
+        }
+        k = __reduce_min_sync(FULL, k);
+        if (lane == L && k < bestk) {  // (queued entries of L still pending add to sbest[L] by atomicMin)
+          atomicMin(&sbest[lane], k);
+          bestk = min(bestk, k);
+          tq = (int)(bestk >> 19);
+        }
+        __syncwarp();
+      };
+
+      // rows in the order own row, then the rest: the partner of a small flow sits in the own row, so bounds tighten first
+      const int rown = min(max(__shfl_sync(FULL, v, 0), rlo), rhi - 1);
+      for (int ri = rlo - 1; ri < rhi; ri++) {
+        if (ri == rown) continue;
+        const int r = (ri < rlo) ? rown : ri;
         bool act = (r >= vlo) && (r < vhi);
         int tqe = act ? tq : -1;  // tq while this lane searches the current row, else -1 (never passes)
         int pg = t.segOff[r][j0] >> 2;            // candidate groups of 4 (every bin list is padded to 4)
@@ -444,42 +504,46 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         while (pg < pg1) {
           const int nb = min(32, pg1 - pg);
           uint32_t m = 0;  // MISS bits while filtering, newest group in bit 0
+          // bias + Q has its sign bit set exactly when Q exceeds the lane's bound (tqe = -1: always; no bound yet: never), so a
+          // group of four candidates misses iff the AND of its four sums is negative: 2 LOP3 + 1 SHF per group on top of
+          // the VABSDIFF4s, no minimum and no subtraction
+          const uint32_t bias = 0x7FFFFFFFu - (uint32_t)tqe;
           if (PRUNE && two) {
             const uint4* qp = Q4 + pg;
             const uint4* rp = Q14 + pg;
-            auto gmin = [&](const uint4& x, const uint4& y) {
-              return (int)min(min(sad4(qb, y.x, sad4(qa, x.x, 0u)), sad4(qb, y.y, sad4(qa, x.y, 0u))),
-                              min(sad4(qb, y.z, sad4(qa, x.z, 0u)), sad4(qb, y.w, sad4(qa, x.w, 0u))));
+            auto gmiss = [&](const uint4& x, const uint4& y) {
+              return (sad4(qb, y.x, sad4(qa, x.x, bias)) & sad4(qb, y.y, sad4(qa, x.y, bias))) &
+                     (sad4(qb, y.z, sad4(qa, x.z, bias)) & sad4(qb, y.w, sad4(qa, x.w, bias)));
             };
             int i = 0;
-#pragma unroll 2
-            for (; i + 1 < nb; i += 2, qp += 2, rp += 2) {
-              const int ma = gmin(qp[0], rp[0]), mb = gmin(qp[1], rp[1]);
-              m = __funnelshift_l((uint32_t)(tqe - ma), m, 1);
-              m = __funnelshift_l((uint32_t)(tqe - mb), m, 1);
+#pragma unroll 1
+            for (; i + 3 < nb; i += 4) {
+              const uint32_t ma = gmiss(qp[i], rp[i]), mb = gmiss(qp[i + 1], rp[i + 1]);
+              const uint32_t mc = gmiss(qp[i + 2], rp[i + 2]), md = gmiss(qp[i + 3], rp[i + 3]);
+              m = __funnelshift_l(ma, m, 1);
+              m = __funnelshift_l(mb, m, 1);
+              m = __funnelshift_l(mc, m, 1);
+              m = __funnelshift_l(md, m, 1);
             }
-            if (i < nb) m = __funnelshift_l((uint32_t)(tqe - gmin(qp[0], rp[0])), m, 1);
+#pragma unroll 1
+            for (; i < nb; i++) m = __funnelshift_l(gmiss(qp[i], rp[i]), m, 1);
             m = ~m;
           } else if (PRUNE) {
             const uint4* qp = Q4 + pg;  // one uint4 = the signatures of one group of 4 candidates
+            auto gmiss1 = [&](const uint4& x) {
+              return (sad4(qa, x.x, bias) & sad4(qa, x.y, bias)) & (sad4(qa, x.z, bias) & sad4(qa, x.w, bias));
+            };
             int i = 0;
-#pragma unroll 2
-            for (; i + 3 < nb; i += 4, qp += 4) {
-              const uint4 qx = qp[0], qy = qp[1], qz = qp[2], qw = qp[3];
-              const int ma = min(min(sadq(qa, qx.x), sadq(qa, qx.y)), min(sadq(qa, qx.z), sadq(qa, qx.w)));
-              const int mb = min(min(sadq(qa, qy.x), sadq(qa, qy.y)), min(sadq(qa, qy.z), sadq(qa, qy.w)));
-              const int mc = min(min(sadq(qa, qz.x), sadq(qa, qz.y)), min(sadq(qa, qz.z), sadq(qa, qz.w)));
-              const int md = min(min(sadq(qa, qw.x), sadq(qa, qw.y)), min(sadq(qa, qw.z), sadq(qa, qw.w)));
-              m = __funnelshift_l((uint32_t)(tqe - ma), m, 1);  // shifts in the sign: 1 = lower bound above the threshold
-              m = __funnelshift_l((uint32_t)(tqe - mb), m, 1);
-              m = __funnelshift_l((uint32_t)(tqe - mc), m, 1);
-              m = __funnelshift_l((uint32_t)(tqe - md), m, 1);
+#pragma unroll 1
+            for (; i + 3 < nb; i += 4) {
+              const uint32_t ma = gmiss1(qp[i]), mb = gmiss1(qp[i + 1]), mc = gmiss1(qp[i + 2]), md = gmiss1(qp[i + 3]);
+              m = __funnelshift_l(ma, m, 1);  // shifts in the sign: 1 = lower bound above the threshold
+              m = __funnelshift_l(mb, m, 1);
+              m = __funnelshift_l(mc, m, 1);
+              m = __funnelshift_l(md, m, 1);
             }
-            for (; i < nb; i++, qp++) {
-              const uint4 qx = qp[0];
-              const int ma = min(min(sadq(qa, qx.x), sadq(qa, qx.y)), min(sadq(qa, qx.z), sadq(qa, qx.w)));
-              m = __funnelshift_l((uint32_t)(tqe - ma), m, 1);
-            }
+#pragma unroll 1
+            for (; i < nb; i++) m = __funnelshift_l(gmiss1(qp[i]), m, 1);
             m = ~m;
           } else {
             m = act ? kNone : 0u;
@@ -491,19 +555,40 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             if (!two && hits > hit_budget && hand_over()) { m = 0u; act = false; tqe = -1; K2STAT(5, 1); }
           }
           const uint32_t gfirst = lane16 + (uint32_t)(pg + nb - 32);  // owner lane << 16 + group of bit 31 (mod 2^32)
-          for (;;) {
-            const uint32_t bal = __ballot_sync(FULL, m != 0u);
-            if (bal == 0u) break;
-            const int z = __clz((int)m);  // 32 when this lane has nothing left
-            const int slot = (m != 0u) ? qn + __popc(bal & lt_mask) : kQueue + lane;  // branch-free: idle lanes hit a dump slot
-            queue[slot] = gfirst + (uint32_t)z;
-            m &= ~__funnelshift_rc(0x80000000u, 0u, z);  // clears the bit; shift 32 -> 0
-            qn += __popc(bal);
-            if (qn >= 32) {
-              __syncwarp();
-              flush();
-              tqe = act ? tq : -1;
+          uint32_t anyb = __ballot_sync(FULL, m != 0u);
+          if (anyb != 0u) {
+            // (1) a lane the bound hardly prunes (no partner in sight yet, or none at all) would feed the queue for many
+            //     rounds while 31 lanes wait: the whole warp takes its mask instead, lane j its group j
+            int left = __popc(m);
+            uint32_t flood = __ballot_sync(FULL, left >= kFlood);
+            while (flood != 0u) {
+              const int L = __ffs((int)flood) - 1;
+              flood &= flood - 1u;
+              expand(L, m, pg + nb - 32);
+              if (lane == L) { m = 0u; left = 0; }
             }
+            // (2) the other lanes append up to kAppend groups per pass at positions given by two ballots (the count is a
+            //     2-bit number), then the queue is drained 32 entries at a time
+            anyb = __ballot_sync(FULL, m != 0u);
+            while (anyb != 0u) {
+              const int cn = min(left, kAppend);
+              const uint32_t b0 = __ballot_sync(FULL, cn & 1), b1 = __ballot_sync(FULL, cn & 2);
+              const int pos = qn + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask);
+#pragma unroll
+              for (int k = 0; k < kAppend; k++) {
+                if (k < cn) {
+                  const int z = __clz((int)m);
+                  queue[pos + k] = gfirst + (uint32_t)z;
+                  m &= ~(0x80000000u >> z);
+                }
+              }
+              left -= cn;
+              qn += __popc(b0) + 2 * __popc(b1);
+              __syncwarp();
+              while (qn >= 32) flush();
+              anyb = __ballot_sync(FULL, m != 0u);
+            }
+            tqe = act ? tq : -1;
           }
           pg += nb;
         }

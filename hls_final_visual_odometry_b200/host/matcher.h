@@ -87,6 +87,11 @@ class Matcher {
   // reference's removeOutliers, src/remove_outliers.cpp:4); in/out list
   void setOutlierFilter(std::function<void(std::vector<Matcher::p_match>&)> f) { outlier_filter = f; }
 
+  // EXTENSION (unpinned): parameters::nms_tau is dead on the reference's executed path, which always
+  // thresholds at 50 (src/myComputeFeature.cpp:157), and this class ignores it the same way.  Call before the first
+  // pushBack to make it live instead.  nms_n / match_binsize / match_radius stay ignored like in the reference.
+  void useLiveNmsTau(bool on) { live_nms_tau = on; }
+
   // last C-ABI status (0 = ok) and message, for callers that want more than the reference's cerr line
   int lastStatus() const { return last_status; }
   const char* lastError() const;
@@ -99,6 +104,7 @@ class Matcher {
   bool stereo;
   vo_engine* eng;
   int last_status;
+  bool live_nms_tau = false;
   std::function<void(std::vector<Matcher::p_match>&)> outlier_filter;
 };
 

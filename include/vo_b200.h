@@ -141,6 +141,19 @@ vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, in
                             float bucket_w, float bucket_h, vo_p_match* out, int32_t out_cap,
                             int32_t* n_out);
 
+/* The reference's FPGA operator signatures, 1:1, for a host that drives the three kernels directly
+ * (hls_opencl/host/main2.cpp:429-444,477-504):
+ *   myMatching(m1p, m1c, n1p, n1c, p_matched, p_matched_num, iter)     hls_opencl/kernel/myMatch.hpp:51-57
+ *     iter == 0 (first frame, no previous features) -> *p_matched_num = 0, nothing else touched (.cpp:221-224)
+ *   removeOutliers(p_matched, p_matched_cnt, p_matched_res, p_matched_res_cnt)   hls_opencl/kernel/remove_outliers.hpp:9-11
+ *     = Delaunay support filter, THEN bucketing with max_features = 2, 50 x 50 px (.cpp:104-154); with
+ *     *in_cnt <= 3 it returns with out / *out_cnt untouched, exactly as the reference (.cpp:20-21). */
+vo_status vo_matching_iter(vo_engine* e, const int32_t* m1p, const int32_t* n1p, const int32_t* m1c,
+                           const int32_t* n1c, int32_t cap_stride, vo_p_match* p_matched,
+                           int32_t p_matched_cap, int32_t* p_matched_num, int32_t iter);
+vo_status vo_remove_outliers_bucket(vo_engine* e, const vo_p_match* in, const int32_t* in_cnt,
+                                    vo_p_match* out, int32_t out_cap, int32_t* out_cnt);
+
 /* ---------------------------------------------------------------------------------------- */
 /* 2. Matcher level: a prev/curr ring on frame slots 0/1 of the engine                         */
 /* ---------------------------------------------------------------------------------------- */

@@ -118,3 +118,35 @@ def test_batch_equals_oracle(setup):
         wb = orc.bucket_features(want, 2, 50.0, 50.0)
         assert bk_n[p] == len(wb)
         assert_matches_equal(eng.batch_get_matches(p, 1), wb, f"batch bucketed {p}")
+
+
+def test_fpga_operator_signatures(setup):
+    """the reference's FPGA-side operator signatures, 1:1: myMatching(..., iter) (hls_opencl/kernel/myMatch.hpp:51-57, iter == 0 ->
+    zero matches) and the fused removeOutliers = Delaunay filter then bucketing 2 per 50x50 (remove_outliers.hpp:9-11)"""
+    from hls_final_visual_odometry_b200.api import remove_outliers_host
+    w, h, seq, orc, eng = setup
+    m0, n0, _ = orc.compute_features(seq[0])
+    m1, n1, _ = orc.compute_features(seq[1])
+    want, _ = orc.matching(m0, n0, m1, n1)
+    assert len(eng.matching_iter(m0, n0, m1, n1, 0)) == 0
+    assert_matches_equal(eng.matching_iter(m0, n0, m1, n1, 3), want, f"{w}x{h} iter 3")
+    fused = eng.remove_outliers_bucket(want)
+    assert_matches_equal(fused, orc.bucket_features(remove_outliers_host(want), 2, 50.0, 50.0), f"{w}x{h} fused removeOutliers")
+    assert eng.remove_outliers_bucket(want[:3]) is None    # <= 3 matches: outputs untouched (remove_outliers.cpp:20-21)
+
+
+def test_bad_slots_leave_the_pair_tables_intact(setup):
+    """an out-of-range slot is refused before the table generation advances (round-1 advisor finding): the previous
+    batch's tables stay valid and the next good call works"""
+    from hls_final_visual_odometry_b200 import VoError
+    from hls_final_visual_odometry_b200 import api
+    w, h, seq, orc, eng = setup
+    eng.batch_extract_host(0, seq[:2])
+    eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+    good = eng.batch_get_matches(0, 0)
+    for prev, curr in (([0], [99]), ([-1], [1]), ([0, 0, 0], [1, 1, 1])):   # bad slot, bad slot, more pairs than buffers
+        with pytest.raises(VoError) as ei:
+            eng.batch_match(prev, curr, max_features=2, bw=50.0, bh=50.0)
+        assert ei.value.status == api.VO_ERR_INVALID
+    eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+    assert_matches_equal(eng.batch_get_matches(0, 0), good, "after refused calls")

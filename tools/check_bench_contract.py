@@ -27,7 +27,24 @@ def main():
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and r["peak"] > 0 and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
     assert set(d["clocks"]) >= {"sm_mhz", "sm_max_mhz", "reasons"}
-    assert d["with_sensor_noise"]["value"] > 0
+    assert "int_pipe" in r and r["binding_resource"] == "sm_integer_alu_pipe"
+    assert "+-2 grey levels" in d["config"]["workload"]      # the headline runs on frames with sensor noise
+    legs = d["other_noise_levels"]
+    assert legs["best_case_noise_free"]["value"] > 0 and legs["noise_8"]["value"] > 0
+    # the reference arm names the same workload and metric (the driver compares the two lines)
+    ref = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert ref.returncode == 0, ref.stderr[-2000:]
+    rd = json.loads([ln for ln in ref.stdout.splitlines() if ln.strip()][-1])
+    assert rd["impl"] == "reference" and rd["metric"] == d["metric"] and rd["config"]["workload"] == d["config"]["workload"]
+    assert rd["cpu_baseline"]["value"] == rd["value"] and rd["e2e"]["h2d_bytes_per_step"] == 0
+    # config 5 (BASELINE configs[4]) is a runnable, correctly labelled configuration
+    c5 = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--config", "5", "--steps", "2", "--warmup", "3", "--batch", "16",
+                         "--pool", "32", "--no-cpu", "--no-extra-legs"], capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert c5.returncode == 0, c5.stderr[-2000:]
+    cd = json.loads([ln for ln in c5.stdout.splitlines() if ln.strip()][-1])
+    assert cd["metric"] == "frame_pairs_per_s_2048x1024" and cd["scaling"] == "strong" and cd["config"]["sequences_per_gpu"] == 8
+    assert cd["config"]["pairs_per_step"] == 16 and cd["value"] > 0
     print("bench contract ok")
 
 
