@@ -34,6 +34,14 @@
 #include <cstdio>
 
 namespace vo {
+// -DVO_DEBUG_BOUNDS: every shared-memory index K2 computes is checked and a violation traps the launch (the pool's
+// compute-sanitizer is closed, profiles/r2_sanitizer_refused.txt; tools/bounds_check.sh runs the parity and stress suites
+// against such a build)
+#ifdef VO_DEBUG_BOUNDS
+#define K2CHECK(cond) do { if (!(cond)) { printf("K2CHECK failed: %s (line %d, block %d,%d,%d thread %d)\n", #cond, __LINE__, blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x); __trap(); } } while (0)
+#else
+#define K2CHECK(cond)
+#endif
 #ifdef VO_K2_STATS
 __device__ unsigned long long g_k2_stats[8];
 #define K2STAT(i, n) atomicAdd(&g_k2_stats[i], (unsigned long long)(n))
@@ -61,6 +69,7 @@ constexpr int kBig = 1 << 20;
 static_assert(kCandCap <= 2048, "k2 hard pass packs the staged position into 11 bits");
 static_assert(kAppend >= 1 && kAppend <= 3 && 31 + 32 * kAppend <= kQueue, "a compaction pass must fit the queue");
 constexpr int kHardCap = 1024;  // origins per chunk handed to the warp-per-origin pass
+constexpr uint32_t kSkip = 0xFFFFFFFEu;  // best[] between the chunks of a hinted search: nobody points at this origin (never a real key: SAD <= 8160)
 constexpr int kSeedGood = 128;  // an origin whose seed SAD is above this has no partner worth a lane-per-origin walk: warp-per-origin pass
 constexpr int kHitBudget = 4;   // default of vo_config.match_hit_budget: filter hits (groups of 4) a lane may queue before its origin is handed over
 
@@ -113,6 +122,7 @@ __device__ __forceinline__ int sadq(uint32_t a, uint32_t x) { return (int)sad4(a
 // packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
 __device__ __forceinline__ uint32_t cand_key(const K2Smem& S, int p, const uint4& a, const uint4& b, uint32_t lo_p,
                                              uint32_t hi_p) {
+  K2CHECK(p >= 0 && p < kCandCap);
   const uint2 xr = S.xr[p];
   const uint32_t sad = sad32(a, b, S.lo[p], S.hi[p]);
   const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
@@ -233,8 +243,10 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     // ---- chunk = as many whole rows as fit the staging buffer ------------------------------
     int rb = ra, staged = 0;
     while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
-    // hints (see k2_hint_scatter) are only used when the whole window is staged at once; a chunked window searches in full
-    const bool use_hint = hinted && first_chunk && rb >= row_hi;
+    // hints (see k2_hint_scatter) are validated against the candidate's record in global memory, so they work whether or
+    // not the window is staged in one piece; an origin nobody points at is parked as kSkip until the last chunk
+    const bool use_hint = hinted;
+    const bool last_chunk = rb >= row_hi;
     __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
     if (tid == THREADS - 1) S.hard_n = 0;
     if (tid <= rb - ra) {
@@ -256,6 +268,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       const int dst = t.segOff[v][j];
       const int64_t src = (int64_t)((v * U + ulo + j) * 4 + c) * g.cap;
       const uint32_t rank0 = ((uint32_t)j << 16) | (uint32_t)t.colT[j][v];
+      K2CHECK(dst >= 0 && dst + npad <= kCandCap && n <= g.cap);
       for (int k = lane; k < npad; k += 32) {
         if (k < n) {
           const uint4 d0 = desc_to[(src + k) * 2], d1 = desc_to[(src + k) * 2 + 1];
@@ -294,6 +307,8 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       uint32_t bestk = kNone;
       uint32_t hint = kNone;
       bool full = valid;  // this lane runs an unseeded search (seed pass below)
+      bool skip = false;  // hinted direction: no feature of the other frame points here, the cycle cannot close
+      int lo_full = 0, hi_full = 0;  // the origin's rows before clipping to the staged chunk
       if (valid) {
         while (t.prefO[cc][v + 1] <= o) v++;
         const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
@@ -307,30 +322,39 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int lo_r = max(max(max(vb - 3, 0), ra), v - reach);  // src/myMatch.cpp:92-93,99
         const int hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
         if (lo_r < hi_r) { vlo = lo_r; vhi = hi_r; }
-        if (use_hint) {
+        lo_full = max(max(vb - 3, 0), v - reach);
+        hi_full = min(min(vb + 3, V - 1), v + reach + 1);
+        if (use_hint && first_chunk) {
           hint = bo[o];
           full = false;
-          if (hint == kNone) { vlo = kBig; vhi = 0; }  // no feature of the other frame points here: the cycle cannot close
-        }
-        if (!first_chunk) {
+          skip = hint == kNone;
+        } else if (!first_chunk) {
           bestk = bo[o];
+          skip = bestk == kSkip;
+          if (skip) bestk = kNone;
           if (bestk != kNone) bestk += (uint32_t)j0 << 16;
+          if (use_hint) full = bestk == kNone;  // a validated hint (or better) is already the bound
         }
+        if (skip) { vlo = kBig; vhi = 0; full = false; }
       }
       const int rlo = __reduce_min_sync(FULL, vlo), rhi = __reduce_max_sync(FULL, vhi);
       const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
       const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
       const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
 
-      if (PRUNE && use_hint && vlo < vhi) {
+      if (PRUNE && use_hint && first_chunk && valid && !skip) {
         // the hinted candidate must be one this origin may legally take (bin ranges are not symmetric between the two
-        // directions): locate it in the staged window and evaluate it; anything unexpected -> plain search
+        // directions): locate its record in global memory and evaluate it; anything unexpected -> plain search
         const int jr = (int)((hint >> 16) & 7u), kb = (int)(hint & 0xFFFFu), j = j0 + jr;
         uint32_t k = kNone;
         if (jr < 6 && j < j1) {
-          for (int r = vlo; r < vhi; r++) {
+          for (int r = lo_full; r < hi_full; r++) {
             if (kb >= t.colT[j][r] && kb < t.colT[j][r + 1]) {
-              k = cand_key(S, t.segOff[r][j] + kb - t.colT[j][r], a, b, lo_p, hi_p);
+              const int64_t rec = (int64_t)((r * U + ulo + j) * 4 + c) * g.cap + (kb - t.colT[j][r]);
+              const uint32_t x = __ldg(&xy_to[rec]) + 0x80008000u;
+              const uint32_t sad = sad32(a, b, __ldg(&desc_to[2 * rec]), __ldg(&desc_to[2 * rec + 1]));
+              const uint32_t t1 = x - lo_p, t2 = x - hi_p;
+              if (((t1 & ~t2) & 0x80008000u) == 0x80008000u) k = sad * 0x80000u + (((uint32_t)j << 16) | (uint32_t)kb);
               break;
             }
           }
@@ -434,8 +458,10 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const int n = min(qn, 32);
         qn -= n;
         const bool on = lane < n;
+        K2CHECK(qn >= 0 && qn + n <= kQueue);
         const uint32_t e = on ? queue[qn + lane] : 0u;
         const int owner = (int)(e >> 16), p = (int)(e & 0xFFFFu) << 2;
+        K2CHECK(!on || (owner < 32 && p + 3 < kCandCap));
         uint4 oa, ob;
         oa.x = __shfl_sync(FULL, a.x, owner); oa.y = __shfl_sync(FULL, a.y, owner);
         oa.z = __shfl_sync(FULL, a.z, owner); oa.w = __shfl_sync(FULL, a.w, owner);
@@ -474,6 +500,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         uint32_t k = kNone;
         if ((mL << lane) & 0x80000000u) {
           const int p = (g0 + lane) << 2;
+          K2CHECK(p >= 0 && p + 3 < kCandCap);
           const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
           if ((int)sad4(oq1, q1.x, sad4(oq, qq.x, 0u)) <= otq) k = cand_key(S, p, oa, ob, olo, ohi);
           if ((int)sad4(oq1, q1.y, sad4(oq, qq.y, 0u)) <= otq) k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
@@ -503,6 +530,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         // bits into the exact-evaluation queue, one entry per lane and round.
         while (pg < pg1) {
           const int nb = min(32, pg1 - pg);
+          K2CHECK(pg >= 0 && (pg + nb) * 4 <= kCandCap);
           uint32_t m = 0;  // MISS bits while filtering, newest group in bit 0
           // bias + Q has its sign bit set exactly when Q exceeds the lane's bound (tqe = -1: always; no bound yet: never), so a
           // group of four candidates misses iff the AND of its four sums is negative: 2 LOP3 + 1 SHF per group on top of
@@ -578,6 +606,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
               for (int k = 0; k < kAppend; k++) {
                 if (k < cn) {
                   const int z = __clz((int)m);
+                  K2CHECK(pos + k >= 0 && pos + k < kQueue && m != 0u);
                   queue[pos + k] = gfirst + (uint32_t)z;
                   m &= ~(0x80000000u >> z);
                 }
@@ -595,7 +624,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       }
       __syncwarp();
       while (qn > 0) flush();
-      if (valid && !handed) bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
+      if (valid && !handed) bo[o] = (skip && !last_chunk) ? kSkip : (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
       __syncwarp();  // sbest/queue are reused by this warp's next task
     }
     if (PRUNE) {
@@ -670,6 +699,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             const bool hA = (pA < p1) && (qA <= tl), hB = (pB < p1) && (qB <= tl);
             const uint32_t balA = __ballot_sync(FULL, hA), balB = __ballot_sync(FULL, hB);
             const int nA = __popc(balA);
+            K2CHECK(hn >= 0 && hn + nA + __popc(balB) <= kQueue && p1 <= kCandCap);
             if (hA) queue[hn + __popc(balA & lt_mask)] = ((uint32_t)qA << 11) | (uint32_t)pA;
             if (hB) queue[hn + nA + __popc(balB & lt_mask)] = ((uint32_t)qB << 11) | (uint32_t)pB;
             hn += nA + __popc(balB);
