@@ -25,7 +25,7 @@ cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t*
 cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
                         int cap_stride, cudaStream_t st);
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                      int rows_per_group, int prune, int threads, int hit_budget, int split, cudaStream_t st);
+                      int rows_per_group, int prune, int threads, int seed_good, int split, cudaStream_t st);
 cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* quads, const int2* pairs, int n_items,
                            const uint32_t* best, uint8_t* flags, int32_t* list_cnt, uint32_t* qxy, void* out,
                            int64_t out_stride_matches, int32_t max_matches, int32_t* n_raw, int32_t* status,
@@ -294,7 +294,7 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)pair0 * 2, 2 * n_pairs,
                          e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap, e->rows_per_group, e->prune,
-                         e->match_threads, e->cfg.match_hit_budget, e->split_match, e->stream));
+                         e->match_threads, e->cfg.match_seed_good, e->split_match, e->stream));
     e->launches += (e->prune && e->split_match) ? 3 : 1;
   }
   {
@@ -402,7 +402,7 @@ vo_status do_match_quad(vo_engine* e, int item0, int n_items, int refinement, in
   {
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)item0 * 4, 4 * n_items, e->d_best + (int64_t)item0 * 4 * lists,
-                         e->rows_per_group, e->prune, e->match_threads, e->cfg.match_hit_budget, 0, e->stream));
+                         e->rows_per_group, e->prune, e->match_threads, e->cfg.match_seed_good, 0, e->stream));
     e->launches += 1;
   }
   {

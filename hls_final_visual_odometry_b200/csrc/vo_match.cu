@@ -9,23 +9,26 @@
 // K2 (k2_match): one CTA per (pair of origin u-bin columns, group of origin v-bin rows, class,
 // direction, frame pair).  The CTA stages the target window of the OTHER frame -- up to 7 u-bin
 // columns x the v-bin rows its origins can see -- into shared memory ordered (v_bin, u_bin, slot),
-// every bin list padded to a multiple of 4.  A LANE owns an origin: the 32 lanes of a warp hold 32
-// consecutive origins of one column list and walk the same candidates, so every shared-memory
-// read is a broadcast and no per-origin work is replicated across lanes.  Per candidate and lane:
-// a 2-instruction lower bound Q of the SAD (see desc_q) against the lane's running threshold;
-// only candidates that could still win or tie pay the exact SAD (8 VABSDIFF4.U8.ACC) + packed
-// window test, and the key min(SAD<<19 | u_rel<<16 | col_idx) is exactly the reference's
-// "strict <, first candidate in (u_bin asc, col_idx asc) order wins".  The threshold is seeded
-// from the bins the origins themselves sit in (zero-flow prior).  Pruning is conservative, so the
-// result is identical to evaluating every SAD (PRUNE=false does that, for the tests).
-// The bound has two words (one per descriptor half, desc_q).  A warp whose origins found exact partners
-// (bit-identical patches: rendered or noise-free frames) filters with the first word only; a warp whose
-// seeds carry non-zero bounds (sensor noise) filters with both words -- twice the shared-memory reads, six
-// times fewer false hits -- and keeps its poorly seeded origins on the lane path.  Queued groups are
-// re-tested candidate by candidate with both words against the owner's CURRENT bound before an exact SAD
-// is spent.  Origins without a usable seed go to a warp-per-origin pass whose survivors are compacted
-// through the warp's queue so that exact SADs run 32 at a time (tools/noise_probe.py: 1.3-1.7x over the
-// one-word filter on noisy frames, -4 % on noise-free ones).
+// every bin list padded to a multiple of 4.  A LANE owns an origin: the 32 lanes of a warp walk the
+// same candidates, so every shared-memory read is a broadcast and no per-origin work is replicated.
+// The key min(SAD<<19 | u_rel<<16 | col_idx) is exactly the reference's "strict <, first candidate in
+// (u_bin asc, col_idx asc) order wins".
+//
+// Two passes per CTA (r2f):
+//   pass 1  every origin gets a bound -- the hint of the other direction (mono pairs, second launch) or the
+//           candidate with the smallest signature distance in its own bin (zero-flow prior), evaluated exactly --
+//           and is SORTED by what that bound is worth into three lists:
+//             Z  bound 0   (an exact partner: rendered or noise-free frames)   -> one-word filter
+//             N  0 < bound <= seed_good (a partner under sensor noise)         -> two-word filter
+//             P  no usable bound (unmatched feature, partner outside the own bin, exhaustive mode)
+//   pass 2  warps pull work items from a shared counter: Z/N tasks of 32 sorted origins run the lower-bound
+//           filter (desc_q: SAD >= Q, one VABSDIFF4 per signature word) over their window and collect one bit
+//           per CANDIDATE; each lane then evaluates its own few hits exactly, no queue, no shuffles.  P tasks
+//           are split by window row into items that evaluate EVERY candidate exactly (8 VABSDIFF4.U8.ACC +
+//           packed window test, ~13 instructions per lane and candidate): for an origin whose bound prunes
+//           little that is cheaper than filtering, and it bounds the cost of any input at about twice a clean
+//           frame's.  Pruning is conservative, so the result equals evaluating every SAD (PRUNE=false sends
+//           every origin down the P path, for the tests).
 // SAD is not a contraction: no tensor cores here by design.
 //
 // K3 (k3_flags, k3_emit): closed-cycle test, same-pixel dedupe (lowest class wins, via the twin
@@ -55,23 +58,19 @@ constexpr int kMaxCols = kOC + 5;  // staged target columns: [ub0-3, ub_last+3) 
 constexpr int kSegW = kMaxCols + 1;
 constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
 constexpr int kMaxWarps = 16;
-constexpr int kTwoWordVotes = 3;  // a warp filters with both signature words when more than 3/4 of its searching lanes hold a non-zero bound
-constexpr int kQueue = 128;     // deferred exact evaluations per warp: < 32 left over + up to kAppend per lane and pass
-#ifndef VO_K2_APPEND
-#define VO_K2_APPEND 3
+constexpr int kQueue = 128;     // pending hits per warp (M tasks): < 32 left over + what one 32-candidate word adds in one go
+constexpr int kListCap = 512;   // origins per column sorted in one go (a longer column list is processed in segments)
+constexpr int kMergeBelow = 12; // a Z or N list shorter than this joins the other list's tasks (either filter is exact for both)
+#ifndef VO_K2_ROW_CHUNK
+#define VO_K2_ROW_CHUNK 2
 #endif
-#ifndef VO_K2_FLOOD
-#define VO_K2_FLOOD 20
-#endif
-constexpr int kAppend = VO_K2_APPEND;  // queue entries a lane contributes per compaction pass (1..3: the count travels in two ballots)
-constexpr int kFlood = VO_K2_FLOOD;    // a lane with at least this many filter hits in a chunk of 32 groups is expanded by the whole warp
+constexpr int kRowChunk = VO_K2_ROW_CHUNK;  // window rows per work item of pass 2
 constexpr int kBig = 1 << 20;
-static_assert(kCandCap <= 2048, "k2 hard pass packs the staged position into 11 bits");
-static_assert(kAppend >= 1 && kAppend <= 3 && 31 + 32 * kAppend <= kQueue, "a compaction pass must fit the queue");
-constexpr int kHardCap = 1024;  // origins per chunk handed to the warp-per-origin pass
 constexpr uint32_t kSkip = 0xFFFFFFFEu;  // best[] between the chunks of a hinted search: nobody points at this origin (never a real key: SAD <= 8160)
-constexpr int kSeedGood = 128;  // an origin whose seed SAD is above this has no partner worth a lane-per-origin walk: warp-per-origin pass
-constexpr int kHitBudget = 4;   // default of vo_config.match_hit_budget: filter hits (groups of 4) a lane may queue before its origin is handed over
+#ifndef VO_K2_SEED_GOOD
+#define VO_K2_SEED_GOOD 96
+#endif
+constexpr int kSeedGood = VO_K2_SEED_GOOD;  // default of vo_config.match_seed_good: an origin whose bound is above this is matched exhaustively
 
 struct K2Tables {
   int32_t cntT[kMaxV][kSegW];         // target counts (row, staged column)
@@ -86,16 +85,21 @@ struct K2Tables {
 
 struct __align__(128) K2Smem {
   K2Tables t;
-  uint32_t sbest[kMaxWarps][32];      // running best key of the 32 origins of a warp's task
-  uint32_t queue[kMaxWarps][kQueue];  // deferred exact evaluations: owner lane << 16 | candidate group
-  int32_t hard_n;                     // origins handed to the warp-per-origin pass in this chunk
-  uint16_t hard[kHardCap];            // origin column (bit 15) | col_idx
+  int32_t n_z[kOC], n_n[kOC], n_p[kOC];  // entries of the three lists of this segment
+  int32_t next_item;                  // pass 2: next unclaimed work item
+  uint16_t glist[kOC][kListCap];      // well-bounded origins (index within the segment): Z from the front, N from the back
+  uint32_t gkey[kOC][kListCap];       // bound of every origin of the segment (key, staged-column form), by index
+  uint16_t plist[kOC][kListCap];      // M: origins with a poor bound or none (exhaustive mode: every origin)
+  uint8_t cls[kOC][kListCap];         // pass 1 -> ordered scan: 0 nothing to search, 1 Z, 2 N, 3 M
+  uint32_t sbest[kMaxWarps][32];      // M tasks: best key of the warp's 32 origins (results of the cooperative evaluations)
+  uint16_t queue[kMaxWarps][kQueue];  // M tasks: filter hits awaiting exact evaluation, owner lane << 11 | staged position
   __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
   uint4 hi[kCandCap];                 // descriptor bytes 16..31
   uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
-  __align__(16) uint32_t q[kCandCap];  // signature word 0: 4 coded group sums of bytes 0..15 (first-level filter); read four at a time
-  __align__(16) uint32_t q1[kCandCap]; // signature word 1: bytes 16..31 (second level: Q0 + Q1)
+  __align__(16) uint32_t q[kCandCap];  // signature word 0: 4 coded group sums of bytes 0..15; read four at a time
+  __align__(16) uint32_t q1[kCandCap]; // signature word 1: bytes 16..31
 };
+static_assert(kCandCap <= 2048, "queue entries pack the staged position into 11 bits");
 static_assert(sizeof(K2Smem) <= 113 * 1024, "two K2 CTAs per SM need <= 113 KB each (227 KB minus the per-CTA reserve)");
 
 // acc + sum of |a_i - b_i| over the four packed bytes: one VABSDIFF4.U8.ACC
@@ -106,17 +110,15 @@ __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) {
 }
 
 __device__ __forceinline__ uint32_t sad32(const uint4& a, const uint4& b, const uint4& x, const uint4& y) {
-  uint32_t s = sad4(a.x, x.x, 0u);
+  uint32_t s = sad4(a.x, x.x, 0u), r = sad4(b.x, y.x, 0u);  // two chains: the accumulating form serialises
   s = sad4(a.y, x.y, s);
+  r = sad4(b.y, y.y, r);
   s = sad4(a.z, x.z, s);
+  r = sad4(b.z, y.z, r);
   s = sad4(a.w, x.w, s);
-  s = sad4(b.x, y.x, s);
-  s = sad4(b.y, y.y, s);
-  s = sad4(b.z, y.z, s);
-  return sad4(b.w, y.w, s);
+  r = sad4(b.w, y.w, r);
+  return s + r;
 }
-
-__device__ __forceinline__ int sadq(uint32_t a, uint32_t x) { return (int)sad4(a, x, 0u); }
 
 // key of one staged candidate for an origin (a, b, window lo_p/hi_p), kNone if outside the window.
 // packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
@@ -141,13 +143,23 @@ __device__ __forceinline__ int origin_vb(const K2Tables& t, int cc, int col_idx,
 
 __device__ __forceinline__ int pad4(int n) { return (n + 3) & ~3; }
 
+// one origin in a lane's registers
+struct K2Origin {
+  uint4 a, b;            // descriptor
+  uint32_t qa, qb;       // signature words
+  uint32_t lo_p, hi_p;   // packed pixel window (src/myMatch.cpp:84-87,101)
+  int v;                 // own v-bin row
+  int vlo, vhi;          // candidate rows clipped to the staged chunk (vlo >= vhi: nothing to search here)
+  int lo_full, hi_full;  // candidate rows before clipping
+};
+
 // Matches the origins of columns [ub0, ub0+noc) x rows of group `grp`.  Returns false (having
 // written nothing) when a row of the shared (noc+5)-column window does not fit the staging buffer;
 // the caller then runs the columns one at a time (a 6-column row always fits).
 template <bool PRUNE, int THREADS>
 __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
                                            uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
-                                           int rows_per_group, int rad_v, int reach, int hit_budget, bool hinted,
+                                           int rows_per_group, int rad_v, int reach, int seed_good, bool hinted,
                                            uint32_t* __restrict__ clear_dir) {
   constexpr int NW = THREADS / 32;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -204,20 +216,21 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     }
   }
   const int r0 = grp * rows_per_group, r1 = min(r0 + rows_per_group, V);
-  int oB0 = 0, nT0 = 0, ntasks = 0, row_lo = V;
+  static_assert(kOC == 2, "the per-column scalars below are written out for two origin columns");
+  int row_lo = V;
+  const int oB0 = t.prefO[0][r0], oB1 = t.prefO[1][r0];
+  const int nO0 = t.prefO[0][r1] - oB0, nO1 = t.prefO[1][r1] - oB1;
+  const int n_max = max(nO0, nO1);
 #pragma unroll
   for (int cc = 0; cc < kOC; cc++) {
-    const int ob = t.prefO[cc][r0];
-    const int n = t.prefO[cc][r1] - ob;
-    if (cc == 0) { oB0 = ob; nT0 = (n + 31) >> 5; }
-    ntasks += (n + 31) >> 5;
-    if (n > 0) {  // rows any origin of this group can see: vb is non-decreasing along the column list
+    const int ob = cc ? oB1 : oB0;
+    if ((cc ? nO1 : nO0) > 0) {  // rows any origin of this group can see: vb is non-decreasing along the column list
       int v_first = r0;
       while (t.prefO[cc][v_first + 1] <= ob) v_first++;
       row_lo = min(row_lo, max(max(origin_vb(t, cc, ob, v_first) - 3, v_first - reach), 0));
     }
   }
-  if (ntasks == 0) return true;
+  if (n_max == 0) return true;
   // exclusive: src/myMatch.cpp:93,99.  `reach` (>= V on flow edges: no restriction) narrows the rows of a
   // left<->right edge to those that can hold a candidate inside its +-rad_v window: a bin row spans 45 block
   // rows, so |dv| <= rad_v <= 16 keeps the candidate's row within +-1 of the origin's own row
@@ -234,21 +247,16 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
   const uint2* q_to = fa.q + (int64_t)to_slot * fa.rec_stride;
   const uint4* Q4 = reinterpret_cast<const uint4*>(S.q);
   const uint4* Q14 = reinterpret_cast<const uint4*>(S.q1);
-  uint32_t* sbest = S.sbest[warp];
-  uint32_t* queue = S.queue[warp];
-  const uint32_t lt_mask = (1u << lane) - 1u, lane16 = (uint32_t)lane << 16;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int nseg = (n_max + kListCap - 1) / kListCap;
 
   bool first_chunk = true;
   for (int ra = row_lo;;) {
     // ---- chunk = as many whole rows as fit the staging buffer ------------------------------
     int rb = ra, staged = 0;
     while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
-    // hints (see k2_hint_scatter) are validated against the candidate's record in global memory, so they work whether or
-    // not the window is staged in one piece; an origin nobody points at is parked as kSkip until the last chunk
-    const bool use_hint = hinted;
     const bool last_chunk = rb >= row_hi;
     __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
-    if (tid == THREADS - 1) S.hard_n = 0;
     if (tid <= rb - ra) {
       const int v = ra + tid;
       int acc = 0;
@@ -287,429 +295,419 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         }
       }
     }
-    __syncthreads();
 
-    // ---- tasks: 32 consecutive origins of one column list, one per lane.  Every lane walks the
-    //      same candidates (shared-memory broadcast); its own search rows are [vlo, vhi). ----------
-    for (int task = warp; task < ntasks; task += NW) {
-      const int cc = (kOC > 1 && task >= nT0) ? 1 : 0;
-      const int tb = task - (cc ? nT0 : 0);
-      const int ub = ub0 + cc;
-      const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo, jown = ub - ulo;  // src/myMatch.cpp:90-91,97
-      const int o = (cc ? t.prefO[cc][r0] : oB0) + tb * 32 + lane;
-      const bool valid = o < t.prefO[cc][r1];
-      uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
-
-      int v = r0, vlo = kBig, vhi = 0;
+    // origin (column cc, col_idx o) into a lane's registers; its candidate rows clipped to this chunk
+    auto load_origin = [&](int cc, int o, bool valid, K2Origin& og) {
+      og.v = r0; og.vlo = kBig; og.vhi = 0; og.lo_full = 0; og.hi_full = 0;
+      og.a = make_uint4(0, 0, 0, 0); og.b = og.a; og.qa = 0; og.qb = 0;
       uint32_t oxy = 0;
-      uint4 a = make_uint4(0, 0, 0, 0), b = a;
-      uint32_t qa = 0, qb = 0;
-      uint32_t bestk = kNone;
-      uint32_t hint = kNone;
-      bool full = valid;  // this lane runs an unseeded search (seed pass below)
-      bool skip = false;  // hinted direction: no feature of the other frame points here, the cycle cannot close
-      int lo_full = 0, hi_full = 0;  // the origin's rows before clipping to the staged chunk
       if (valid) {
-        while (t.prefO[cc][v + 1] <= o) v++;
-        const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
-        oxy = __ldg(&xy_from[rec]);
-        a = __ldg(&desc_from[2 * rec]);
-        b = __ldg(&desc_from[2 * rec + 1]);
-        const uint2 qo = __ldg(&q_from[rec]);
-        qa = qo.x; qb = qo.y;
-        // lagging v_bin (src/myMatch.cpp:153-158): only the first origins after empty bins
-        const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
-        const int lo_r = max(max(max(vb - 3, 0), ra), v - reach);  // src/myMatch.cpp:92-93,99
-        const int hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
-        if (lo_r < hi_r) { vlo = lo_r; vhi = hi_r; }
-        lo_full = max(max(vb - 3, 0), v - reach);
-        hi_full = min(min(vb + 3, V - 1), v + reach + 1);
-        if (use_hint && first_chunk) {
-          hint = bo[o];
-          full = false;
-          skip = hint == kNone;
-        } else if (!first_chunk) {
-          bestk = bo[o];
-          skip = bestk == kSkip;
-          if (skip) bestk = kNone;
-          if (bestk != kNone) bestk += (uint32_t)j0 << 16;
-          if (use_hint) full = bestk == kNone;  // a validated hint (or better) is already the bound
-        }
-        if (skip) { vlo = kBig; vhi = 0; full = false; }
-      }
-      const int rlo = __reduce_min_sync(FULL, vlo), rhi = __reduce_max_sync(FULL, vhi);
-      const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
-      const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
-      const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
-
-      if (PRUNE && use_hint && first_chunk && valid && !skip) {
-        // the hinted candidate must be one this origin may legally take (bin ranges are not symmetric between the two
-        // directions): locate its record in global memory and evaluate it; anything unexpected -> plain search
-        const int jr = (int)((hint >> 16) & 7u), kb = (int)(hint & 0xFFFFu), j = j0 + jr;
-        uint32_t k = kNone;
-        if (jr < 6 && j < j1) {
-          for (int r = lo_full; r < hi_full; r++) {
-            if (kb >= t.colT[j][r] && kb < t.colT[j][r + 1]) {
-              const int64_t rec = (int64_t)((r * U + ulo + j) * 4 + c) * g.cap + (kb - t.colT[j][r]);
-              const uint32_t x = __ldg(&xy_to[rec]) + 0x80008000u;
-              const uint32_t sad = sad32(a, b, __ldg(&desc_to[2 * rec]), __ldg(&desc_to[2 * rec + 1]));
-              const uint32_t t1 = x - lo_p, t2 = x - hi_p;
-              if (((t1 & ~t2) & 0x80008000u) == 0x80008000u) k = sad * 0x80000u + (((uint32_t)j << 16) | (uint32_t)kb);
-              break;
-            }
-          }
-        }
-        if (k != kNone && k == hint + ((uint32_t)j0 << 16)) bestk = k;
-        else full = true;
-      }
-      if (PRUNE && __any_sync(FULL, full && vlo < vhi)) {
-        // seed: the candidate with the smallest lower bound among the bins the origins themselves
-        // sit in (zero-flow prior); any legal candidate gives a valid bound
-        const int smin = max(__reduce_min_sync(FULL, valid ? v : kBig), ra);
-        const int smax = min(__reduce_max_sync(FULL, valid ? v : -1), rb - 1);
-        uint32_t k1 = kNone;
-        int sa = jown, sb = jown + 1;  // seed bins of the own rows
-        if (reach >= kMaxV) {  // flow edge: the +-135-row window admits practically every candidate of the own bin
-          for (int r = smin; r <= smax; r++) {
-            const int p1 = t.segOff[r][jown + 1];
-            for (int p = t.segOff[r][jown]; p < p1; p += 4) {  // bin lists are padded to 4
-              const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
-              const uint32_t ka = sad4(qb, q1.x, sad4(qa, qq.x, 0u)) * 0x100000u + (uint32_t)p;
-              const uint32_t kb = sad4(qb, q1.y, sad4(qa, qq.y, 0u)) * 0x100000u + (uint32_t)(p + 1);
-              const uint32_t kc = sad4(qb, q1.z, sad4(qa, qq.z, 0u)) * 0x100000u + (uint32_t)(p + 2);
-              const uint32_t kd = sad4(qb, q1.w, sad4(qa, qq.w, 0u)) * 0x100000u + (uint32_t)(p + 3);
-              k1 = min(k1, min(min(ka, kb), min(kc, kd)));
-            }
-          }
-        } else {  // narrow (left<->right) edge: only candidates inside the +-rad_v rows can seed; a disparity may cross
-                  // into the neighbouring bins, so the own row's bins jown-1 .. jown+1 are searched
-          const int ja = max(jown - 1, j0), jb = min(jown + 2, j1);
-          sa = ja; sb = jb;
-          for (int r = smin; r <= smax; r++) {
-            const int p1 = t.segOff[r][jb];
-            for (int p = t.segOff[r][ja]; p < p1; p++) {
-              const uint32_t x = S.xr[p].x;
-              const uint32_t t1 = x - lo_p, t2 = x - hi_p;
-              const uint32_t kq = sad4(qb, S.q1[p], sad4(qa, S.q[p], 0u)) * 0x100000u + (uint32_t)p;
-              k1 = min(k1, (((t1 & ~t2) & 0x80008000u) == 0x80008000u) ? kq : kNone);
-            }
-          }
-        }
-        if (k1 != kNone && vlo < vhi && full) {
-          const int p = (int)(k1 & 0xFFFFFu);
-          if (p >= t.rowStart[vlo] && p < t.rowStart[vhi]) bestk = min(bestk, cand_key(S, p, a, b, lo_p, hi_p));
-        }
-#ifdef VO_K2_SEEDX
-        if (reach >= kMaxV) {  // second look at the own bins: every candidate the first seed's SAD cannot exclude, exactly
-          int tqs = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
-          const bool me = full && vlo < vhi;
-          const int pa = me ? t.rowStart[vlo] : 0, pb = me ? t.rowStart[vhi] : 0;
-          for (int r = smin; r <= smax; r++) {
-            const int p1 = t.segOff[r][jown + 1];
-            for (int p = t.segOff[r][jown]; p < p1; p++) {
-              const int q = (int)sad4(qb, S.q1[p], sad4(qa, S.q[p], 0u));
-              if (p >= pa && p < pb && q <= tqs) {
-                bestk = min(bestk, cand_key(S, p, a, b, lo_p, hi_p));
-                tqs = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
-              }
-            }
-          }
-        }
-#endif
-      }
-      sbest[lane] = bestk;
-      __syncwarp();
-      // tq: a candidate can still win (or tie) only if its lower bound Q <= best SAD so far
-      int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
-      int qn = 0;  // queued groups (warp-uniform)
-      int hits = 0;
-      bool handed = false;
-      // An origin the filter cannot prune (no near-exact match: every candidate may still win) would
-      // flood the queue; it leaves the lane-per-origin walk and is matched by a whole warp after the
-      // tasks of this chunk.  It takes the best key found so far along (through best[]) as its starting bound.
-      auto hand_over = [&]() {
-        const int hs = atomicAdd(&S.hard_n, 1);
-        hits = -kBig;  // once per task (if the list is full the origin stays on the queue path)
-        if (hs < kHardCap) {
-          S.hard[hs] = (uint16_t)((cc << 15) | o);
-          bo[o] = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
-          vlo = kBig; vhi = 0;
-          handed = true;
-          return true;
-        }
-        return false;
-      };
-      K2STAT(0, valid ? 1 : 0);
-      K2STAT(2, (valid && vlo < vhi && bestk == kNone) ? 1 : 0);
-      K2STAT(3, (valid && vlo < vhi && bestk != kNone && (bestk >> 19) == 0) ? 1 : 0);
-      // Filter width, chosen per warp: on clean frames most origins find an exact partner (bound 0) and the first
-      // signature word alone prunes everything; once sensor noise leaves the seeds with non-zero bounds the filter
-      // tests both words (twice the shared-memory reads, ~6x fewer false hits) and can afford to keep poorly seeded
-      // origins on the lane path.
-      const uint32_t searching = __ballot_sync(FULL, vlo < vhi);
-      const bool two = PRUNE && __popc(__ballot_sync(FULL, vlo < vhi && tq > 0)) * 4 > __popc(searching) * kTwoWordVotes;
-      K2STAT(1, (valid && two) ? 1 : 0);
-      if (PRUNE && vlo < vhi && (two ? bestk == kNone : tq > kSeedGood)) hand_over();  // no seed or a poor one: nearly every group would hit
-
-      // exact SAD + window test of up to 32 queued (origin, group of 4 candidates) entries, one per
-      // lane; the origin's record comes from its owner lane by shuffle, the result goes back
-      // through a shared-memory atomicMin.  Every lane then refreshes its bound.
-      auto flush = [&]() {
-        const int n = min(qn, 32);
-        qn -= n;
-        const bool on = lane < n;
-        K2CHECK(qn >= 0 && qn + n <= kQueue);
-        const uint32_t e = on ? queue[qn + lane] : 0u;
-        const int owner = (int)(e >> 16), p = (int)(e & 0xFFFFu) << 2;
-        K2CHECK(!on || (owner < 32 && p + 3 < kCandCap));
-        uint4 oa, ob;
-        oa.x = __shfl_sync(FULL, a.x, owner); oa.y = __shfl_sync(FULL, a.y, owner);
-        oa.z = __shfl_sync(FULL, a.z, owner); oa.w = __shfl_sync(FULL, a.w, owner);
-        ob.x = __shfl_sync(FULL, b.x, owner); ob.y = __shfl_sync(FULL, b.y, owner);
-        ob.z = __shfl_sync(FULL, b.z, owner); ob.w = __shfl_sync(FULL, b.w, owner);
-        const uint32_t olo = __shfl_sync(FULL, lo_p, owner), ohi = __shfl_sync(FULL, hi_p, owner);
-        const uint32_t oq = __shfl_sync(FULL, qa, owner), oq1 = __shfl_sync(FULL, qb, owner);
-        const int otq = __shfl_sync(FULL, tq, owner);  // the owner's bound NOW (it may have dropped since the group was queued)
-        if (on) {
-          // a group was queued because ONE of its four candidates may win: re-test each against the bound first
-          const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
-          uint32_t k = kNone;
-          if ((int)sad4(oq1, q1.x, sad4(oq, qq.x, 0u)) <= otq) k = cand_key(S, p, oa, ob, olo, ohi);
-          if ((int)sad4(oq1, q1.y, sad4(oq, qq.y, 0u)) <= otq) k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
-          if ((int)sad4(oq1, q1.z, sad4(oq, qq.z, 0u)) <= otq) k = min(k, cand_key(S, p + 2, oa, ob, olo, ohi));
-          if ((int)sad4(oq1, q1.w, sad4(oq, qq.w, 0u)) <= otq) k = min(k, cand_key(S, p + 3, oa, ob, olo, ohi));
-          if (k != kNone) atomicMin(&sbest[owner], k);
-        }
-        __syncwarp();
-        bestk = sbest[lane];
-        tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
-      };
-
-      // The set bits of lane L's hit mask, evaluated by the whole warp at once: lane j takes the group of bit 31 - j
-      // (group g0 + j), re-tests its four candidates against L's bound and evaluates the survivors exactly.
-      auto expand = [&](int L, uint32_t mine, int g0) {
-        const uint32_t mL = __shfl_sync(FULL, mine, L);
-        uint4 oa, ob;
-        oa.x = __shfl_sync(FULL, a.x, L); oa.y = __shfl_sync(FULL, a.y, L);
-        oa.z = __shfl_sync(FULL, a.z, L); oa.w = __shfl_sync(FULL, a.w, L);
-        ob.x = __shfl_sync(FULL, b.x, L); ob.y = __shfl_sync(FULL, b.y, L);
-        ob.z = __shfl_sync(FULL, b.z, L); ob.w = __shfl_sync(FULL, b.w, L);
-        const uint32_t olo = __shfl_sync(FULL, lo_p, L), ohi = __shfl_sync(FULL, hi_p, L);
-        const uint32_t oq = __shfl_sync(FULL, qa, L), oq1 = __shfl_sync(FULL, qb, L);
-        const int otq = __shfl_sync(FULL, tq, L);
-        uint32_t k = kNone;
-        if ((mL << lane) & 0x80000000u) {
-          const int p = (g0 + lane) << 2;
-          K2CHECK(p >= 0 && p + 3 < kCandCap);
-          const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
-          if ((int)sad4(oq1, q1.x, sad4(oq, qq.x, 0u)) <= otq) k = cand_key(S, p, oa, ob, olo, ohi);
-          if ((int)sad4(oq1, q1.y, sad4(oq, qq.y, 0u)) <= otq) k = min(k, cand_key(S, p + 1, oa, ob, olo, ohi));
-          if ((int)sad4(oq1, q1.z, sad4(oq, qq.z, 0u)) <= otq) k = min(k, cand_key(S, p + 2, oa, ob, olo, ohi));
-          if ((int)sad4(oq1, q1.w, sad4(oq, qq.w, 0u)) <= otq) k = min(k, cand_key(S, p + 3, oa, ob, olo, ohi));
-        }
-        k = __reduce_min_sync(FULL, k);
-        if (lane == L && k < bestk) {  // (queued entries of L still pending add to sbest[L] by atomicMin)
-          atomicMin(&sbest[lane], k);
-          bestk = min(bestk, k);
-          tq = (int)(bestk >> 19);
-        }
-        __syncwarp();
-      };
-
-      // rows in the order own row, then the rest: the partner of a small flow sits in the own row, so bounds tighten first
-      const int rown = min(max(__shfl_sync(FULL, v, 0), rlo), rhi - 1);
-      for (int ri = rlo - 1; ri < rhi; ri++) {
-        if (ri == rown) continue;
-        const int r = (ri < rlo) ? rown : ri;
-        bool act = (r >= vlo) && (r < vhi);
-        int tqe = act ? tq : -1;  // tq while this lane searches the current row, else -1 (never passes)
-        int pg = t.segOff[r][j0] >> 2;            // candidate groups of 4 (every bin list is padded to 4)
-        const int pg1 = t.segOff[r][j1] >> 2;
-        // Chunks of up to 32 groups: every lane first collects a private bit mask of the groups that may
-        // still hold a winner (no votes, no branches in the filter loop), then the warp compacts the set
-        // bits into the exact-evaluation queue, one entry per lane and round.
-        while (pg < pg1) {
-          const int nb = min(32, pg1 - pg);
-          K2CHECK(pg >= 0 && (pg + nb) * 4 <= kCandCap);
-          uint32_t m = 0;  // MISS bits while filtering, newest group in bit 0
-          // bias + Q has its sign bit set exactly when Q exceeds the lane's bound (tqe = -1: always; no bound yet: never), so a
-          // group of four candidates misses iff the AND of its four sums is negative: 2 LOP3 + 1 SHF per group on top of
-          // the VABSDIFF4s, no minimum and no subtraction
-          const uint32_t bias = 0x7FFFFFFFu - (uint32_t)tqe;
-          if (PRUNE && two) {
-            const uint4* qp = Q4 + pg;
-            const uint4* rp = Q14 + pg;
-            auto gmiss = [&](const uint4& x, const uint4& y) {
-              return (sad4(qb, y.x, sad4(qa, x.x, bias)) & sad4(qb, y.y, sad4(qa, x.y, bias))) &
-                     (sad4(qb, y.z, sad4(qa, x.z, bias)) & sad4(qb, y.w, sad4(qa, x.w, bias)));
-            };
-            int i = 0;
-#pragma unroll 1
-            for (; i + 3 < nb; i += 4) {
-              const uint32_t ma = gmiss(qp[i], rp[i]), mb = gmiss(qp[i + 1], rp[i + 1]);
-              const uint32_t mc = gmiss(qp[i + 2], rp[i + 2]), md = gmiss(qp[i + 3], rp[i + 3]);
-              m = __funnelshift_l(ma, m, 1);
-              m = __funnelshift_l(mb, m, 1);
-              m = __funnelshift_l(mc, m, 1);
-              m = __funnelshift_l(md, m, 1);
-            }
-#pragma unroll 1
-            for (; i < nb; i++) m = __funnelshift_l(gmiss(qp[i], rp[i]), m, 1);
-            m = ~m;
-          } else if (PRUNE) {
-            const uint4* qp = Q4 + pg;  // one uint4 = the signatures of one group of 4 candidates
-            auto gmiss1 = [&](const uint4& x) {
-              return (sad4(qa, x.x, bias) & sad4(qa, x.y, bias)) & (sad4(qa, x.z, bias) & sad4(qa, x.w, bias));
-            };
-            int i = 0;
-#pragma unroll 1
-            for (; i + 3 < nb; i += 4) {
-              const uint32_t ma = gmiss1(qp[i]), mb = gmiss1(qp[i + 1]), mc = gmiss1(qp[i + 2]), md = gmiss1(qp[i + 3]);
-              m = __funnelshift_l(ma, m, 1);  // shifts in the sign: 1 = lower bound above the threshold
-              m = __funnelshift_l(mb, m, 1);
-              m = __funnelshift_l(mc, m, 1);
-              m = __funnelshift_l(md, m, 1);
-            }
-#pragma unroll 1
-            for (; i < nb; i++) m = __funnelshift_l(gmiss1(qp[i]), m, 1);
-            m = ~m;
-          } else {
-            m = act ? kNone : 0u;
-          }
-          m &= kNone >> (32 - nb);  // bit b <-> group pg + nb-1-b
-          if (PRUNE) {
-            hits += __popc(m);
-            K2STAT(4, __popc(m));
-            if (!two && hits > hit_budget && hand_over()) { m = 0u; act = false; tqe = -1; K2STAT(5, 1); }
-          }
-          const uint32_t gfirst = lane16 + (uint32_t)(pg + nb - 32);  // owner lane << 16 + group of bit 31 (mod 2^32)
-          uint32_t anyb = __ballot_sync(FULL, m != 0u);
-          if (anyb != 0u) {
-            // (1) a lane the bound hardly prunes (no partner in sight yet, or none at all) would feed the queue for many
-            //     rounds while 31 lanes wait: the whole warp takes its mask instead, lane j its group j
-            int left = __popc(m);
-            uint32_t flood = __ballot_sync(FULL, left >= kFlood);
-            while (flood != 0u) {
-              const int L = __ffs((int)flood) - 1;
-              flood &= flood - 1u;
-              expand(L, m, pg + nb - 32);
-              if (lane == L) { m = 0u; left = 0; }
-            }
-            // (2) the other lanes append up to kAppend groups per pass at positions given by two ballots (the count is a
-            //     2-bit number), then the queue is drained 32 entries at a time
-            anyb = __ballot_sync(FULL, m != 0u);
-            while (anyb != 0u) {
-              const int cn = min(left, kAppend);
-              const uint32_t b0 = __ballot_sync(FULL, cn & 1), b1 = __ballot_sync(FULL, cn & 2);
-              const int pos = qn + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask);
-#pragma unroll
-              for (int k = 0; k < kAppend; k++) {
-                if (k < cn) {
-                  const int z = __clz((int)m);
-                  K2CHECK(pos + k >= 0 && pos + k < kQueue && m != 0u);
-                  queue[pos + k] = gfirst + (uint32_t)z;
-                  m &= ~(0x80000000u >> z);
-                }
-              }
-              left -= cn;
-              qn += __popc(b0) + 2 * __popc(b1);
-              __syncwarp();
-              while (qn >= 32) flush();
-              anyb = __ballot_sync(FULL, m != 0u);
-            }
-            tqe = act ? tq : -1;
-          }
-          pg += nb;
-        }
-      }
-      __syncwarp();
-      while (qn > 0) flush();
-      if (valid && !handed) bo[o] = (skip && !last_chunk) ? kSkip : (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
-      __syncwarp();  // sbest/queue are reused by this warp's next task
-    }
-    if (PRUNE) {
-      // ---- handed-over origins: one warp per origin, lanes stride its candidates ----------------------
-      __syncthreads();
-      const int nh = min(S.hard_n, kHardCap);
-      for (int h = warp; h < nh; h += NW) {
-        const uint32_t e = S.hard[h];
-        const int cc = (int)(e >> 15), o = (int)(e & 0x7FFFu);
-        const int ub = ub0 + cc;
-        const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo;
-        uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
         int v = r0;
         while (t.prefO[cc][v + 1] <= o) v++;
-        const int64_t rec = (int64_t)((v * U + ub) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
-        const uint32_t oxy = __ldg(&xy_from[rec]);
-        const uint4 a = __ldg(&desc_from[2 * rec]), b = __ldg(&desc_from[2 * rec + 1]);
+        const int64_t rec = (int64_t)((v * U + ub0 + cc) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
+        oxy = __ldg(&xy_from[rec]);
+        og.a = __ldg(&desc_from[2 * rec]);
+        og.b = __ldg(&desc_from[2 * rec + 1]);
         const uint2 qo = __ldg(&q_from[rec]);
-        const uint32_t qa = qo.x, qb = qo.y;
+        og.qa = qo.x; og.qb = qo.y;
+        // lagging v_bin (src/myMatch.cpp:153-158): only the first origins after empty bins
         const int vb = (o >= t.lagEnd[cc][v]) ? v + 1 : origin_vb(t, cc, o, v);
-        const int lo_r = max(max(max(vb - 3, 0), ra), v - reach), hi_r = min(min(min(vb + 3, V - 1), rb), v + reach + 1);
-        const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
-        const uint32_t lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);
-        const uint32_t hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
-        uint32_t bk = kNone;
-        {  // the best key the lane-per-origin walk (and the earlier chunks) left in best[]
-          const uint32_t prev = bo[o];
-          if (prev != kNone) bk = prev + ((uint32_t)j0 << 16);
-        }
-        int tl = (int)(bk >> 19);  // kNone >> 19 = 8191 > any SAD
-        if (lane == 0) K2STAT(6, 1);
-        // One pass, the origin's own row first (zero-flow prior).  Lanes test the two-word lower bound of 32 candidates at
-        // a time against the best SAD known to the warp and COMPACT the survivors into the warp's queue; exact SADs are
-        // then taken 32 at a time with every lane busy (evaluating in place would run the exact path whenever ANY lane
-        // survives: with a few per cent survivors that is nearly every iteration).
-        int hn = 0;
-        auto drain = [&](int n) {  // exact evaluation of the last n (<= 32) queued candidates
-          hn -= n;
-          if (lane < n) {
-            const uint32_t e2 = queue[hn + lane];
-            K2STAT(7, 1);
-            if ((int)(e2 >> 11) <= tl) bk = min(bk, cand_key(S, (int)(e2 & 0x7FFu), a, b, lo_p, hi_p));  // bound re-tested: tl may have dropped
+        og.lo_full = max(max(vb - 3, 0), v - reach);  // src/myMatch.cpp:92-93,99
+        og.hi_full = min(min(vb + 3, V - 1), v + reach + 1);
+        const int lo_r = max(og.lo_full, ra), hi_r = min(og.hi_full, rb);
+        if (lo_r < hi_r) { og.vlo = lo_r; og.vhi = hi_r; }
+        og.v = v;
+      }
+      const int ou = (int)(oxy & 0xFFFFu), ov = (int)(oxy >> 16);
+      og.lo_p = (uint32_t)max(ou - g.rad_u, 0) | ((uint32_t)max(ov - rad_v, 0) << 16);  // src/myMatch.cpp:84-87,101
+      og.hi_p = (uint32_t)(ou + g.rad_u + 1) | ((uint32_t)(ov + rad_v + 1) << 16);
+    };
+
+    for (int seg = 0; seg < nseg; seg++) {
+      __syncthreads();  // staging complete / previous segment's lists consumed
+      if (tid == 32) S.next_item = 0;
+      __syncthreads();
+
+      // ================= pass 1: a bound for every origin, origins sorted by what it is worth =================
+      // this segment's origins of column cc: [sO, sO + sN)
+      const int sO0 = oB0 + seg * kListCap, sO1 = oB1 + seg * kListCap;
+      const int sN0 = max(min(nO0 - seg * kListCap, kListCap), 0), sN1 = max(min(nO1 - seg * kListCap, kListCap), 0);
+      const int nT10 = (sN0 + 31) >> 5, nT11 = (sN1 + 31) >> 5;
+      for (int task = warp; task < nT10 + nT11; task += NW) {
+        const int cc = (task >= nT10) ? 1 : 0;
+        const int tb = task - (cc ? nT10 : 0);
+        const int ub = ub0 + cc;
+        const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo, jown = ub - ulo;  // src/myMatch.cpp:90-91,97
+        const int o = (cc ? sO1 : sO0) + tb * 32 + lane;
+        const bool valid = tb * 32 + lane < (cc ? sN1 : sN0);
+        uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
+        K2Origin og;
+        load_origin(cc, o, valid, og);
+        uint32_t bestk = kNone, hint = kNone;
+        bool need_seed = valid;  // no bound yet
+        bool skip = false;       // hinted direction: no feature of the other frame points here, the cycle cannot close
+        if (valid) {
+          if (hinted && first_chunk) {
+            hint = bo[o];
+            need_seed = false;
+            skip = hint == kNone;
+          } else if (!first_chunk) {
+            bestk = bo[o];
+            skip = bestk == kSkip;
+            if (skip) bestk = kNone;
+            if (bestk != kNone) bestk += (uint32_t)j0 << 16;
+            need_seed = bestk == kNone && !skip;
           }
-          tl = min(tl, (int)(__reduce_min_sync(FULL, bk) >> 19));
-          __syncwarp();
-        };
-        const bool own = (v >= lo_r) && (v < hi_r);
-        const bool dense = tl > kSeedGood;  // no partner in sight: the bound prunes little, most lanes would evaluate anyway
-        for (int rr = own ? lo_r - 1 : lo_r; rr < hi_r; rr++) {
-          const int r = (rr < lo_r) ? v : rr;
-          if (own && rr == v) continue;
-          const int p1 = t.segOff[r][j1];
-          if (dense) {
-            // evaluate in place; the bound is lane-private inside a row and shared warp-wide after it
-#pragma unroll 2
-            for (int p = t.segOff[r][j0] + lane; p < p1; p += 32) {
-              if ((int)sad4(qb, S.q1[p], sad4(qa, S.q[p], 0u)) <= tl) {
-                bk = min(bk, cand_key(S, p, a, b, lo_p, hi_p));
-                tl = min(tl, (int)(bk >> 19));
+          if (skip) { og.vlo = kBig; og.vhi = 0; }
+        }
+        if (PRUNE && hinted && first_chunk && valid && !skip) {
+          // the hinted candidate must be one this origin may legally take (bin ranges are not symmetric between the two
+          // directions): locate its record in global memory and evaluate it; anything unexpected -> plain search
+          const int jr = (int)((hint >> 16) & 7u), kb = (int)(hint & 0xFFFFu), j = j0 + jr;
+          uint32_t k = kNone;
+          if (jr < 6 && j < j1) {
+            for (int r = og.lo_full; r < og.hi_full; r++) {
+              if (kb >= t.colT[j][r] && kb < t.colT[j][r + 1]) {
+                const int64_t rec = (int64_t)((r * U + ulo + j) * 4 + c) * g.cap + (kb - t.colT[j][r]);
+                const uint32_t x = __ldg(&xy_to[rec]) + 0x80008000u;
+                const uint32_t sad = sad32(og.a, og.b, __ldg(&desc_to[2 * rec]), __ldg(&desc_to[2 * rec + 1]));
+                const uint32_t t1 = x - og.lo_p, t2 = x - og.hi_p;
+                if (((t1 & ~t2) & 0x80008000u) == 0x80008000u) k = sad * 0x80000u + (((uint32_t)j << 16) | (uint32_t)kb);
+                break;
               }
             }
-            tl = __reduce_min_sync(FULL, tl);
-            continue;
           }
-          // 64 candidates per iteration, two per lane; loads are unconditional (positions past p1 are clamped into the
-          // staging arrays and masked out of the ballots)
-          for (int pb = t.segOff[r][j0]; pb < p1; pb += 64) {
-            const int pA = pb + lane, pB = pA + 32;
-            const int cA = min(pA, kCandCap - 1), cB = min(pB, kCandCap - 1);
-            const int qA = (int)sad4(qb, S.q1[cA], sad4(qa, S.q[cA], 0u));
-            const int qB = (int)sad4(qb, S.q1[cB], sad4(qa, S.q[cB], 0u));
-            const bool hA = (pA < p1) && (qA <= tl), hB = (pB < p1) && (qB <= tl);
-            const uint32_t balA = __ballot_sync(FULL, hA), balB = __ballot_sync(FULL, hB);
-            const int nA = __popc(balA);
-            K2CHECK(hn >= 0 && hn + nA + __popc(balB) <= kQueue && p1 <= kCandCap);
-            if (hA) queue[hn + __popc(balA & lt_mask)] = ((uint32_t)qA << 11) | (uint32_t)pA;
-            if (hB) queue[hn + nA + __popc(balB & lt_mask)] = ((uint32_t)qB << 11) | (uint32_t)pB;
-            hn += nA + __popc(balB);
-            while (hn >= 32) { __syncwarp(); drain(32); }
+          if (k != kNone && k == hint + ((uint32_t)j0 << 16)) bestk = k;
+          else need_seed = true;
+        }
+        const bool rows_here = og.vlo < og.vhi;
+        if (PRUNE && __any_sync(FULL, need_seed && rows_here)) {
+          // seed: the candidate with the smallest lower bound among the bins the origins themselves
+          // sit in (zero-flow prior); any legal candidate gives a valid bound
+          const int smin = max(__reduce_min_sync(FULL, valid ? og.v : kBig), ra);
+          const int smax = min(__reduce_max_sync(FULL, valid ? og.v : -1), rb - 1);
+          uint32_t k1 = kNone;
+          if (reach >= kMaxV) {  // flow edge: the +-135-row window admits practically every candidate of the own bin
+            for (int r = smin; r <= smax; r++) {
+              const int p1 = t.segOff[r][jown + 1];
+              for (int p = t.segOff[r][jown]; p < p1; p += 4) {  // bin lists are padded to 4
+                const uint4 qq = Q4[p >> 2], q1 = Q14[p >> 2];
+                const uint32_t ka = sad4(og.qb, q1.x, sad4(og.qa, qq.x, 0u)) * 0x100000u + (uint32_t)p;
+                const uint32_t kb = sad4(og.qb, q1.y, sad4(og.qa, qq.y, 0u)) * 0x100000u + (uint32_t)(p + 1);
+                const uint32_t kc = sad4(og.qb, q1.z, sad4(og.qa, qq.z, 0u)) * 0x100000u + (uint32_t)(p + 2);
+                const uint32_t kd = sad4(og.qb, q1.w, sad4(og.qa, qq.w, 0u)) * 0x100000u + (uint32_t)(p + 3);
+                k1 = min(k1, min(min(ka, kb), min(kc, kd)));
+              }
+            }
+          } else {  // narrow (left<->right) edge: only candidates inside the +-rad_v rows can seed; a disparity may cross
+                    // into the neighbouring bins, so the own row's bins jown-1 .. jown+1 are searched
+            const int ja = max(jown - 1, j0), jb = min(jown + 2, j1);
+            for (int r = smin; r <= smax; r++) {
+              const int p1 = t.segOff[r][jb];
+              for (int p = t.segOff[r][ja]; p < p1; p++) {
+                const uint32_t x = S.xr[p].x;
+                const uint32_t t1 = x - og.lo_p, t2 = x - og.hi_p;
+                const uint32_t kq = sad4(og.qb, S.q1[p], sad4(og.qa, S.q[p], 0u)) * 0x100000u + (uint32_t)p;
+                k1 = min(k1, (((t1 & ~t2) & 0x80008000u) == 0x80008000u) ? kq : kNone);
+              }
+            }
+          }
+          if (k1 != kNone && rows_here && need_seed) {
+            const int p = (int)(k1 & 0xFFFFFu);
+            if (p >= t.rowStart[og.vlo] && p < t.rowStart[og.vhi]) bestk = min(bestk, cand_key(S, p, og.a, og.b, og.lo_p, og.hi_p));
           }
         }
-        __syncwarp();
-        if (hn > 0) drain(hn);
-        bk = __reduce_min_sync(FULL, bk);
-        if (lane == 0) bo[o] = (bk == kNone) ? kNone : bk - ((uint32_t)j0 << 16);
+        // ---- class: Z (bound 0), N (bound <= seed_good), M (everything else that has rows to search) ----
+        const int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
+        const bool searching = valid && rows_here;
+        const bool poor = searching && (!PRUNE || tq > seed_good);
+        const uint32_t ext = (bestk == kNone) ? kNone : bestk - ((uint32_t)j0 << 16);
+        K2STAT(0, valid ? 1 : 0); K2STAT(1, (searching && !poor && tq == 0) ? 1 : 0); K2STAT(2, (searching && !poor && tq) ? 1 : 0);
+        K2STAT(3, poor ? 1 : 0);
+        if (valid) {
+          const int i = tb * 32 + lane;
+          S.cls[cc][i] = !searching ? 0 : poor ? 3 : (tq == 0 ? 1 : 2);
+          S.gkey[cc][i] = bestk;
+          if (poor) bo[o] = ext;  // exhaustive mode merges into it with atomicMin
+          else if (!searching) bo[o] = (skip && !last_chunk) ? kSkip : ext;  // nothing to search in this chunk
+        }
+      }
+      __syncthreads();
+      // ordered lists (a task of pass 2 takes 32 CONSECUTIVE origins of one class, so its lanes share most of their rows):
+      // one warp per column scans the class codes in origin order
+      if (warp < kOC) {
+        const int cc = warp, n = cc ? sN1 : sN0;
+        int tz = 0, tn = 0, tm = 0;
+        for (int i0 = 0; i0 < n; i0 += 128) {  // four chunks of 32 per trip: the loads and votes of a trip are independent
+          int k[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int i = i0 + u * 32 + lane;
+            k[u] = (i < n) ? (int)S.cls[cc][i] : 0;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int i = i0 + u * 32 + lane;
+            const uint32_t bz = __ballot_sync(FULL, k[u] == 1), bn = __ballot_sync(FULL, k[u] == 2), bm = __ballot_sync(FULL, k[u] == 3);
+            if (k[u] == 1) S.glist[cc][tz + __popc(bz & lt_mask)] = (uint16_t)i;
+            if (k[u] == 2) S.glist[cc][kListCap - 1 - (tn + __popc(bn & lt_mask))] = (uint16_t)i;
+            if (k[u] == 3) S.plist[cc][tm + __popc(bm & lt_mask)] = (uint16_t)i;
+            tz += __popc(bz); tn += __popc(bn); tm += __popc(bm);
+          }
+        }
+        if (lane == 0) { S.n_z[cc] = tz; S.n_n[cc] = tn; S.n_p[cc] = tm; }
+      }
+      __syncthreads();
+
+      // ================= pass 2: work items from a shared counter, long ones first =================
+      // filter tasks (32 sorted origins, whole window) of kind M (poor or no bound), N, Z per column; without pruning the M
+      // lists become P tasks split by window row instead
+      // few exact-partner origins ride the two-word tasks (zAsN), few noisy ones the one-word tasks (nAsZ): either filter is exact
+      const int nz0 = S.n_z[0], nn0 = S.n_n[0], nz1 = S.n_z[1], nn1 = S.n_n[1], np0 = S.n_p[0], np1 = S.n_p[1];
+      const bool zAsN0 = nz0 > 0 && nn0 > 0 && nz0 < kMergeBelow, nAsZ0 = !zAsN0 && nz0 > 0 && nn0 > 0 && nn0 < kMergeBelow;
+      const bool zAsN1 = nz1 > 0 && nn1 > 0 && nz1 < kMergeBelow, nAsZ1 = !zAsN1 && nz1 > 0 && nn1 > 0 && nn1 < kMergeBelow;
+      const int nTN0 = nAsZ0 ? 0 : (nn0 + (zAsN0 ? nz0 : 0) + 31) >> 5, nTZ0 = zAsN0 ? 0 : (nz0 + (nAsZ0 ? nn0 : 0) + 31) >> 5;
+      const int nTN1 = nAsZ1 ? 0 : (nn1 + (zAsN1 ? nz1 : 0) + 31) >> 5, nTZ1 = zAsN1 ? 0 : (nz1 + (nAsZ1 ? nn1 : 0) + 31) >> 5;
+      const int nTM0 = PRUNE ? (np0 + 31) >> 5 : 0, nTM1 = PRUNE ? (np1 + 31) >> 5 : 0;
+      const int nrows = rb - ra;
+      const int iM = nTM0 + nTM1;
+      const int i1 = iM + nTN0, i2 = i1 + nTN1, i3 = i2 + nTZ0, i4 = i3 + nTZ1;
+      // A filter task is cut into work items of kRowChunk window rows so that the warps of the CTA stay evenly loaded; the
+      // items of a task share their origins' bounds through gkey[].  Items 0..i4-1 are every task's chunk around its own
+      // row (where a small flow puts the partner: bounds tighten first), the remaining chunks follow.
+      const int nchunks = (nrows + kRowChunk - 1) / kRowChunk;
+      const int nFilterItems = i4 * nchunks;
+      const int i5 = nFilterItems + (PRUNE ? 0 : ((np0 + 31) >> 5) * nrows), n_items = i5 + (PRUNE ? 0 : ((np1 + 31) >> 5) * nrows);
+      for (;;) {
+        int item_raw = 0;
+        if (lane == 0) item_raw = atomicAdd(&S.next_item, 1);
+        item_raw = __shfl_sync(FULL, item_raw, 0);
+        if (item_raw >= n_items) break;
+        if (item_raw < nFilterItems) {
+          const bool own_chunk = item_raw < i4;
+          const int item = own_chunk ? item_raw : (item_raw - i4) / (nchunks - 1);
+          const int other = own_chunk ? 0 : (item_raw - i4) - item * (nchunks - 1);
+          // ---------- filter task: lower-bound filter, one bit per candidate, every lane evaluates its own hits ----------
+          const bool kindM = item < iM;
+          const int cc = kindM ? (item < nTM0 ? 0 : 1) : (item < i1) ? 0 : (item < i2) ? 1 : (item < i3) ? 0 : 1;
+          const bool two = item < i2;  // M and N kinds: both signature words
+          const int tb = item - (kindM ? (cc ? nTM0 : 0) : (item < i1) ? iM : (item < i2) ? i1 : (item < i3) ? i2 : i3);
+          const int ub = ub0 + cc;
+          const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo;
+          // logical list of this kind: its own entries first, then the merged-in entries of the other kind
+          const int nz = cc ? nz1 : nz0, nn = cc ? nn1 : nn0;
+          const bool merged = two ? (cc ? zAsN1 : zAsN0) : (cc ? nAsZ1 : nAsZ0);
+          const int n_own = kindM ? (cc ? np1 : np0) : two ? nn : nz;
+          const int n_all = n_own + ((!kindM && merged) ? (two ? nz : nn) : 0);
+          const int idx = tb * 32 + lane;
+          const bool valid = idx < n_all;
+          int slot = 0;
+          if (valid && !kindM) {
+            const bool n_entry = two ? (idx < n_own) : (idx >= n_own);
+            const int k = (idx < n_own) ? idx : idx - n_own;
+            slot = n_entry ? kListCap - 1 - k : k;
+          } else if (valid) {
+            slot = idx;
+          }
+          K2CHECK(slot >= 0 && slot < kListCap);
+          const int ei = valid ? (int)(kindM ? S.plist[cc][slot] : S.glist[cc][slot]) : 0;
+          const int o = (cc ? sO1 : sO0) + ei;
+          uint32_t bestk = valid ? S.gkey[cc][ei] : kNone;
+          K2Origin og;
+          load_origin(cc, o, valid, og);
+          const uint4 a = og.a, b = og.b;
+          const uint32_t qa = og.qa, qb = og.qb, lo_p = og.lo_p, hi_p = og.hi_p;
+          const int vlo = og.vlo, vhi = og.vhi;
+          const int rlo = __reduce_min_sync(FULL, vlo), rhi = __reduce_max_sync(FULL, vhi);
+          int tq = (bestk == kNone) ? 0x7FFFFFFF : (int)(bestk >> 19);
+          // M tasks evaluate their hits COOPERATIVELY: a lane of such a task still has ~1 hit per 32 candidates, but the
+          // lanes' counts differ widely, so private loops would run as long as the unluckiest lane's.  Hits go to a per-warp
+          // queue at positions from a warp scan; 32 queued (origin, candidate) pairs are then evaluated at once, one per
+          // lane, the origin's record coming from its owner lane by shuffle and the result going back through shared memory.
+          uint32_t* sbest = S.sbest[warp];
+          uint16_t* queue = S.queue[warp];
+          int qn = 0;  // queued hits (warp-uniform)
+          if (kindM) { sbest[lane] = bestk; __syncwarp(); }
+          auto flush = [&]() {
+            const int n = min(qn, 32);
+            qn -= n;
+            const bool on = lane < n;
+            K2CHECK(qn >= 0 && qn + n <= kQueue);
+            const uint32_t e = on ? (uint32_t)queue[qn + lane] : 0u;
+            const int owner = (int)(e >> 11), p = (int)(e & 0x7FFu);
+            uint4 oa, ob;
+            oa.x = __shfl_sync(FULL, a.x, owner); oa.y = __shfl_sync(FULL, a.y, owner);
+            oa.z = __shfl_sync(FULL, a.z, owner); oa.w = __shfl_sync(FULL, a.w, owner);
+            ob.x = __shfl_sync(FULL, b.x, owner); ob.y = __shfl_sync(FULL, b.y, owner);
+            ob.z = __shfl_sync(FULL, b.z, owner); ob.w = __shfl_sync(FULL, b.w, owner);
+            const uint32_t olo = __shfl_sync(FULL, lo_p, owner), ohi = __shfl_sync(FULL, hi_p, owner);
+            if (on) {
+              const uint32_t k = cand_key(S, p, oa, ob, olo, ohi);
+              K2STAT(5, 1);
+              if (k < sbest[owner]) atomicMin(&sbest[owner], k);
+            }
+            if (lane == 0) K2STAT(7, 1);
+            __syncwarp();
+            const uint32_t sb = sbest[lane];
+            if (sb < bestk) { bestk = sb; tq = (int)(sb >> 19); }
+          };
+          // this item's rows: the chunk around the task's own row (of its first lane), or one of the others
+          const int rown = min(max(__shfl_sync(FULL, og.v, 0), rlo), rhi - 1);
+          const int oc = (rown - ra) / kRowChunk;
+          const int ch = own_chunk ? oc : (other < oc ? other : other + 1);
+          const int ilo = max(ra + ch * kRowChunk, rlo), ihi = min(min(ra + (ch + 1) * kRowChunk, rb), rhi);
+          const bool own_here = own_chunk && rown >= ilo && rown < ihi;
+          for (int ri = own_here ? ilo - 1 : ilo; ri < ihi; ri++) {
+            if (own_here && ri == rown) continue;
+            const int r = (ri < ilo) ? rown : ri;
+            if (valid) {  // bounds found meanwhile by the task's other items
+              const uint32_t gk = *(volatile uint32_t*)&S.gkey[cc][ei];
+              if (gk < bestk) { bestk = gk; tq = (int)(gk >> 19); }
+            }
+            const bool act = (r >= vlo) && (r < vhi);
+            int pg = t.segOff[r][j0] >> 2;            // candidate groups of 4 (every bin list is padded to 4)
+            const int pg1 = t.segOff[r][j1] >> 2;
+            K2CHECK(pg >= 0 && pg1 * 4 <= kCandCap);
+            // 32 candidates (8 groups) at a time: bias + Q has its sign bit set exactly when Q exceeds the lane's bound (lane not
+            // searching this row: always; no bound yet: never), and one funnel shift per candidate collects the signs
+            for (; pg < pg1; pg += 8) {
+              const int nbw = min(8, pg1 - pg);
+              const uint32_t bias = 0x7FFFFFFFu - (uint32_t)(act ? tq : -1);
+              const uint4* qp = Q4 + pg;
+              const uint4* rp = Q14 + pg;
+              uint32_t m = 0;  // MISS bits, candidate i of the word in bit 31 - i once the word is complete
+              if (nbw == 8) {
+                // two independent 16-candidate chains (the funnel shifts of one chain depend on each other)
+                uint32_t mA = 0, mB = 0;
+                if (two) {
+#pragma unroll
+                  for (int i = 0; i < 4; i++) {
+                    const uint4 x = qp[i], y = rp[i], x2 = qp[i + 4], y2 = rp[i + 4];
+                    mA = __funnelshift_l(sad4(qb, y.x, sad4(qa, x.x, bias)), mA, 1);
+                    mB = __funnelshift_l(sad4(qb, y2.x, sad4(qa, x2.x, bias)), mB, 1);
+                    mA = __funnelshift_l(sad4(qb, y.y, sad4(qa, x.y, bias)), mA, 1);
+                    mB = __funnelshift_l(sad4(qb, y2.y, sad4(qa, x2.y, bias)), mB, 1);
+                    mA = __funnelshift_l(sad4(qb, y.z, sad4(qa, x.z, bias)), mA, 1);
+                    mB = __funnelshift_l(sad4(qb, y2.z, sad4(qa, x2.z, bias)), mB, 1);
+                    mA = __funnelshift_l(sad4(qb, y.w, sad4(qa, x.w, bias)), mA, 1);
+                    mB = __funnelshift_l(sad4(qb, y2.w, sad4(qa, x2.w, bias)), mB, 1);
+                  }
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 4; i++) {
+                    const uint4 x = qp[i], x2 = qp[i + 4];
+                    mA = __funnelshift_l(sad4(qa, x.x, bias), mA, 1);
+                    mB = __funnelshift_l(sad4(qa, x2.x, bias), mB, 1);
+                    mA = __funnelshift_l(sad4(qa, x.y, bias), mA, 1);
+                    mB = __funnelshift_l(sad4(qa, x2.y, bias), mB, 1);
+                    mA = __funnelshift_l(sad4(qa, x.z, bias), mA, 1);
+                    mB = __funnelshift_l(sad4(qa, x2.z, bias), mB, 1);
+                    mA = __funnelshift_l(sad4(qa, x.w, bias), mA, 1);
+                    mB = __funnelshift_l(sad4(qa, x2.w, bias), mB, 1);
+                  }
+                }
+                m = mA * 0x10000u + mB;  // both hold 16 bits
+              } else if (two) {
+#pragma unroll 1
+                for (int i = 0; i < nbw; i++) {
+                  const uint4 x = qp[i], y = rp[i];
+                  m = __funnelshift_l(sad4(qb, y.x, sad4(qa, x.x, bias)), m, 1);
+                  m = __funnelshift_l(sad4(qb, y.y, sad4(qa, x.y, bias)), m, 1);
+                  m = __funnelshift_l(sad4(qb, y.z, sad4(qa, x.z, bias)), m, 1);
+                  m = __funnelshift_l(sad4(qb, y.w, sad4(qa, x.w, bias)), m, 1);
+                }
+              } else {
+#pragma unroll 1
+                for (int i = 0; i < nbw; i++) {
+                  const uint4 x = qp[i];
+                  m = __funnelshift_l(sad4(qa, x.x, bias), m, 1);
+                  m = __funnelshift_l(sad4(qa, x.y, bias), m, 1);
+                  m = __funnelshift_l(sad4(qa, x.z, bias), m, 1);
+                  m = __funnelshift_l(sad4(qa, x.w, bias), m, 1);
+                }
+              }
+              uint32_t hit = ~m;
+              if (nbw < 8) hit <<= 32 - 4 * nbw;  // nbw in 1..7: candidate 0 to bit 31, absent candidates never hit
+              bool own = true;  // every lane evaluates its own hits (Z / N tasks: a couple per origin and scan)
+              if (kindM) {
+                const int n = __popc(hit);
+                int incl = n;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                  const int up = __shfl_up_sync(FULL, incl, d);
+                  if (lane >= d) incl += up;
+                }
+                const int total = __shfl_sync(FULL, incl, 31);
+                own = qn + total > kQueue;  // lanes still without a bound hit everything: too many for the queue at once
+                if (!own && total > 0) {
+                  int pos = qn + incl - n;
+                  while (hit != 0u) {
+                    const int z = __clz((int)hit);
+                    hit &= ~(0x80000000u >> z);
+                    K2CHECK(pos >= 0 && pos < kQueue);
+                    queue[pos++] = (uint16_t)((lane << 11) | ((pg << 2) + z));
+                  }
+                  qn += total;
+                  __syncwarp();
+                  while (qn >= 32) flush();
+                }
+              }
+              if (own) {
+                while (hit != 0u) {
+                  const int z = __clz((int)hit);
+                  hit &= ~(0x80000000u >> z);
+                  const uint32_t k = cand_key(S, (pg << 2) + z, a, b, lo_p, hi_p);
+                  K2STAT(kindM ? 5 : 4, 1);
+                  if (__ffs(__activemask()) - 1 == lane) K2STAT(kindM ? 7 : 6, 1);
+                  if (k < bestk) { bestk = k; tq = (int)(k >> 19); }
+                }
+              }
+            }
+          }
+          if (kindM) {
+            __syncwarp();
+            while (qn > 0) flush();
+          }
+          if (valid && bestk < *(volatile uint32_t*)&S.gkey[cc][ei]) atomicMin(&S.gkey[cc][ei], bestk);
+        } else if (!PRUNE) {
+          const int item = item_raw;
+          // ---------- P item (exhaustive mode): 32 origins x one window row, every candidate exactly ----------
+          const int cc = (item < i5) ? 0 : 1;
+          const int pi = item - (cc ? i5 : nFilterItems);
+          const int tb = pi / nrows, r = ra + (pi - tb * nrows);
+          const int ub = ub0 + cc;
+          const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo;
+          uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
+          const int idx = tb * 32 + lane;
+          const bool valid = idx < S.n_p[cc];
+          const int o = (cc ? sO1 : sO0) + (valid ? (int)S.plist[cc][idx] : 0);
+          K2Origin og;
+          load_origin(cc, o, valid, og);
+          const bool act = valid && r >= og.vlo && r < og.vhi;
+          if (!__any_sync(FULL, act)) continue;
+          const uint4 a = og.a, b = og.b;
+          const uint32_t lo_p = og.lo_p, hi_p = og.hi_p;
+          const int p0 = t.segOff[r][j0], p1 = t.segOff[r][j1];
+          K2CHECK(p0 >= 0 && p1 <= kCandCap);
+          uint32_t k = kNone;
+#pragma unroll 2
+          for (int p = p0; p < p1; p++) k = min(k, cand_key(S, p, a, b, lo_p, hi_p));
+          if (act && k != kNone) atomicMin(&bo[o], k - ((uint32_t)j0 << 16));
+        }
+      }
+      if (PRUNE) {
+        // every searched origin's key, from the shared bounds to best[] (origin-column form)
+        __syncthreads();
+#pragma unroll
+        for (int cc = 0; cc < kOC; cc++) {
+          const int ub = ub0 + cc, j0 = max(ub - 3, 0) - ulo;
+          uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
+          for (int i = tid, n = cc ? sN1 : sN0; i < n; i += THREADS) {
+            if (S.cls[cc][i] == 0) continue;
+            const uint32_t k = S.gkey[cc][i];
+            bo[(cc ? sO1 : sO0) + i] = (k == kNone) ? kNone : k - ((uint32_t)j0 << 16);
+          }
+        }
       }
     }
     first_chunk = false;
@@ -722,7 +720,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 template <bool PRUNE, int THREADS>
 __global__ void __launch_bounds__(THREADS, 2)
 k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best, int rows_per_group,
-         int ngroups, int hit_budget, int mode) {
+         int ngroups, int seed_good, int mode) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   K2Smem& S = *reinterpret_cast<K2Smem*>(smem_raw);
   const int cg = blockIdx.x / ngroups, grp = blockIdx.x - cg * ngroups;
@@ -739,7 +737,7 @@ k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __res
   // joint pass over both columns; if a row of the shared window does not fit, one pass per column
   for (int it = -1;;) {
     const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
-                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, hit_budget, mode == 2,
+                                               it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, seed_good, mode == 2,
                                                mode == 1 ? best + (int64_t)(edge - 1) * g.U * 4 * g.col_cap : nullptr);
     if (it < 0 && ok) break;
     if (++it >= noc) break;
@@ -1073,11 +1071,11 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
 
 template <bool PRUNE, int THREADS>
 static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                               int rows_per_group, int hit_budget, bool split, cudaStream_t st) {
+                               int rows_per_group, int seed_good, bool split, cudaStream_t st) {
   const int bytes = (int)sizeof(K2Smem);
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   const int cgroups = (g.U - 1 + kOC - 1) / kOC;
-  const int budget = hit_budget > 0 ? hit_budget : kHitBudget;
+  const int budget = seed_good > 0 ? seed_good : kSeedGood;
   if (!split) {
     dim3 grid(cgroups * ngroups, 8, n_edges / 2);  // edges come in twos (mono: curr->prev, prev->curr; quad: four)
     k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 0);
@@ -1102,12 +1100,12 @@ cudaError_t init_k2_device() {
 }
 
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                      int rows_per_group, int prune, int threads, int hit_budget, int split, cudaStream_t st) {
+                      int rows_per_group, int prune, int threads, int seed_good, int split, cudaStream_t st) {
   // split != 0: the edges are mono pairs (curr->prev, prev->curr) and may run as two dependent launches
-  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, false, st);
-  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, split, st);
-  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, split, st);
-  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, hit_budget, split, st);
+  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, seed_good, false, st);
+  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
+  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
+  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,

@@ -72,8 +72,9 @@ typedef struct vo_config {
                                  (vo_push_back extracts I2), vo_match_features(2) and vo_batch_match_quad run the
                                  quad matcher.  0 (default) = the reference's behaviour: I2 and `method` are ignored. */
   int32_t match_disp_tolerance; /* |dv| window of left<->right edges, src/matcher.h:51; 0 = the default 2 */
-  int32_t match_hit_budget;   /* tuning: candidate groups a lane-per-origin search may queue for exact evaluation before its
-                                 origin is handed to the warp-per-origin pass (0 = library default).  Results do not depend on it. */
+  int32_t match_seed_good;    /* tuning: an origin whose starting bound (SAD of its seed or hint) is above this is matched by
+                                 evaluating every candidate exactly instead of filtering (0 = library default 96).
+                                 Results do not depend on it. */
   int32_t reserved[2];
 } vo_config;
 

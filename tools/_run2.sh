@@ -1,0 +1,9 @@
+set -u
+out=gpurun_out; tag=r2f
+timeout 600 python -m pytest tests/test_gpu_cases.py tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -8 > $out/${tag}_pytest.txt
+cat $out/${tag}_pytest.txt
+for sg in 0 32 64 128 200; do echo "== seed_good $sg"; VO_SEED_GOOD=$sg VO_PROBE_PARITY=1 timeout 300 python tools/noise_probe.py 0 2 8 2>&1 | grep -E "noise|parity|Error" | sed 's/features.*per 64 pairs://'; done > $out/${tag}_seed_sweep.txt 2>&1
+cat $out/${tag}_seed_sweep.txt
+for a in 0 2 8; do VO_B200_LIB=build/ab/libvo_stats.so timeout 120 python tools/k2_stats.py $a; done > $out/${tag}_k2_stats.txt 2>&1
+cat $out/${tag}_k2_stats.txt
+timeout 300 python tools/stress_match.py 40 7 2>&1 | tail -2

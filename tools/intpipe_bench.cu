@@ -26,13 +26,14 @@ constexpr int THREADS = 256;
 constexpr int CTAS_PER_SM = 4;
 
 enum Op { VABS_ACC, VABS_NOACC, IADD3, LOP3, VIMNMX, SHF, IMAD, DP4A, PRMT, POPC, CLZ, BALLOT, REDUX_MIN, SHFL, LDS128_BCAST, LDS32_BCAST,
-          LDS32_GATHER, MIX_VABS_IMAD, MIX_VABS_DP4A, MIX_SAD32_KEY, MIX_FILTER2, N_OPS };
+          LDS32_GATHER, MIX_VABS_IMAD, MIX_VABS_DP4A, MIX_SAD32_KEY, MIX_FILTER2, IMADHI, MIX_F3_SHF, MIX_F3_MADHI, MIX_F3_ADDC, MIX_F3_MADHI1, N_OPS };
 static const char* kNames[N_OPS] = {
     "vabsdiff4_acc", "vabsdiff4", "iadd3", "lop3", "vimnmx_u32", "shf_l_wrap", "imad", "dp4a_u32", "prmt", "popc", "clz", "ballot",
     "redux_min_u32", "shfl_idx", "lds128_broadcast", "lds32_broadcast", "lds32_gather_conflict_free", "mix_1vabs_1imad", "mix_1vabs_1dp4a",
-    "mix_sad32_key(8vabs+imad+min)", "mix_filter(2vabs+and+shf per cand)"};
+    "mix_sad32_key(8vabs+imad+min)", "mix_filter(2vabs+and+shf per cand)",
+    "imad_hi_u32", "mix_filter3(2vabs+shf)", "mix_filter4(2vabs+mad.hi+mad.lo)", "mix_filter4(2vabs+add.cc+addc)", "mix_filter3(2vabs+mad.hi count)"};
 // warp instructions per chain step (for the rate arithmetic)
-static const int kInstPerStep[N_OPS] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 10, 4};
+static const int kInstPerStep[N_OPS] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 10, 4, 1, 3, 4, 4, 3};
 
 template <int OP>
 __global__ void __launch_bounds__(THREADS) bench(uint32_t* out, long long* cycles, uint32_t seed) {
@@ -83,6 +84,32 @@ __global__ void __launch_bounds__(THREADS) bench(uint32_t* out, long long* cycle
         for (int k = 0; k < 8; k++) asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(a[i]), "r"(c + k));
         asm volatile("mad.lo.u32 %0, %0, 0x80000, %1;" : "+r"(s) : "r"(c));
         asm volatile("min.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(s));
+      }
+      if (OP == IMADHI) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+      if (OP == MIX_F3_SHF) {     // per-candidate sign collection, all on the ALU pipe
+        uint32_t s = 0x7FFFFF00u;
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(b), "r"(a[i]));
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(c), "r"(a[i]));
+        asm volatile("shf.l.wrap.b32 %0, %1, %0, 1;" : "+r"(a[i]) : "r"(s));
+      }
+      if (OP == MIX_F3_MADHI) {   // sign bit through the FMA pipe: t = (s * 2) >> 32, m = m * 2 + t
+        uint32_t s = 0x7FFFFF00u, t;
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(b), "r"(a[i]));
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(c), "r"(a[i]));
+        asm volatile("mad.hi.u32 %0, %1, 2, 0;" : "=r"(t) : "r"(s));
+        asm volatile("mad.lo.u32 %0, %0, 2, %1;" : "+r"(a[i]) : "r"(t));
+      }
+      if (OP == MIX_F3_ADDC) {    // sign bit through the carry: s + s sets CF, m = m + m + CF
+        uint32_t s = 0x7FFFFF00u, t;
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(b), "r"(a[i]));
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(c), "r"(a[i]));
+        asm volatile("add.cc.u32 %0, %1, %1;\n\taddc.u32 %2, %2, %2;" : "=r"(t), "+r"(s), "+r"(a[i]));
+      }
+      if (OP == MIX_F3_MADHI1) {  // hit COUNT only: m += (s * 2) >> 32
+        uint32_t s = 0x7FFFFF00u;
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(b), "r"(a[i]));
+        asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(s) : "r"(c), "r"(a[i]));
+        asm volatile("mad.hi.u32 %0, %1, 2, %0;" : "+r"(a[i]) : "r"(s));
       }
       if (OP == MIX_FILTER2) {    // one candidate of K2's two-word filter: bias + Q0 + Q1, sign collected by AND and a funnel shift
         uint32_t s = 0x7FFFFF00u;
@@ -180,6 +207,11 @@ int main() {
   run<MIX_VABS_DP4A>(sms, d_out, d_cyc, h_cyc, ghz, false);
   run<MIX_SAD32_KEY>(sms, d_out, d_cyc, h_cyc, ghz, false);
   run<MIX_FILTER2>(sms, d_out, d_cyc, h_cyc, ghz, false);
+  run<IMADHI>(sms, d_out, d_cyc, h_cyc, ghz, false);
+  run<MIX_F3_SHF>(sms, d_out, d_cyc, h_cyc, ghz, false);
+  run<MIX_F3_MADHI>(sms, d_out, d_cyc, h_cyc, ghz, false);
+  run<MIX_F3_ADDC>(sms, d_out, d_cyc, h_cyc, ghz, false);
+  run<MIX_F3_MADHI1>(sms, d_out, d_cyc, h_cyc, ghz, false);
   printf("\n]}\n");
   return 0;
 }

@@ -17,18 +17,17 @@ ANCHORS = [  # (first line containing the string starts the region)
     ("tables", "const int32_t* cnt_to = fa.cnt"),
     ("chunk setup", "bool first_chunk = true;"),
     ("staging", "// ---- stage: warp per (row, column) bin list"),
-    ("task setup + origin load", "// ---- tasks: 32 consecutive origins"),
-    ("hint validate", "if (PRUNE && use_hint && vlo < vhi) {"),
-    ("seed", "if (PRUNE && __any_sync(FULL, full && vlo < vhi)) {"),
-    ("pre-filter (hand_over, votes)", "sbest[lane] = bestk;"),
-    ("flush (exact evaluation of queued groups)", "auto flush = [&]() {"),
-    ("expand (flooding lane)", "auto expand = [&](int L"),
-    ("row loop", "// rows in the order own row"),
-    ("filter loops", "const uint32_t bias = 0x7FFFFFFFu"),
-    ("hits / budget", "m &= kNone >> (32 - nb);"),
-    ("compaction", "const uint32_t gfirst = lane16"),
-    ("task end", "while (qn > 0) flush();"),
-    ("hard pass", "// ---- handed-over origins"),
+    ("load_origin", "auto load_origin = [&]"),
+    ("pass 1: setup / hint", "// ================= pass 1"),
+    ("pass 1: seed", "if (PRUNE && __any_sync(FULL, need_seed && rows_here)) {"),
+    ("pass 1: class + ordered lists", "// ---- class: Z (bound 0)"),
+    ("pass 2: item claim", "// ================= pass 2"),
+    ("good task: setup", "// ---------- filter task"),
+    ("good task: flush (cooperative evaluation)", "auto flush = [&]() {"),
+    ("good task: row loop", "// rows in the order own row (of the first lane)"),
+    ("good task: filter", "// 32 candidates (8 groups) at a time"),
+    ("good task: hits (queue / own loop)", "bool own = true;  // every lane evaluates its own hits"),
+    ("P item", "// ---------- P item"),
     ("kernel entry / rest", "first_chunk = false;"),
 ]
 

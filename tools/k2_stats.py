@@ -12,7 +12,7 @@ if amp:
     rng = np.random.default_rng(100 + amp)
     seq = np.clip(seq.astype(np.int16) + rng.integers(-amp, amp + 1, seq.shape, dtype=np.int16), 0, 255).astype(np.uint8)
 eng = Engine(W, H, max_frames=B + 1, max_pairs=B)
-lib = ctypes.CDLL(LIB)
+lib = ctypes.CDLL(os.environ.get("VO_B200_LIB", LIB))
 out = (ctypes.c_ulonglong * 8)()
 eng.batch_extract_host(0, seq)
 lib.vo_debug_k2_stats(out)
@@ -20,8 +20,7 @@ prev = np.arange(B, dtype=np.int32); curr = prev + 1
 eng.batch_match(prev, curr, 2, 50.0, 50.0)
 eng.synchronize()
 lib.vo_debug_k2_stats(out)
-names = ["origins", "lanes in two-word warps", "seed none", "seed T==0", "filter hits (groups)", "budget handovers", "hard pass: origins",
-         "hard pass: queued candidates"]
+names = ["origins (per chunk)", "Z: bound 0", "N: bound <= seed_good", "P: exhaustive", "lane hits, Z/N tasks", "lane hits, M tasks", "warp hit iterations, Z/N tasks", "warp hit iterations, M tasks"]
 print(f"noise +-{amp}")
 for n, v in zip(names, out):
     print(f"{n:24s} {v / B:12.1f} per pair")

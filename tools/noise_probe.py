@@ -16,12 +16,12 @@ from hls_final_visual_odometry_b200.synth import make_sequence  # noqa: E402
 
 W, H, B = 1241, 376, 64
 amps = [int(a) for a in sys.argv[1:]] or [0, 1, 2, 4, 8]
-budget = int(os.environ.get("VO_HIT_BUDGET", "0"))
+budget = int(os.environ.get("VO_SEED_GOOD", "0"))
 base = make_sequence(W, H, B + 1, seed=1).astype(np.int16)
 for amp in amps:
     rng = np.random.default_rng(100 + amp)
     seq = np.clip(base + (rng.integers(-amp, amp + 1, base.shape, dtype=np.int16) if amp else 0), 0, 255).astype(np.uint8)
-    eng = Engine(W, H, max_frames=B + 1, max_pairs=B, match_hit_budget=budget,
+    eng = Engine(W, H, max_frames=B + 1, max_pairs=B, match_seed_good=budget,
                  match_threads=int(os.environ.get("VO_MATCH_THREADS", "0")))
     prev = np.arange(B, dtype=np.int32)
     eng.batch_extract_host(0, seq)
