@@ -59,10 +59,11 @@ constexpr int kSegW = kMaxCols + 1;
 constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
 constexpr int kMaxWarps = 16;
 constexpr int kQueue = 128;     // pending hits per warp (M tasks): < 32 left over + what one 32-candidate word adds in one go
+static_assert(kMaxV <= 64, "list entries carry the row in 6 bits");
 constexpr int kListCap = 512;   // origins per column sorted in one go (a longer column list is processed in segments)
 constexpr int kMergeBelow = 12; // a Z or N list shorter than this joins the other list's tasks (either filter is exact for both)
 #ifndef VO_K2_ROW_CHUNK
-#define VO_K2_ROW_CHUNK 2
+#define VO_K2_ROW_CHUNK 3
 #endif
 constexpr int kRowChunk = VO_K2_ROW_CHUNK;  // window rows per work item of pass 2
 constexpr int kBig = 1 << 20;
@@ -297,13 +298,15 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     }
 
     // origin (column cc, col_idx o) into a lane's registers; its candidate rows clipped to this chunk
-    auto load_origin = [&](int cc, int o, bool valid, K2Origin& og) {
+    auto load_origin = [&](int cc, int o, bool valid, int v_known, K2Origin& og) {  // v_known < 0: find the row
       og.v = r0; og.vlo = kBig; og.vhi = 0; og.lo_full = 0; og.hi_full = 0;
       og.a = make_uint4(0, 0, 0, 0); og.b = og.a; og.qa = 0; og.qb = 0;
       uint32_t oxy = 0;
       if (valid) {
         int v = r0;
-        while (t.prefO[cc][v + 1] <= o) v++;
+        if (v_known >= 0) v = v_known;
+        else while (t.prefO[cc][v + 1] <= o) v++;
+        K2CHECK(v >= r0 && v < r1 && o >= t.prefO[cc][v] && o < t.prefO[cc][v + 1]);
         const int64_t rec = (int64_t)((v * U + ub0 + cc) * 4 + c) * g.cap + (o - t.prefO[cc][v]);
         oxy = __ldg(&xy_from[rec]);
         og.a = __ldg(&desc_from[2 * rec]);
@@ -342,7 +345,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         const bool valid = tb * 32 + lane < (cc ? sN1 : sN0);
         uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
         K2Origin og;
-        load_origin(cc, o, valid, og);
+        load_origin(cc, o, valid, -1, og);
         uint32_t bestk = kNone, hint = kNone;
         bool need_seed = valid;  // no bound yet
         bool skip = false;       // hinted direction: no feature of the other frame points here, the cycle cannot close
@@ -426,7 +429,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
         K2STAT(3, poor ? 1 : 0);
         if (valid) {
           const int i = tb * 32 + lane;
-          S.cls[cc][i] = !searching ? 0 : poor ? 3 : (tq == 0 ? 1 : 2);
+          S.cls[cc][i] = (uint8_t)((!searching ? 0 : poor ? 3 : (tq == 0 ? 1 : 2)) | (og.v << 2));  // kind | row << 2
           S.gkey[cc][i] = bestk;
           if (poor) bo[o] = ext;  // exhaustive mode merges into it with atomicMin
           else if (!searching) bo[o] = (skip && !last_chunk) ? kSkip : ext;  // nothing to search in this chunk
@@ -448,10 +451,12 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
 #pragma unroll
           for (int u = 0; u < 4; u++) {
             const int i = i0 + u * 32 + lane;
-            const uint32_t bz = __ballot_sync(FULL, k[u] == 1), bn = __ballot_sync(FULL, k[u] == 2), bm = __ballot_sync(FULL, k[u] == 3);
-            if (k[u] == 1) S.glist[cc][tz + __popc(bz & lt_mask)] = (uint16_t)i;
-            if (k[u] == 2) S.glist[cc][kListCap - 1 - (tn + __popc(bn & lt_mask))] = (uint16_t)i;
-            if (k[u] == 3) S.plist[cc][tm + __popc(bm & lt_mask)] = (uint16_t)i;
+            const int kind = k[u] & 3;
+            const uint16_t ent = (uint16_t)(i | ((k[u] >> 2) << 9));  // list entry: index within the segment | row << 9
+            const uint32_t bz = __ballot_sync(FULL, kind == 1), bn = __ballot_sync(FULL, kind == 2), bm = __ballot_sync(FULL, kind == 3);
+            if (kind == 1) S.glist[cc][tz + __popc(bz & lt_mask)] = ent;
+            if (kind == 2) S.glist[cc][kListCap - 1 - (tn + __popc(bn & lt_mask))] = ent;
+            if (kind == 3) S.plist[cc][tm + __popc(bm & lt_mask)] = ent;
             tz += __popc(bz); tn += __popc(bn); tm += __popc(bm);
           }
         }
@@ -510,11 +515,12 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             slot = idx;
           }
           K2CHECK(slot >= 0 && slot < kListCap);
-          const int ei = valid ? (int)(kindM ? S.plist[cc][slot] : S.glist[cc][slot]) : 0;
+          const int ent = valid ? (int)(kindM ? S.plist[cc][slot] : S.glist[cc][slot]) : 0;
+          const int ei = ent & (kListCap - 1);
           const int o = (cc ? sO1 : sO0) + ei;
           uint32_t bestk = valid ? S.gkey[cc][ei] : kNone;
           K2Origin og;
-          load_origin(cc, o, valid, og);
+          load_origin(cc, o, valid, ent >> 9, og);
           const uint4 a = og.a, b = og.b;
           const uint32_t qa = og.qa, qb = og.qb, lo_p = og.lo_p, hi_p = og.hi_p;
           const int vlo = og.vlo, vhi = og.vhi;
@@ -680,9 +686,10 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
           const int idx = tb * 32 + lane;
           const bool valid = idx < S.n_p[cc];
-          const int o = (cc ? sO1 : sO0) + (valid ? (int)S.plist[cc][idx] : 0);
+          const int ent = valid ? (int)S.plist[cc][idx] : 0;
+          const int o = (cc ? sO1 : sO0) + (ent & (kListCap - 1));
           K2Origin og;
-          load_origin(cc, o, valid, og);
+          load_origin(cc, o, valid, ent >> 9, og);
           const bool act = valid && r >= og.vlo && r < og.vhi;
           if (!__any_sync(FULL, act)) continue;
           const uint4 a = og.a, b = og.b;
@@ -703,7 +710,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           const int ub = ub0 + cc, j0 = max(ub - 3, 0) - ulo;
           uint32_t* bo = best_dir + (int64_t)(ub * 4 + c) * g.col_cap;
           for (int i = tid, n = cc ? sN1 : sN0; i < n; i += THREADS) {
-            if (S.cls[cc][i] == 0) continue;
+            if ((S.cls[cc][i] & 3) == 0) continue;
             const uint32_t k = S.gkey[cc][i];
             bo[(cc ? sO1 : sO0) + i] = (k == kNone) ? kNone : k - ((uint32_t)j0 << 16);
           }
