@@ -66,6 +66,10 @@ constexpr int kMergeBelow = 12; // a Z or N list shorter than this joins the oth
 #define VO_K2_ROW_CHUNK 3
 #endif
 constexpr int kRowChunk = VO_K2_ROW_CHUNK;  // window rows per work item of pass 2
+#ifndef VO_K2_FLOOD
+#define VO_K2_FLOOD 12
+#endif
+constexpr int kFlood = VO_K2_FLOOD;  // M tasks: a lane with at least this many hits in a 32-candidate word is expanded by the whole warp
 constexpr int kBig = 1 << 20;
 constexpr uint32_t kSkip = 0xFFFFFFFEu;  // best[] between the chunks of a hinted search: nobody points at this origin (never a real key: SAD <= 8160)
 #ifndef VO_K2_SEED_GOOD
@@ -549,7 +553,6 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             const uint32_t olo = __shfl_sync(FULL, lo_p, owner), ohi = __shfl_sync(FULL, hi_p, owner);
             if (on) {
               const uint32_t k = cand_key(S, p, oa, ob, olo, ohi);
-              K2STAT(5, 1);
               if (k < sbest[owner]) atomicMin(&sbest[owner], k);
             }
             if (lane == 0) K2STAT(7, 1);
@@ -636,7 +639,34 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
               if (nbw < 8) hit <<= 32 - 4 * nbw;  // nbw in 1..7: candidate 0 to bit 31, absent candidates never hit
               bool own = true;  // every lane evaluates its own hits (Z / N tasks: a couple per origin and scan)
               if (kindM) {
-                const int n = __popc(hit);
+                // (1) a lane whose bound hardly prunes (none yet, or a flat patch that is close to everything) would keep the
+                //     queue writes below running for its many hits while 31 lanes wait: the whole warp takes its word
+                //     instead, lane j its candidate j
+                int n = __popc(hit);
+#ifdef VO_K2_STATS
+                { const int mx = __reduce_max_sync(FULL, n), tot = __reduce_add_sync(FULL, n); const int nl = __popc(__ballot_sync(FULL, n > 0));
+                  if (lane == 0) { K2STAT(4, 1); K2STAT(5, tot); K2STAT(6, mx); K2STAT(7, nl); } }
+#endif
+                uint32_t flood = __ballot_sync(FULL, n >= kFlood);
+                while (flood != 0u) {
+                  const int L = __ffs((int)flood) - 1;
+                  flood &= flood - 1u;
+                  const uint32_t mL = __shfl_sync(FULL, hit, L);
+                  uint4 oa, ob;
+                  oa.x = __shfl_sync(FULL, a.x, L); oa.y = __shfl_sync(FULL, a.y, L);
+                  oa.z = __shfl_sync(FULL, a.z, L); oa.w = __shfl_sync(FULL, a.w, L);
+                  ob.x = __shfl_sync(FULL, b.x, L); ob.y = __shfl_sync(FULL, b.y, L);
+                  ob.z = __shfl_sync(FULL, b.z, L); ob.w = __shfl_sync(FULL, b.w, L);
+                  const uint32_t olo = __shfl_sync(FULL, lo_p, L), ohi = __shfl_sync(FULL, hi_p, L);
+                  uint32_t k = kNone;
+                  if ((mL << lane) & 0x80000000u) { k = cand_key(S, (pg << 2) + lane, oa, ob, olo, ohi); }
+                  k = __reduce_min_sync(FULL, k);
+                  if (lane == L) {
+                    hit = 0u; n = 0;
+                    if (k < bestk) { bestk = k; tq = (int)(k >> 19); }
+                  }
+                }
+                // (2) the other lanes' hits join the queue at positions from a warp scan
                 int incl = n;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
@@ -646,12 +676,13 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                 const int total = __shfl_sync(FULL, incl, 31);
                 own = qn + total > kQueue;  // lanes still without a bound hit everything: too many for the queue at once
                 if (!own && total > 0) {
-                  int pos = qn + incl - n;
+                  uint16_t* qw = queue + (qn + incl - n);
+                  const uint32_t ebase = ((uint32_t)lane << 11) | (uint32_t)(pg << 2);
+                  K2CHECK(qn + incl <= kQueue);
                   while (hit != 0u) {
                     const int z = __clz((int)hit);
                     hit &= ~(0x80000000u >> z);
-                    K2CHECK(pos >= 0 && pos < kQueue);
-                    queue[pos++] = (uint16_t)((lane << 11) | ((pg << 2) + z));
+                    *qw++ = (uint16_t)(ebase + (uint32_t)z);
                   }
                   qn += total;
                   __syncwarp();
@@ -663,8 +694,6 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                   const int z = __clz((int)hit);
                   hit &= ~(0x80000000u >> z);
                   const uint32_t k = cand_key(S, (pg << 2) + z, a, b, lo_p, hi_p);
-                  K2STAT(kindM ? 5 : 4, 1);
-                  if (__ffs(__activemask()) - 1 == lane) K2STAT(kindM ? 7 : 6, 1);
                   if (k < bestk) { bestk = k; tq = (int)(k >> 19); }
                 }
               }

@@ -26,7 +26,7 @@ ANCHORS = [  # (first line containing the string starts the region)
     ("good task: flush (cooperative evaluation)", "auto flush = [&]() {"),
     ("good task: row loop", "rows: the chunk around the task"),
     ("good task: filter", "// 32 candidates (8 groups) at a time"),
-    ("good task: hits (queue rounds)", "queue, one per lane and round (most words"),
+    ("good task: hits (queue / own loop)", "bool own = true;  // every lane evaluates its own hits"),
     ("P item", "// ---------- P item"),
     ("write-out", "// every searched origin's key, from the shared bounds"),
     ("kernel entry / rest", "first_chunk = false;"),

@@ -20,7 +20,7 @@ prev = np.arange(B, dtype=np.int32); curr = prev + 1
 eng.batch_match(prev, curr, 2, 50.0, 50.0)
 eng.synchronize()
 lib.vo_debug_k2_stats(out)
-names = ["origins (per chunk)", "Z: bound 0", "N: bound <= seed_good", "P: exhaustive", "lane hits, Z/N tasks", "lane hits, M tasks", "warp hit iterations, Z/N tasks", "warp hit iterations, M tasks"]
+names = ["origins (per chunk)", "Z: bound 0", "N: bound <= seed_good", "P: exhaustive", "M tasks: 32-candidate words", "M tasks: filter hits", "M tasks: sum over words of the busiest lane's hits", "M tasks: sum over words of lanes with a hit"]
 print(f"noise +-{amp}")
 for n, v in zip(names, out):
     print(f"{n:24s} {v / B:12.1f} per pair")
