@@ -57,7 +57,7 @@ EXPORTS = [
     "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
     "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
-    "vo_pipeline_process", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
+    "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
 ]
 
 class VoStereoParams(C.Structure):  # vo_stereo_params: /root/reference/src/viso_stereo.h:31-43
@@ -141,6 +141,7 @@ def load_library() -> C.CDLL:
         "vo_pipeline_create": [vp, C.POINTER(VoMonoParams), i32, f32, f32, i32, C.POINTER(vp)],
         "vo_pipeline_destroy": [vp],
         "vo_pipeline_process": [vp, i32, vp, i64, i32, vp, vp, vp, vp, vp, i64],
+        "vo_pipeline_stage_seconds": [vp, vp],
         "vo_estimate_motion_stereo": [vp, vp, i32, C.POINTER(VoStereoParams), C.POINTER(C.c_double), C.POINTER(i32)],
         "vo_batch_match_quad": [vp, i32, vp, vp, vp, vp, i32, i32, i32, f32, f32],
         "vo_batch_refine": [vp, i32],
@@ -679,6 +680,17 @@ class Pipeline:
             self.lib.vo_pipeline_destroy(self.h)
             self.h = None
             self.engine.close()
+
+    STAGES = ("extract_match_gpu", "raw_lists_d2h", "remove_outliers_host", "bucket_h2d_gpu_d2h", "ransac_samples_host",
+              "egomotion_host")
+
+    def stage_seconds(self) -> dict:
+        """Wall seconds process() has spent per stage since creation (vo_pipeline_stage_seconds)."""
+        out = np.zeros(6, np.float64)
+        st = self.lib.vo_pipeline_stage_seconds(self.h, _ptr(out))
+        if st != VO_OK:
+            raise VoError(st, "vo_pipeline_stage_seconds")
+        return dict(zip(self.STAGES, out.tolist()))
 
     def process(self, frames: np.ndarray, want_matches: bool = False):
         """frames: (n, H, pitch>=W) uint8, n <= batch.  -> ok[n], tr[n,6], n_matches[n], n_inliers[n] (, lists)."""

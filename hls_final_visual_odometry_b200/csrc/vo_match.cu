@@ -56,16 +56,13 @@ constexpr int kMaxV = 64;       // v-bin rows supported by the shared-memory tab
 constexpr int kOC = 2;          // origin u-bin columns per CTA (they share the staged window)
 constexpr int kMaxCols = kOC + 5;  // staged target columns: [ub0-3, ub_last+3) clipped
 constexpr int kSegW = kMaxCols + 1;
-constexpr int kCandCap = 1920;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
+constexpr int kCandCap = 1896;  // staged candidates per chunk; >= 6*300 so a row of a one-column window always fits
 constexpr int kMaxWarps = 16;
 constexpr int kQueue = 128;     // pending hits per warp (M tasks): < 32 left over + what one 32-candidate word adds in one go
 static_assert(kMaxV <= 64, "list entries carry the row in 6 bits");
+constexpr int kMaxTasks = 72;   // filter tasks of one segment: per column <= 16 Z/N (+1 for a split) + 16 M, two columns
 constexpr int kListCap = 512;   // origins per column sorted in one go (a longer column list is processed in segments)
 constexpr int kMergeBelow = 12; // a Z or N list shorter than this joins the other list's tasks (either filter is exact for both)
-#ifndef VO_K2_ROW_CHUNK
-#define VO_K2_ROW_CHUNK 3
-#endif
-constexpr int kRowChunk = VO_K2_ROW_CHUNK;  // window rows per work item of pass 2
 #ifndef VO_K2_FLOOD
 #define VO_K2_FLOOD 12
 #endif
@@ -91,7 +88,9 @@ struct K2Tables {
 struct __align__(128) K2Smem {
   K2Tables t;
   int32_t n_z[kOC], n_n[kOC], n_p[kOC];  // entries of the three lists of this segment
-  int32_t next_item;                  // pass 2: next unclaimed work item
+  int32_t next_item;                  // pass 2: next unclaimed task
+  int32_t task_ctr[kMaxTasks];        // pass 2: next unclaimed window row of a task (in its own row order)
+  int32_t task_nr[kMaxTasks];         // pass 2: window rows of a task, once some warp has looked (-1 before)
   uint16_t glist[kOC][kListCap];      // well-bounded origins (index within the segment): Z from the front, N from the back
   uint32_t gkey[kOC][kListCap];       // bound of every origin of the segment (key, staged-column form), by index
   uint16_t plist[kOC][kListCap];      // M: origins with a poor bound or none (exhaustive mode: every origin)
@@ -333,6 +332,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
     for (int seg = 0; seg < nseg; seg++) {
       __syncthreads();  // staging complete / previous segment's lists consumed
       if (tid == 32) S.next_item = 0;
+      if (tid >= 64 && tid < 64 + kMaxTasks) { S.task_ctr[tid - 64] = 0; S.task_nr[tid - 64] = -1; }
       __syncthreads();
 
       // ================= pass 1: a bound for every origin, origins sorted by what it is worth =================
@@ -481,21 +481,15 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       const int nrows = rb - ra;
       const int iM = nTM0 + nTM1;
       const int i1 = iM + nTN0, i2 = i1 + nTN1, i3 = i2 + nTZ0, i4 = i3 + nTZ1;
-      // A filter task is cut into work items of kRowChunk window rows so that the warps of the CTA stay evenly loaded; the
-      // items of a task share their origins' bounds through gkey[].  Items 0..i4-1 are every task's chunk around its own
-      // row (where a small flow puts the partner: bounds tighten first), the remaining chunks follow.
-      const int nchunks = (nrows + kRowChunk - 1) / kRowChunk;
-      const int nFilterItems = i4 * nchunks;
-      const int i5 = nFilterItems + (PRUNE ? 0 : ((np0 + 31) >> 5) * nrows), n_items = i5 + (PRUNE ? 0 : ((np1 + 31) >> 5) * nrows);
-      for (;;) {
-        int item_raw = 0;
-        if (lane == 0) item_raw = atomicAdd(&S.next_item, 1);
-        item_raw = __shfl_sync(FULL, item_raw, 0);
-        if (item_raw >= n_items) break;
-        if (item_raw < nFilterItems) {
-          const bool own_chunk = item_raw < i4;
-          const int item = own_chunk ? item_raw : (item_raw - i4) / (nchunks - 1);
-          const int other = own_chunk ? 0 : (item_raw - i4) - item * (nchunks - 1);
+      // Scheduling: a warp claims a task (32 sorted origins; M first: the long ones), loads its origins once and then takes
+      // the task's window rows one at a time from a per-task counter -- own row first, where a small flow puts the partner.
+      // A warp that finds no unclaimed task JOINS unfinished ones and takes rows from the same counters, so the CTA's
+      // warps finish within a row of each other; the warps working on a task share its bounds through gkey[].
+      const int nFilterTasks = i4;
+      K2CHECK(nFilterTasks <= kMaxTasks);
+      const int i5 = (PRUNE ? 0 : ((np0 + 31) >> 5) * nrows), n_items = i5 + (PRUNE ? 0 : ((np1 + 31) >> 5) * nrows);
+      if (PRUNE) {
+        auto run_task = [&](const int item) {
           // ---------- filter task: lower-bound filter, one bit per candidate, every lane evaluates its own hits ----------
           const bool kindM = item < iM;
           const int cc = kindM ? (item < nTM0 ? 0 : 1) : (item < i1) ? 0 : (item < i2) ? 1 : (item < i3) ? 0 : 1;
@@ -560,16 +554,17 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             const uint32_t sb = sbest[lane];
             if (sb < bestk) { bestk = sb; tq = (int)(sb >> 19); }
           };
-          // this item's rows: the chunk around the task's own row (of its first lane), or one of the others
+          // rows in the order own row (of the first lane), then the rest, each claimed from the task's counter
           const int rown = min(max(__shfl_sync(FULL, og.v, 0), rlo), rhi - 1);
-          const int oc = (rown - ra) / kRowChunk;
-          const int ch = own_chunk ? oc : (other < oc ? other : other + 1);
-          const int ilo = max(ra + ch * kRowChunk, rlo), ihi = min(min(ra + (ch + 1) * kRowChunk, rb), rhi);
-          const bool own_here = own_chunk && rown >= ilo && rown < ihi;
-          for (int ri = own_here ? ilo - 1 : ilo; ri < ihi; ri++) {
-            if (own_here && ri == rown) continue;
-            const int r = (ri < ilo) ? rown : ri;
-            if (valid) {  // bounds found meanwhile by the task's other items
+          const int nr = rhi - rlo;
+          if (lane == 0) *(volatile int32_t*)&S.task_nr[item] = nr;
+          for (;;) {
+            int sq = 0;
+            if (lane == 0) sq = atomicAdd(&S.task_ctr[item], 1);
+            sq = __shfl_sync(FULL, sq, 0);
+            if (sq >= nr) break;
+            const int r = (sq == 0) ? rown : (rlo + sq - 1 >= rown ? rlo + sq : rlo + sq - 1);
+            if (valid) {  // bounds found meanwhile by the other warps working on this task
               const uint32_t gk = *(volatile uint32_t*)&S.gkey[cc][ei];
               if (gk < bestk) { bestk = gk; tq = (int)(gk >> 19); }
             }
@@ -698,17 +693,41 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                 }
               }
             }
+            if (valid && bestk < *(volatile uint32_t*)&S.gkey[cc][ei]) atomicMin(&S.gkey[cc][ei], bestk);  // publish
           }
           if (kindM) {
             __syncwarp();
             while (qn > 0) flush();
           }
           if (valid && bestk < *(volatile uint32_t*)&S.gkey[cc][ei]) atomicMin(&S.gkey[cc][ei], bestk);
-        } else if (!PRUNE) {
+        };
+        for (int help = -1;;) {
+          int item = 0;
+          if (help < 0) {  // fresh tasks first
+            if (lane == 0) item = atomicAdd(&S.next_item, 1);
+            item = __shfl_sync(FULL, item, 0);
+            if (item >= nFilterTasks) { help = 0; continue; }
+          } else {         // then help with what is still running, longest (M) first
+            for (; help < nFilterTasks; help++) {
+              const int nr = *(volatile int32_t*)&S.task_nr[help];
+              if (nr < 0 || *(volatile int32_t*)&S.task_ctr[help] < nr) break;  // rows of it are still unclaimed
+            }
+            if (help >= nFilterTasks) break;
+            item = help++;
+          }
+          run_task(item);
+        }
+      }
+      for (; !PRUNE;) {
+        int item_raw = 0;
+        if (lane == 0) item_raw = atomicAdd(&S.next_item, 1);
+        item_raw = __shfl_sync(FULL, item_raw, 0);
+        if (item_raw >= n_items) break;
+        {
           const int item = item_raw;
           // ---------- P item (exhaustive mode): 32 origins x one window row, every candidate exactly ----------
           const int cc = (item < i5) ? 0 : 1;
-          const int pi = item - (cc ? i5 : nFilterItems);
+          const int pi = item - (cc ? i5 : 0);
           const int tb = pi / nrows, r = ra + (pi - tb * nrows);
           const int ub = ub0 + cc;
           const int j0 = max(ub - 3, 0) - ulo, j1 = min(ub + 3, U - 1) - ulo;

@@ -11,6 +11,7 @@
 // Results per frame are exactly those of calling process() frame by frame (same stages, same order, same random
 // samples); only the schedule differs.  Built on the public entry points of vo_b200.h alone.
 #include <atomic>
+#include <chrono>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -33,9 +34,15 @@ struct vo_pipeline {
   int32_t* counts;          // pinned: 2 x max_pairs
   int32_t bucket_cap;
   std::vector<int32_t> n_raw, n_filtered;
+  double stage_s[6];        // wall seconds spent so far: extract+match (GPU), raw lists to host, removeOutliers (host pool),
+                            // host->bucket->host (GPU), RANSAC sample sets (host, serial), egomotion (host pool)
 };
 
 namespace {
+
+inline double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 template <class F>
 void parallel_for(int n, int threads, F fn) {
@@ -81,6 +88,7 @@ vo_status vo_pipeline_create(vo_engine* e, const vo_mono_params* prm, int32_t ma
   p->threads = host_threads > 0 ? host_threads : hw;
   p->frames_seen = 0;
   p->last_slot = -1;
+  for (double& x : p->stage_s) x = 0.0;
   // buckets: (W / bw + 1) x (H / bh + 1), max_features each
   p->bucket_cap = ((int32_t)(p->geo.width / bucket_w) + 2) * ((int32_t)(p->geo.height / bucket_h) + 2) * max_features;
   if (p->bucket_cap > p->geo.max_matches) p->bucket_cap = p->geo.max_matches;
@@ -123,6 +131,8 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
   const int S = p->geo.max_frames;
   int64_t M = p->geo.max_matches;
   vo_status st;
+  double t_mark = now_s();
+  auto lap = [&](int stage) { const double t = now_s(); p->stage_s[stage] += t - t_mark; t_mark = t; };
   // ---- frames into consecutive slots of the ring (split at the wrap) ------------------------------------------
   const int first = (p->last_slot + 1) % S;
   for (int done = 0; done < n;) {
@@ -147,6 +157,7 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
     p->n_raw.assign(np, 0);
     st = vo_batch_counts(p->eng, np, p->n_raw.data(), nullptr);
     if (st != VO_OK) return st;
+    lap(0);
     int32_t widest = 1;
     for (int i = 0; i < np; i++) widest = p->n_raw[i] > widest ? p->n_raw[i] : widest;
     M = widest;  // host stride of the raw lists of this batch
@@ -161,6 +172,7 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
     if (st != VO_OK) return st;
     st = vo_engine_synchronize(p->eng);
     if (st != VO_OK) return st;
+    lap(1);
     // ---- host: Delaunay support filter, pairs in parallel (src/matcher.cpp:108, src/remove_outliers.cpp:4) --------
     p->n_filtered = p->n_raw;
     std::atomic<int> bad(0);
@@ -168,6 +180,7 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
       if (vo_remove_outliers_host(p->raw + (int64_t)i * M, &p->n_filtered[i]) != VO_OK) bad = 1;
     });
     if (bad) return VO_ERR_INVALID;
+    lap(2);
     // ---- GPU: bucketing of the filtered lists (src/matcher.cpp:140-187) -------------------------------------------
     st = vo_batch_bucket_host(p->eng, np, p->raw, M, p->n_filtered.data(), p->max_features, p->bw, p->bh);
     if (st != VO_OK) return st;
@@ -175,6 +188,7 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
     if (st != VO_OK) return st;
     st = vo_engine_synchronize(p->eng);
     if (st != VO_OK) return st;
+    lap(3);
     // ---- host: sample sets in frame order, then egomotion of every pair in parallel -------------------------------
     const int iters = p->prm.ransac_iters > 0 ? p->prm.ransac_iters : 0;
     std::vector<int32_t> samples((size_t)np * iters * 8), drawn(np, 0);
@@ -185,6 +199,7 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
                                      samples.data() + (size_t)i * iters * 8, &drawn[i]);
       if (st != VO_OK) return st;
     }
+    lap(4);
     parallel_for(np, p->threads, [&](int i) {
       const int f = i + skip;
       const int32_t nb = p->counts[np + i];
@@ -196,9 +211,17 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
         std::memcpy(matches_out + (int64_t)f * matches_stride, p->bucketed + (int64_t)i * p->bucket_cap, sizeof(vo_p_match) * (size_t)nb);
     });
     if (bad) return VO_ERR_INVALID;
+    lap(5);
   }
   p->frames_seen += n;
   p->last_slot = (first + n - 1) % S;
+  return VO_OK;
+}
+
+// wall seconds per stage accumulated by vo_pipeline_process since creation (see vo_pipeline::stage_s)
+vo_status vo_pipeline_stage_seconds(const vo_pipeline* p, double* out6) {
+  if (!p || !out6) return VO_ERR_INVALID;
+  for (int i = 0; i < 6; i++) out6[i] = p->stage_s[i];
   return VO_OK;
 }
 

@@ -322,6 +322,9 @@ void      vo_pipeline_destroy(vo_pipeline* p);
 vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, int64_t frame_stride_bytes,
                               int32_t pitch_bytes, int32_t* ok, double* tr_delta, int32_t* n_matches,
                               int32_t* n_inliers, vo_p_match* matches_out, int64_t matches_stride);
+/* Wall seconds vo_pipeline_process has spent per stage since creation: {extract + match (GPU), raw lists to the host,
+   removeOutliers (host pool), host -> bucketing -> host (GPU), RANSAC sample sets (host, serial), egomotion (host pool)}. */
+vo_status vo_pipeline_stage_seconds(const vo_pipeline* p, double* out6);
 
 /* ---------------------------------------------------------------------------------------- */
 /* instrumentation                                                                           */

@@ -45,13 +45,15 @@ def main():
         ok, tr, nm, ni = pipe.process(host[s:s + args.batch])
         oks.append(ok); nms.append(nm); nis.append(ni)
     wall = time.perf_counter() - t0
+    stages = pipe.stage_seconds()
     pipe.close()
     ok, nm, ni = np.concatenate(oks), np.concatenate(nms), np.concatenate(nis)
     out = {"workload": f"configs[2]: {args.frames}-frame rendered corridor sequence {W}x{H}, full process() loop",
            "frames": args.frames, "seconds": wall, "frames_per_s": args.frames / wall,
            "process_ok_frames": int(ok.sum()), "mean_bucketed_matches": float(nm[1:].mean()),
            "mean_inliers": float(ni[ok == 1].mean()) if ok.any() else 0.0,
-           "host_threads": args.threads or os.cpu_count(), "batch": args.batch}
+           "host_threads": args.threads or os.cpu_count(), "batch": args.batch,
+           "stage_seconds": stages, "stage_ms_per_frame": {k: 1e3 * v / args.frames for k, v in stages.items()}}
     # ---- the reference's own chain, one thread (it has no threads), on a few frames -----------------------------
     try:
         from oracle.oracle_lib import Oracle
