@@ -14,7 +14,9 @@
 #include <vector>
 
 namespace vo {
-size_t k1_smem_bytes();
+bool k1_supports(int bin_w, int bin_h);
+int k2_cand_cap();
+void k1_box(int bin_w, int bin_h, int* tw, int* th);
 cudaError_t init_k1_device();
 cudaError_t init_k2_device();
 cudaError_t init_k4_device();
@@ -173,13 +175,16 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// 3-D u8 tensor (x, y, frame) with a 96x59x1 box; out-of-bounds reads return zeros.
-vo_status make_tmap(CUtensorMap* m, const void* base, int W, int H, int n, int64_t pitch, int64_t frame_stride) {
+// 3-D u8 tensor (x, y, frame) with the tile kernel's box (96x59x1 for 60x45 bins); out-of-bounds reads return zeros.
+vo_status make_tmap(CUtensorMap* m, const void* base, int W, int H, int n, int64_t pitch, int64_t frame_stride, int bin_w, int bin_h) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return fail(VO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
   cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
-  cuuint32_t box[3] = {96, 59, 1};
+  int tw = 0, th = 0;
+  vo::k1_box(bin_w, bin_h, &tw, &th);
+  if (tw <= 0) return fail(VO_ERR_UNSUPPORTED, "bin size %dx%d", bin_w, bin_h);
+  cuuint32_t box[3] = {(cuuint32_t)tw, (cuuint32_t)th, 1};
   cuuint32_t es[3] = {1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, es,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -487,9 +492,9 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   if (cfg.max_pairs == 0) cfg.max_pairs = 1;
   if (cfg.width < 128 || cfg.height < 64 || cfg.width > 16384 || cfg.height > 16384)
     return fail(VO_ERR_INVALID, "image size %dx%d outside [128..16384]x[64..16384]", cfg.width, cfg.height);
-  if (cfg.bin_w != 60 || cfg.bin_h != 45)
-    return fail(VO_ERR_UNSUPPORTED, "bin size %dx%d: the reference path (src/size.h:10-11) and the sm_100a tile "
-                "kernel are specialised for 60x45", cfg.bin_w, cfg.bin_h);
+  if (!vo::k1_supports(cfg.bin_w, cfg.bin_h))
+    return fail(VO_ERR_UNSUPPORTED, "bin size %dx%d: the sm_100a tile kernel is built for 60x45 (the reference's, "
+                "src/size.h:10-11), 45x45, 60x30 and 90x30", cfg.bin_w, cfg.bin_h);
   if (cfg.nms_tau < 1 || cfg.nms_tau > 32767) return fail(VO_ERR_INVALID, "nms_tau out of range");
   if (cfg.max_frames < 2 || cfg.max_pairs < 1) return fail(VO_ERR_INVALID, "max_frames >= 2 and max_pairs >= 1 required");
 
@@ -526,6 +531,11 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
     const int gu = g.U, gv = g.V;
     delete e;
     return fail(VO_ERR_UNSUPPORTED, "geometry U=%d V=%d exceeds kernel tables (V<=64, cap*V<=65535)", gu, gv);
+  }
+  if (6 * ((g.cap + 3) & ~3) > vo::k2_cand_cap()) {
+    const int cap = g.cap;
+    delete e;
+    return fail(VO_ERR_UNSUPPORTED, "bin capacity %d: six bin lists of a window row exceed the matcher's staging buffer", cap);
   }
   if (cfg.max_matches == 0) cfg.max_matches = g.U * g.V * g.cap;
   e->cfg = cfg;
@@ -621,7 +631,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   }
   e->h_pairs = e->h_pairs_base; e->h_edges = e->h_edges_base; e->h_quads = e->h_quads_base;
   for (int64_t i = 0; i < P * vo_engine::kStageGens; i++) e->h_quads_base[i] = make_int4(-1, -1, -1, -1);
-  vo_status s = make_tmap(&e->tmap_slots, e->fa.img, g.W, g.H, (int)S, g.pitch, e->fa.img_stride);
+  vo_status s = make_tmap(&e->tmap_slots, e->fa.img, g.W, g.H, (int)S, g.pitch, e->fa.img_stride, g.bin_w, g.bin_h);
   if (s != VO_OK) { vo_engine_destroy(e); return s; }
   if (cudaStreamSynchronize(e->stream) != cudaSuccess) { vo_engine_destroy(e); return fail(VO_ERR_CUDA, "init sync"); }
   *out = e;
@@ -1001,7 +1011,7 @@ vo_status vo_batch_extract_device(vo_engine* e, int32_t first_slot, int32_t n, c
   const bool tma_ok = ((uintptr_t)d_images % 16 == 0) && (pitch_bytes % 16 == 0) && (frame_stride_bytes % 16 == 0);
   if (tma_ok) {  // read the caller's HBM-resident frames in place through a tensor map of their own
     CUtensorMap tm;
-    vo_status s = make_tmap(&tm, d_images, e->g.W, e->g.H, n, pitch_bytes, frame_stride_bytes);
+    vo_status s = make_tmap(&tm, d_images, e->g.W, e->g.H, n, pitch_bytes, frame_stride_bytes, e->g.bin_w, e->g.bin_h);
     if (s != VO_OK) return s;
     for (int i = 0; i < n; i++) e->slot_has_image[first_slot + i] = 0;  // the slots hold features only
     return do_extract(e, tm, first_slot, 0, n);

@@ -1,4 +1,4 @@
-// K1: fused feature extraction for one 60x45-pixel bin tile per CTA (sm_100a).
+// K1: fused feature extraction for one bin tile (60x45 pixels in the reference) per CTA (sm_100a).
 //
 // Replaces, bit-exactly, the reference's
 //   mySobel5x5 / myBlob5x5 / myCheckerboard5x5           src/myComputeFeature.cpp:58-151
@@ -15,34 +15,43 @@
 
 namespace vo {
 
-constexpr int BW = 60, BH = 45;          // bin size this kernel is specialised for
-constexpr int TW = 96, TH = 59;          // TMA box: 74x59 needed; the box must START on a 16-byte boundary in x
-                                         // (u8 elements: measured, unaligned inner coordinates fault), so up to 15
-                                         // lead-in bytes + 74 -> 96
-constexpr int OW = 70, OH = 55;          // du/dv/f1/f2 region: tile cols 2..71, rows 2..56
-constexpr int NBX = BW / 3, NBY = BH / 3;  // 20 x 15 NMS blocks per tile
 constexpr int K1_THREADS = 320;
 constexpr int K1_WARPS = K1_THREADS / 32;
-
-struct __align__(128) K1Smem {
-  uint8_t img[TH * TW];
-  unsigned long long bar;
-  uint16_t duv[OH * OW];  // du | dv<<8
-  uint16_t f1[OH * OW];   // blob response + kFBias
-  uint16_t f2[OH * OW];   // checkerboard response + kFBias
-  int32_t warp_tot[K1_WARPS][4];
-  uint32_t work[4][NBX * NBY];  // per class, in list order: ox | oy<<8 | twin rank<<16 | twin class<<30 | has twin<<31
-};
-
-// Filter phase work split: a thread owns two adjacent output columns (packed into the two 16-bit
-// halves of a register) and slides down a strip of kStripRows output rows.
-constexpr int kColPairs = OW / 2;                        // 35
 constexpr int kStripRows = 7;
-constexpr int kStrips = (OH + kStripRows - 1) / kStripRows;  // 8
 constexpr uint32_t kHBias = 0x04000400u;                 // +1024 per half: keeps signed horizontal sums non-negative
 constexpr uint32_t kFBias = 4096;                        // f1/f2 are stored as value + 4096 (range [16, 8176])
-static_assert(kColPairs * kStrips <= K1_THREADS, "filter phase needs one thread per (column pair, strip)");
-static_assert(OW % 2 == 0, "column pairs");
+
+// Tile geometry for a bin of BW_ x BH_ pixels (60 x 45 is the reference's, src/size.h:10-11; the others are the live
+// `match_binsize` of SURVEY.md row F4, checked against the reference compiled with those numbers).
+template <int BW_, int BH_>
+struct K1Tile {
+  static constexpr int BW = BW_, BH = BH_;
+  // TMA box: (BW+14) x (BH+14) needed; the box must START on a 16-byte boundary in x (u8 elements: measured, unaligned
+  // inner coordinates fault), so up to 15 lead-in bytes are added and the width rounded to 16 (60 -> 74 + 15 -> 96)
+  static constexpr int TW = (BW + 14 + 15 + 15) & ~15, TH = BH + 14;
+  static constexpr int OW = (BW + 10 + 1) & ~1, OH = BH + 10;   // du/dv/f1/f2 region: tile cols 2.., rows 2..; even width
+  static constexpr int NBX = BW / 3, NBY = BH / 3;              // NMS blocks per tile (20 x 15)
+  // Filter phase work split: a thread owns two adjacent output columns (packed into the two 16-bit halves of a
+  // register) and slides down a strip of kStripRows output rows.
+  static constexpr int kColPairs = OW / 2;                        // 35
+  static constexpr int kStrips = (OH + kStripRows - 1) / kStripRows;  // 8
+  static_assert(BW % 3 == 0 && BH % 3 == 0, "bins are whole 3x3 NMS blocks");
+  static_assert(kColPairs * kStrips <= K1_THREADS, "filter phase needs one thread per (column pair, strip)");
+  static_assert(NBX * NBY <= K1_THREADS, "NMS phase needs one thread per 3x3 block");
+  static_assert(TW <= 256 && TH <= 256, "TMA box dimensions");
+  static_assert(OW + 19 <= TW, "the box holds the widest lead-in (15) + the last column pair's six bytes");
+};
+
+template <class T>
+struct __align__(128) K1SmemT {
+  uint8_t img[T::TH * T::TW];
+  unsigned long long bar;
+  uint16_t duv[T::OH * T::OW];  // du | dv<<8
+  uint16_t f1[T::OH * T::OW];   // blob response + kFBias
+  uint16_t f2[T::OH * T::OW];   // checkerboard response + kFBias
+  int32_t warp_tot[K1_WARPS][4];
+  uint32_t work[4][T::NBX * T::NBY];  // per class, in list order: ox | oy<<8 | twin rank<<16 | twin class<<30 | has twin<<31
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -57,8 +66,12 @@ __device__ __forceinline__ uint32_t sobel_u8x2(uint32_t x) {
   return ((x + neg * 127u) >> 7) & 0x01FF01FFu;
 }
 
+template <class T>
 __global__ void __launch_bounds__(K1_THREADS)
 k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int first_slot, int z_base) {
+  constexpr int BW = T::BW, BH = T::BH, TW = T::TW, TH = T::TH, OW = T::OW, OH = T::OH, NBX = T::NBX, NBY = T::NBY;
+  constexpr int kColPairs = T::kColPairs, kStrips = T::kStrips;
+  using K1Smem = K1SmemT<T>;
   extern __shared__ __align__(128) uint8_t smem_raw[];
   K1Smem& s = *reinterpret_cast<K1Smem*>(smem_raw);
   const int tid = threadIdx.x;
@@ -309,20 +322,47 @@ __global__ void k_load_features(Geom g, FrameArrays fa, int slot, const int32_t*
   }
 }
 
-size_t k1_smem_bytes() { return sizeof(K1Smem); }
+// ---- bin sizes this library is built for: the reference's 60 x 45 and the live `match_binsize` values of row F4 ----------
+// (a list can hold (BW/3)*(BH/3) records; K2 stages six lists of a window row at once, so 6 * cap must fit its buffer)
+#define VO_K1_TILES(X) X(60, 45) X(45, 45) X(60, 30) X(90, 30)
+
+bool k1_supports(int bin_w, int bin_h) {
+#define X(w, h) if (bin_w == w && bin_h == h) return true;
+  VO_K1_TILES(X)
+#undef X
+  return false;
+}
+
+// TMA box of the tile kernel for a bin size (vo_engine builds the tensor maps)
+void k1_box(int bin_w, int bin_h, int* tw, int* th) {
+  *tw = 0; *th = 0;
+#define X(w, h) if (bin_w == w && bin_h == h) { *tw = K1Tile<w, h>::TW; *th = K1Tile<w, h>::TH; }
+  VO_K1_TILES(X)
+#undef X
+}
 
 // The opt-in to more than 48 KB of dynamic shared memory is a per-DEVICE function attribute: vo_engine_create calls this
 // (and its K2 / K4 counterparts) after cudaSetDevice, so a process that owns engines on several GPUs sets it on each.
 cudaError_t init_k1_device() {
-  return cudaFuncSetAttribute(k1_extract, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem));
+  cudaError_t e = cudaSuccess;
+#define X(w, h) if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_extract<K1Tile<w, h>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1SmemT<K1Tile<w, h>>));
+  VO_K1_TILES(X)
+#undef X
+  return e;
 }
 
 cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
                       cudaStream_t st) {
-  const int rows = g.j_last / BH + 1;  // tile rows that contain at least one block row
+  const int rows = g.j_last / g.bin_h + 1;  // tile rows that contain at least one block row
   dim3 grid(g.U, rows, n);
-  k1_extract<<<grid, K1_THREADS, sizeof(K1Smem), st>>>(tmap, g, fa, first_slot, z_base);
-  return cudaGetLastError();
+#define X(w, h)                                                                                                          \
+  if (g.bin_w == w && g.bin_h == h) {                                                                                    \
+    k1_extract<K1Tile<w, h>><<<grid, K1_THREADS, sizeof(K1SmemT<K1Tile<w, h>>), st>>>(tmap, g, fa, first_slot, z_base);  \
+    return cudaGetLastError();                                                                                           \
+  }
+  VO_K1_TILES(X)
+#undef X
+  return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t* max2, int32_t* max2_num,

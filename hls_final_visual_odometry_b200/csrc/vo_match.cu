@@ -1144,6 +1144,9 @@ static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4*
   return cudaGetLastError();
 }
 
+// staged candidates per chunk: a window row of one origin column (six bin lists, each padded to 4) must fit
+int k2_cand_cap() { return kCandCap; }
+
 // per-device opt-in to K2's dynamic shared memory, every instantiation launch_k2 can pick (see init_k1_device)
 cudaError_t init_k2_device() {
   const int bytes = (int)sizeof(K2Smem);

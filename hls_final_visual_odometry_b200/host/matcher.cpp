@@ -23,6 +23,8 @@ bool Matcher::ensureEngine(int32_t width, int32_t height) {
   // the reference's executed path hard-codes tau = 50 whatever parameters::nms_tau says (src/myComputeFeature.cpp:157);
   // a drop-in does the same unless the caller opts in to the (unpinned) live parameter
   cfg.nms_tau = live_nms_tau ? param.nms_tau : 0;
+  cfg.bin_w = live_bin_w;
+  cfg.bin_h = live_bin_h;
   cfg.stereo = stereo ? 1 : 0;
   cfg.match_disp_tolerance = param.match_disp_tolerance;
   last_status = vo_engine_create(&cfg, device, nullptr, &eng);

@@ -92,6 +92,12 @@ class Matcher {
   // pushBack to make it live instead.  nms_n / match_binsize / match_radius stay ignored like in the reference.
   void useLiveNmsTau(bool on) { live_nms_tau = on; }
 
+  // EXTENSION: the feature-list bin size, BIN_W x BIN_H of src/size.h:10-11 (60 x 45), as a run-time choice.
+  // Supported: 60x45, 45x45, 60x30, 90x30 (bit-exact against the reference compiled with those numbers,
+  // tests/golden/golden.json "*_b<BW>x<BH>"); anything else makes the first pushBack fail with VO_ERR_UNSUPPORTED.  The
+  // search window stays 3 bins either way (SEARCH_RAD_U/V, src/size.h:14-15).  Call before the first pushBack.
+  void useBinSize(int32_t bin_w, int32_t bin_h) { live_bin_w = bin_w; live_bin_h = bin_h; }
+
   // last C-ABI status (0 = ok) and message, for callers that want more than the reference's cerr line
   int lastStatus() const { return last_status; }
   const char* lastError() const;
@@ -105,6 +111,7 @@ class Matcher {
   vo_engine* eng;
   int last_status;
   bool live_nms_tau = false;
+  int32_t live_bin_w = 0, live_bin_h = 0;  // 0 = the reference's 60 x 45
   std::function<void(std::vector<Matcher::p_match>&)> outlier_filter;
 };
 

@@ -59,7 +59,9 @@ typedef struct vo_p_match {
  * Fields left 0 take the reference value. */
 typedef struct vo_config {
   int32_t width, height;   /* image size in pixels; >= 64 x 64 */
-  int32_t bin_w, bin_h;    /* 60, 45 (must be multiples of 3) */
+  int32_t bin_w, bin_h;    /* 0 = 60 x 45 (BIN_W, BIN_H of src/size.h:10-11).  Also built: 45x45, 60x30, 90x30 (live bin size,
+                              SURVEY.md row F4: bit-exact against the reference compiled with those numbers); anything else
+                              -> VO_ERR_UNSUPPORTED */
   int32_t nms_tau;         /* 50 */
   int32_t max_frames;      /* frame slots held on the device (>= 2; default 2) */
   int32_t max_pairs;       /* frame pairs matched per batch call (>= 1; default 1) */

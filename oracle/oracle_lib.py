@@ -34,10 +34,10 @@ def _p(a):
 
 
 class Oracle:
-    def __init__(self, width: int, height: int):
+    def __init__(self, width: int, height: int, bin_w: int = 60, bin_h: int = 45):
         self.lib = C.CDLL(build())
         self.g = Geom()
-        self.lib.vo_oracle_geom_init(C.byref(self.g), width, height, width)
+        self.lib.vo_oracle_geom_init_bins(C.byref(self.g), width, height, width, bin_w, bin_h)
         self.W, self.H = width, height
         self.U, self.V, self.CAP = self.g.u_bins, self.g.v_bins, self.g.cap
         self.lib.vo_oracle_rand_number.restype = C.c_uint32

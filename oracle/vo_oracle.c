@@ -46,14 +46,18 @@ typedef struct vo_oracle_match { /* == Matcher::p_match, src/matcher.h:89-104 */
 /* Geometry for a WxH image with the reference's bin size.  U = bin of the last block origin + 1
  * (block origins are i = 9, 12, ... < W-9, src/myComputeFeature.cpp:175,259); V = H/BIN_H + 1
  * (the trailing flush targets v_bin = IMG_H/BIN_H, src/myComputeFeature.cpp:337). */
-void vo_oracle_geom_init(vo_oracle_geom* g, int32_t width, int32_t height, int32_t pitch) {
+void vo_oracle_geom_init_bins(vo_oracle_geom* g, int32_t width, int32_t height, int32_t pitch, int32_t bin_w, int32_t bin_h) {
   g->width = width; g->height = height; g->pitch = pitch;
-  g->bin_w = 60; g->bin_h = 45;
+  g->bin_w = bin_w; g->bin_h = bin_h;  /* BIN_W, BIN_H: src/size.h:10-11 (multiples of 3: the flush rule of :319 needs it) */
   int32_t last_i = 9 + 3 * ((width - 10 - 9) / 3);
   g->u_bins = last_i / g->bin_w + 1;
   g->v_bins = height / g->bin_h + 1;
   g->cap = (g->bin_w / 3) * (g->bin_h / 3);
   g->tau = 50;
+}
+
+void vo_oracle_geom_init(vo_oracle_geom* g, int32_t width, int32_t height, int32_t pitch) {
+  vo_oracle_geom_init_bins(g, width, height, pitch, 60, 45);
 }
 
 /* ---------------------------------------------------------------------------------------------

@@ -61,7 +61,41 @@ def pair_record(ref: RefLib, prev, curr, with_post=False):
     return rec
 
 
+BIN_TAGS = ["1241x376_b45x45", "1024x284_b60x30", "1241x376_b90x30"]  # live bin size: the reference with other BIN_W / BIN_H
+
+
+def bin_geometries():
+    """geometries of the reference compiled with other bin sizes (oracle/build_ref.sh <W>x<H>_b<BW>x<BH>)"""
+    out = {}
+    for tag in BIN_TAGS:
+        ref = RefLib(tag)
+        g = {"W": ref.W, "H": ref.H, "U": ref.U, "V": ref.V, "bin_w": ref.BIN_W, "bin_h": ref.BIN_H, "cases": {}}
+        seq = make_sequence(ref.W, ref.H, 3, seed=0)
+        g["cases"]["textured_seed0_f01"] = pair_record(ref, seq[0], seq[1], with_post=True)
+        g["cases"]["textured_seed0_f12"] = pair_record(ref, seq[1], seq[2], with_post=True)
+        from oracle.oracle_lib import Oracle
+        orc = Oracle(ref.W, ref.H, ref.BIN_W, ref.BIN_H)
+        for name in ADVERSARIAL:
+            a, b = cases.CASES[name](ref.W, ref.H, 0)
+            fa, fb = orc.compute_features(a), orc.compute_features(b)
+            if orc.matching(fa[0], fa[1], fb[0], fb[1], cap=1 << 18)[1][1] != 0:
+                continue  # an origin without candidates outside the dead column: the reference reads an uninitialised
+                          # min_cand there (SURVEY.md section 8c fence (2)), its output is not defined
+            g["cases"][name] = pair_record(ref, a, b, with_post=(name != "dense"))
+        out[tag] = g
+        print(tag, "done", sorted(g["cases"]), flush=True)
+    return out
+
+
 def main():
+    if "--bins-only" in sys.argv:  # add the bin-size geometries to the committed file, leave the rest as it is
+        path = os.path.join(HERE, "golden.json")
+        out = json.load(open(path))
+        for tag in BIN_TAGS:
+            out["geometries"].pop(tag, None)
+        out["geometries"].update(bin_geometries())
+        json.dump(out, open(path, "w"), indent=1, sort_keys=True)
+        return
     out = {"about": "sha256 digests of outputs of the reference sources compiled in place (oracle/_ref)",
            "geometries": {}, "lfsr": {}, "filters": {}, "matcher_flow": {}, "outliers": {}}
     for tag in ["native", "1024x284", "500x150", "1241x376", "2048x1024"]:
@@ -78,6 +112,7 @@ def main():
                 g["cases"][name] = pair_record(ref, a, b, with_post=(name != "dense"))
         out["geometries"][tag] = g
         print(tag, "done", flush=True)
+    out["geometries"].update(bin_geometries())
 
     ref = RefLib("native")
     x, seq_vals = 5, []

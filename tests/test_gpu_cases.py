@@ -40,6 +40,29 @@ def test_adversarial_vs_oracle(name, size):
         eng.close()
 
 
+# live bin size: the tile kernel's other instantiations, incl. the cases the reference leaves undefined
+@pytest.mark.parametrize("geo", [(1241, 376, 45, 45), (1024, 284, 60, 30), (1241, 376, 90, 30), (2048, 1024, 45, 45)],
+                         ids=lambda g: f"{g[0]}x{g[1]}_b{g[2]}x{g[3]}")
+@pytest.mark.parametrize("name", ["holes", "dead_zone_only", "low_contrast", "dense", "periodic"])
+def test_bin_sizes_vs_oracle(name, geo):
+    w, h, bw, bh = geo
+    prev, curr = cases.CASES[name](w, h, 0)
+    orc = Oracle(w, h, bw, bh)
+    eng = Engine(w, h, max_frames=2, max_pairs=1, bin_w=bw, bin_h=bh)
+    try:
+        assert (eng.U, eng.V, eng.CAP) == (orc.U, orc.V, orc.CAP)
+        fp = orc.compute_features(prev)[:2]
+        fc = orc.compute_features(curr)[:2]
+        eng.batch_extract_host(0, np.stack([prev, curr]))
+        assert_features_equal(eng.slot_dump_features(0), fp, f"{name} prev")
+        assert_features_equal(eng.slot_dump_features(1), fc, f"{name} curr")
+        eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+        want, _ = orc.matching(fp[0], fp[1], fc[0], fc[1], cap=1 << 18)
+        assert_matches_equal(eng.batch_get_matches(0, 0), want, name)
+    finally:
+        eng.close()
+
+
 def test_engines_on_two_devices_in_one_process():
     """the > 48 KB shared-memory opt-in of K1/K2/K4 is a per-device attribute: an engine on a second GPU of the same
     process must work like the first (round-1 bug: a process-wide `static bool attr_set`)"""
@@ -76,7 +99,7 @@ def test_cuda_matches_reference_golden(tag, name):
     geom = GOLD["geometries"][tag]
     rec = geom["cases"][name]
     prev, curr = _inputs(geom, name)
-    eng = Engine(geom["W"], geom["H"], max_frames=2, max_pairs=1)
+    eng = Engine(geom["W"], geom["H"], max_frames=2, max_pairs=1, bin_w=geom.get("bin_w", 0), bin_h=geom.get("bin_h", 0))
     try:
         eng.batch_extract_host(0, np.stack([prev, curr]))
         assert features_digest(*eng.slot_dump_features(0)) == rec["features_prev"]

@@ -34,6 +34,27 @@ def test_operators_bit_exact(tag):
     assert len(raw_r) == len(raw_o) and matches_digest(raw_r) == matches_digest(raw_o)
 
 
+@pytest.mark.parametrize("tag", ["1241x376_b45x45", "1024x284_b60x30", "1241x376_b90x30"])
+def test_bin_sizes_bit_exact(tag):
+    """live bin size: the reference's own sources with other BIN_W / BIN_H numbers (src/size.h:10-11) against
+    the oracle generalised the same way"""
+    if not have_ref(tag):
+        pytest.skip("oracle/_ref not built for this bin size")
+    ref = RefLib(tag)
+    orc = Oracle(ref.W, ref.H, ref.BIN_W, ref.BIN_H)
+    assert (orc.U, orc.V, orc.CAP) == (ref.U, ref.V, ref.CAP)
+    seq = make_sequence(ref.W, ref.H, 3, seed=5)
+    feats_r = [ref.compute_features(seq[f]) for f in range(3)]
+    feats_o = [orc.compute_features(seq[f])[:2] for f in range(3)]
+    for (mr, nr), (mo, no) in zip(feats_r, feats_o):
+        assert features_digest(mr, nr) == features_digest(mo, no)
+    for a, b in ((0, 1), (1, 2)):
+        raw_r = ref.matching(feats_r[a][0], feats_r[a][1], feats_r[b][0], feats_r[b][1])
+        raw_o, stats = orc.matching(feats_o[a][0], feats_o[a][1], feats_o[b][0], feats_o[b][1])
+        assert stats[1] == 0
+        assert len(raw_r) == len(raw_o) and matches_digest(raw_r) == matches_digest(raw_o)
+
+
 @needs_ref
 def test_native_and_override_builds_agree():
     """the geometry-override build (only numbers replaced) reproduces the unmodified reference"""
