@@ -4,9 +4,9 @@ Hand-written CUDA for sm_100a behind a C ABI (include/vo_b200.h); this package i
 mirror of the reference's Matcher interface plus the synthetic-frame generator used by tests and
 bench.py.  No CPU implementation of the hot path lives here.
 """
-from .api import (Engine, Matcher, VoError, P_MATCH_DTYPE, load_library, pinned_empty, Egomotion,  # noqa: F401
+from .api import (Engine, Matcher, VoError, P_MATCH_DTYPE, load_library, pinned_empty, Egomotion, RansacGpu,  # noqa: F401
                   VisualOdometryMono, transformation_vector_to_matrix, Pipeline, EgomotionStereo, VisualOdometryStereo)
 from . import synth  # noqa: F401
 
-__all__ = ["Engine", "Matcher", "VoError", "P_MATCH_DTYPE", "load_library", "pinned_empty", "synth", "Egomotion",
+__all__ = ["Engine", "Matcher", "VoError", "P_MATCH_DTYPE", "load_library", "pinned_empty", "synth", "Egomotion", "RansacGpu",
            "VisualOdometryMono", "transformation_vector_to_matrix", "Pipeline", "EgomotionStereo", "VisualOdometryStereo"]

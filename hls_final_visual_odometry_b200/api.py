@@ -57,7 +57,8 @@ EXPORTS = [
     "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
     "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
-    "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
+    "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_engine_device", "vo_estimate_motion_mono_best",
+    "vo_ransac_gpu_create", "vo_ransac_gpu_destroy", "vo_ransac_gpu_score", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
 ]
 
 class VoStereoParams(C.Structure):  # vo_stereo_params: /root/reference/src/viso_stereo.h:31-43
@@ -137,6 +138,12 @@ def load_library() -> C.CDLL:
         "vo_egomotion_draw_samples": [vp, vp, i32, C.POINTER(VoMonoParams), vp, C.POINTER(i32)],
         "vo_estimate_motion_mono_samples": [vp, i32, C.POINTER(VoMonoParams), vp, i32, i32, C.POINTER(C.c_double), C.POINTER(i32),
                                             vp, i32, C.POINTER(i32)],
+        "vo_estimate_motion_mono_best": [vp, i32, C.POINTER(VoMonoParams), vp, i32, i32, C.POINTER(C.c_double), C.POINTER(i32),
+                                         vp, i32, C.POINTER(i32)],
+        "vo_ransac_gpu_create": [i32, i32, i32, i32, C.POINTER(vp)],
+        "vo_ransac_gpu_destroy": [vp],
+        "vo_ransac_gpu_score": [vp, i32, vp, i64, vp, C.POINTER(VoMonoParams), vp, i64, vp, vp, vp],
+        "vo_engine_device": [vp, C.POINTER(i32)],
         "vo_batch_bucket_host": [vp, i32, vp, i64, vp, i32, f32, f32],
         "vo_pipeline_create": [vp, C.POINTER(VoMonoParams), i32, f32, f32, i32, C.POINTER(vp)],
         "vo_pipeline_destroy": [vp],
@@ -151,7 +158,8 @@ def load_library() -> C.CDLL:
     for name, args in sigs.items():
         fn = getattr(lib, name)
         fn.argtypes = args
-        if name in ("vo_engine_destroy", "vo_egomotion_destroy", "vo_transformation_vector_to_matrix", "vo_pipeline_destroy"):
+        if name in ("vo_engine_destroy", "vo_egomotion_destroy", "vo_transformation_vector_to_matrix", "vo_pipeline_destroy",
+                    "vo_ransac_gpu_destroy"):
             fn.restype = None
         elif name == "vo_egomotion_rand":
             fn.restype = C.c_uint32
@@ -496,6 +504,33 @@ class Egomotion:
             raise VoError(st, "vo_estimate_motion_mono")
         return np.array(tr[:], dtype=np.float64) if ok.value else None
 
+    # ---- the two-step form: sample sets drawn in frame order, estimation stateless (and scorable on the GPU) ----
+    def draw_samples(self, matches: np.ndarray):
+        """-> (samples int32[iters, 8], iters drawn): the sets the reference would draw for this list (advances the stream)."""
+        m = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)
+        smp = np.zeros((max(self.prm.ransac_iters, 1), 8), np.int32)
+        n = C.c_int32(0)
+        st = self.lib.vo_egomotion_draw_samples(self.h, _ptr(m) if len(m) else None, len(m), C.byref(self.prm), _ptr(smp), C.byref(n))
+        if st != VO_OK:
+            raise VoError(st, "vo_egomotion_draw_samples")
+        return smp, n.value
+
+    def estimate_with_samples(self, matches: np.ndarray, samples: np.ndarray, iters: int, best_k: int | None = None):
+        """-> (tr or None, inlier indices).  best_k: the RANSAC winner if already known (RansacGpu.score), else scored here."""
+        m = np.ascontiguousarray(matches, dtype=P_MATCH_DTYPE)
+        tr = (C.c_double * 6)()
+        ok, ni = C.c_int32(0), C.c_int32(0)
+        inl = np.zeros(max(len(m), 1), np.int32)
+        if best_k is None:
+            st = self.lib.vo_estimate_motion_mono_samples(_ptr(m) if len(m) else None, len(m), C.byref(self.prm), _ptr(samples), iters, 1,
+                                                          tr, C.byref(ok), _ptr(inl), len(inl), C.byref(ni))
+        else:
+            st = self.lib.vo_estimate_motion_mono_best(_ptr(m) if len(m) else None, len(m), C.byref(self.prm), _ptr(samples), iters,
+                                                       int(best_k), tr, C.byref(ok), _ptr(inl), len(inl), C.byref(ni))
+        if st != VO_OK:
+            raise VoError(st, "vo_estimate_motion_mono_samples/_best")
+        return (np.array(tr[:], dtype=np.float64) if ok.value else None), inl[: ni.value].copy()
+
     def inliers(self) -> np.ndarray:
         n = C.c_int32(0)
         self.lib.vo_egomotion_inliers(self.h, None, 0, C.byref(n))
@@ -505,6 +540,43 @@ class Egomotion:
 
     def rand(self) -> int:
         return int(self.lib.vo_egomotion_rand(self.h))
+
+
+class RansacGpu:
+    """vo_ransac_gpu_*: the RANSAC hypotheses of VisualOdometryMono::estimateMotion (/root/reference/src/viso_mono.cpp:63-77)
+    scored on the GPU, one thread per hypothesis, with the host stage's own arithmetic."""
+
+    def __init__(self, max_lists: int, max_points: int, max_iters: int = 2000, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        st = self.lib.vo_ransac_gpu_create(device, max_lists, max_points, max_iters, C.byref(h))
+        if st != VO_OK:
+            raise VoError(st, "vo_ransac_gpu_create")
+        self.h, self.max_points, self.max_iters = h, max_points, max_iters
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vo_ransac_gpu_destroy(self.h)
+            self.h = None
+
+    def score(self, lists, prm: "VoMonoParams", samples, drawn):
+        """lists: sequence of match arrays; samples: sequence of int32[iters, 8]; drawn: iterations per list.
+        -> (best_k[n], best_count[n])"""
+        n = len(lists)
+        buf = np.zeros((n, self.max_points), dtype=P_MATCH_DTYPE)
+        cnt = np.zeros(n, np.int32)
+        smp = np.zeros((n, self.max_iters, 8), np.int32)
+        for i, (l, s) in enumerate(zip(lists, samples)):
+            buf[i, : len(l)] = l
+            cnt[i] = len(l)
+            smp[i, : len(s)] = s
+        dr = np.ascontiguousarray(drawn, dtype=np.int32)
+        bk, bc = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        st = self.lib.vo_ransac_gpu_score(self.h, n, _ptr(buf), self.max_points, _ptr(cnt), C.byref(prm), _ptr(smp), self.max_iters,
+                                          _ptr(dr), _ptr(bk), _ptr(bc))
+        if st != VO_OK:
+            raise VoError(st, "vo_ransac_gpu_score")
+        return bk, bc
 
 
 class EgomotionStereo(Egomotion):
@@ -682,11 +754,11 @@ class Pipeline:
             self.engine.close()
 
     STAGES = ("extract_match_gpu", "raw_lists_d2h", "remove_outliers_host", "bucket_h2d_gpu_d2h", "ransac_samples_host",
-              "egomotion_host")
+              "ransac_score_gpu", "egomotion_host")
 
     def stage_seconds(self) -> dict:
         """Wall seconds process() has spent per stage since creation (vo_pipeline_stage_seconds)."""
-        out = np.zeros(6, np.float64)
+        out = np.zeros(7, np.float64)
         st = self.lib.vo_pipeline_stage_seconds(self.h, _ptr(out))
         if st != VO_OK:
             raise VoError(st, "vo_pipeline_stage_seconds")

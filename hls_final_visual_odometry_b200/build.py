@@ -20,6 +20,9 @@ DEMO = os.path.join(_PKG, "vo_demo")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    # no FMA contraction in device code either: vo_ransac.cu scores RANSAC hypotheses with the host stage's own arithmetic
+    # (vo_ransac_core.h) and must land on the same inlier counts; the other kernels are integer code
+    "-fmad=false",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall",
     # the host Delaunay stage (vo_outliers.cpp) must round exactly like the reference's x86 build
     "-Xcompiler", "-ffp-contract=off",

@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "../../include/vo_b200.h"
+#include "vo_ransac_core.h"
 
 namespace {
 
@@ -61,93 +62,15 @@ struct GlibcRand {
   }
 };
 
-// ---------------------------------------------------------------------------------------------
-// One-sided Jacobi SVD of a row-major m x n matrix (any m, n <= kMaxN columns).
-// Output: w[n] singular values in descending order, V (n x n, row-major, orthogonal: a product of plane
-// rotations), and G = A*V (m x n), whose column j has norm w[j] (u_j = G[:,j] / w[j] where w[j] > 0).
-// ---------------------------------------------------------------------------------------------
-constexpr int kMaxN = 9;
+// One-sided Jacobi SVD, 3 x 3 SVD, rank-2 projection, the 8-point system and the Sampson test live in vo_ransac_core.h (shared
+// with the device kernel that scores RANSAC hypotheses).  The general m x n entry keeps its std::vector workspace.
+using vo_ransac::kMaxN;
+using vo_ransac::Svd3;
+using vo_ransac::svd3;
 
-void jacobi_svd(const double* A, int m, int n, std::vector<double>& G, double* w, double* V, bool want_g = false) {
+void jacobi_svd(const double* A, int m, int n, std::vector<double>& G, double* w, double* V) {
   G.assign(A, A + (size_t)m * n);
-  double fro = 0;
-  for (size_t i = 0; i < (size_t)m * n; i++) fro += A[i] * A[i];
-  // a column whose norm has dropped to rounding level of the whole matrix is a null direction already;
-  // rotating it further only chases noise (this is what ends the sweeps for the 8 x 9 systems of RANSAC)
-  const double tiny = fro * 1e-30;
-  for (int i = 0; i < n; i++)
-    for (int j = 0; j < n; j++) V[i * n + j] = (i == j) ? 1.0 : 0.0;
-  for (int sweep = 0; sweep < 60; sweep++) {
-    bool rotated = false;
-    for (int p = 0; p < n - 1; p++) {
-      for (int q = p + 1; q < n; q++) {
-        double alpha = 0, beta = 0, gamma = 0;
-        for (int k = 0; k < m; k++) {
-          const double gp = G[(size_t)k * n + p], gq = G[(size_t)k * n + q];
-          alpha += gp * gp; beta += gq * gq; gamma += gp * gq;
-        }
-        if (alpha <= tiny || beta <= tiny || gamma * gamma <= 1e-30 * alpha * beta) continue;
-        rotated = true;
-        const double zeta = (beta - alpha) / (2.0 * gamma);
-        const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
-        const double c = 1.0 / std::sqrt(1.0 + t * t), s = c * t;
-        for (int k = 0; k < m; k++) {
-          const double gp = G[(size_t)k * n + p], gq = G[(size_t)k * n + q];
-          G[(size_t)k * n + p] = c * gp - s * gq;
-          G[(size_t)k * n + q] = s * gp + c * gq;
-        }
-        for (int k = 0; k < n; k++) {
-          const double vp = V[k * n + p], vq = V[k * n + q];
-          V[k * n + p] = c * vp - s * vq;
-          V[k * n + q] = s * vp + c * vq;
-        }
-      }
-    }
-    if (!rotated) break;
-  }
-  double nrm[kMaxN];
-  int order[kMaxN];
-  for (int j = 0; j < n; j++) {
-    double s = 0;
-    for (int k = 0; k < m; k++) s += G[(size_t)k * n + j] * G[(size_t)k * n + j];
-    nrm[j] = std::sqrt(s);
-    order[j] = j;
-  }
-  std::stable_sort(order, order + n, [&](int a, int b) { return nrm[a] > nrm[b]; });  // descending (src/matrix.cpp:759)
-  double V2[kMaxN * kMaxN];
-  for (int j = 0; j < n; j++) {
-    w[j] = nrm[order[j]];
-    for (int k = 0; k < n; k++) V2[k * n + j] = V[k * n + order[j]];
-  }
-  std::memcpy(V, V2, sizeof(double) * n * n);
-  if (want_g) {  // only the 3 x 3 callers need the left vectors
-    std::vector<double> G2(G.size());
-    for (int j = 0; j < n; j++)
-      for (int k = 0; k < m; k++) G2[(size_t)k * n + j] = G[(size_t)k * n + order[j]];
-    G.swap(G2);
-  }
-}
-
-struct Svd3 { double U[9], w[3], V[9]; };
-
-// 3x3 SVD with an orthogonal U even when the matrix has rank 2: u2 = u0 x u1.  (The reference's U comes
-// from Householder/Givens products and is orthogonal too; its sign of u2 is arbitrary, and so is ours.)
-Svd3 svd3(const double* A) {
-  Svd3 r;
-  std::vector<double> G;
-  jacobi_svd(A, 3, 3, G, r.w, r.V, true);
-  for (int j = 0; j < 2; j++) {
-    const double inv = r.w[j] > 0 ? 1.0 / r.w[j] : 0.0;
-    for (int k = 0; k < 3; k++) r.U[k * 3 + j] = G[k * 3 + j] * inv;
-  }
-  if (r.w[2] > 1e-9 * r.w[0]) {
-    for (int k = 0; k < 3; k++) r.U[k * 3 + 2] = G[k * 3 + 2] / r.w[2];
-  } else {
-    r.U[0 * 3 + 2] = r.U[1 * 3 + 0] * r.U[2 * 3 + 1] - r.U[2 * 3 + 0] * r.U[1 * 3 + 1];
-    r.U[1 * 3 + 2] = r.U[2 * 3 + 0] * r.U[0 * 3 + 1] - r.U[0 * 3 + 0] * r.U[2 * 3 + 1];
-    r.U[2 * 3 + 2] = r.U[0 * 3 + 0] * r.U[1 * 3 + 1] - r.U[1 * 3 + 0] * r.U[0 * 3 + 1];
-  }
-  return r;
+  vo_ransac::jacobi_svd_core(G.data(), m, n, w, V, false);
 }
 
 inline void mul3(const double* A, const double* B, double* C) {  // C = A*B, all 3x3 row-major
@@ -170,15 +93,8 @@ inline double det3(const double* A) {
   return A[0] * (A[4] * A[8] - A[5] * A[7]) - A[1] * (A[3] * A[8] - A[5] * A[6]) + A[2] * (A[3] * A[7] - A[4] * A[6]);
 }
 
-// U * diag(w0, w1, 0) * V^T : the rank-2 projection of src/viso_mono.cpp:271-274 and :93-97
-void rank2(const double* M, double* out) {
-  const Svd3 s = svd3(M);
-  for (int i = 0; i < 3; i++)
-    for (int j = 0; j < 3; j++)
-      out[i * 3 + j] = s.U[i * 3 + 0] * s.w[0] * s.V[j * 3 + 0] + s.U[i * 3 + 1] * s.w[1] * s.V[j * 3 + 1];
-}
-
-struct Pt { float u1p, v1p, u1c, v1c; };
+using vo_ransac::rank2;
+using vo_ransac::Pt;
 
 }  // namespace
 
@@ -224,14 +140,12 @@ bool normalize_points(std::vector<Pt>& p, double Tp[9], double Tc[9]) {
 // The null vector's sign is free; everything downstream (Sampson distance, U*diag*V^T of F) is even in it.
 void fundamental(const std::vector<Pt>& p, const int32_t* active, int n_active, double F[9], std::vector<double>& A,
                  std::vector<double>& G) {
-  A.resize((size_t)n_active * 9);
-  for (int i = 0; i < n_active; i++) {
-    const Pt& m = p[active[i]];
-    double* a = &A[(size_t)i * 9];
-    a[0] = m.u1c * m.u1p; a[1] = m.u1c * m.v1p; a[2] = m.u1c;
-    a[3] = m.v1c * m.u1p; a[4] = m.v1c * m.v1p; a[5] = m.v1c;
-    a[6] = m.u1p;         a[7] = m.v1p;         a[8] = 1;
+  if (n_active == 8) {  // a RANSAC sample: the fixed-size path the device kernel runs too
+    vo_ransac::fundamental8(p.data(), active, F);
+    return;
   }
+  A.resize((size_t)n_active * 9);
+  for (int i = 0; i < n_active; i++) vo_ransac::constraint_row(p[active[i]], &A[(size_t)i * 9]);
   double w[9], V[81];
   jacobi_svd(A.data(), n_active, 9, G, w, V);
   double F0[9];
@@ -242,17 +156,8 @@ void fundamental(const std::vector<Pt>& p, const int32_t* active, int n_active, 
 // src/viso_mono.cpp:277-325: Sampson distance below the threshold
 void sampson_inliers(const std::vector<Pt>& p, const double F[9], double thr, std::vector<int32_t>& out) {
   out.clear();
-  for (int32_t i = 0; i < (int32_t)p.size(); i++) {
-    const double u1 = p[i].u1p, v1 = p[i].v1p, u2 = p[i].u1c, v2 = p[i].v1c;
-    const double Fx1u = F[0] * u1 + F[1] * v1 + F[2];
-    const double Fx1v = F[3] * u1 + F[4] * v1 + F[5];
-    const double Fx1w = F[6] * u1 + F[7] * v1 + F[8];
-    const double Ftx2u = F[0] * u2 + F[3] * v2 + F[6];
-    const double Ftx2v = F[1] * u2 + F[4] * v2 + F[7];
-    const double x2tFx1 = u2 * Fx1u + v2 * Fx1v + Fx1w;
-    const double d = x2tFx1 * x2tFx1 / (Fx1u * Fx1u + Fx1v * Fx1v + Ftx2u * Ftx2u + Ftx2v * Ftx2v);
-    if (std::fabs(d) < thr) out.push_back(i);
-  }
+  for (int32_t i = 0; i < (int32_t)p.size(); i++)
+    if (vo_ransac::sampson_inlier(p[i], F, thr)) out.push_back(i);
 }
 
 // src/viso_mono.cpp:363-401: linear triangulation (null vector of the 4x4 system) and chirality count
@@ -332,13 +237,17 @@ void e_to_rt(const double E[9], const double K[9], const std::vector<Pt>& p, std
 namespace {
 
 // VisualOdometry::getRandomSample(N, 8): src/viso.cpp:86-106 (draw without replacement from a shrinking set)
-void draw_sample(GlibcRand& rng, int32_t N, std::vector<int32_t>& pool, int32_t out[8]) {
-  pool.resize(N);
-  for (int32_t i = 0; i < N; i++) pool[i] = i;
+// The reference erases the drawn element from a vector of all N indices; element j of what is left is the j-th smallest index
+// not drawn yet, which the (at most seven) earlier draws determine without touching N elements.
+void draw_sample(GlibcRand& rng, int32_t N, std::vector<int32_t>& /*pool*/, int32_t out[8]) {
+  int32_t taken[8];  // ascending
   for (int i = 0; i < 8; i++) {
-    const int32_t j = (int32_t)(rng.next() % (uint32_t)pool.size());
-    out[i] = pool[j];
-    pool.erase(pool.begin() + j);
+    int32_t v = (int32_t)(rng.next() % (uint32_t)(N - i));
+    int pos = 0;
+    while (pos < i && taken[pos] <= v) { v++; pos++; }
+    for (int k = i; k > pos; k--) taken[k] = taken[k - 1];
+    taken[pos] = v;
+    out[i] = v;
   }
 }
 
@@ -354,8 +263,10 @@ bool prepare_points(const vo_p_match* matches, int32_t N, std::vector<Pt>& raw, 
 
 // src/viso_mono.cpp:41-160 with the RANSAC sample sets given (8 indices per iteration, in the order the
 // reference draws them).  Stateless.  Returns false where the reference returns an empty vector.
+constexpr int kScoreHere = -2;  // best_k_in: score the hypotheses on the host (any value >= -1: the winner is already known)
+
 bool estimate_motion(const vo_p_match* matches, int32_t N, const vo_mono_params& prm, const int32_t* samples_in, int iters,
-                     int threads, std::vector<int32_t>& inliers, double tr[6]) {
+                     int threads, std::vector<int32_t>& inliers, double tr[6], int best_k_in = kScoreHere) {
   inliers.clear();
   std::vector<Pt> raw, p;
   const double K[9] = {prm.f, 0, prm.cu, 0, prm.f, prm.cv, 0, 0, 1};
@@ -367,7 +278,7 @@ bool estimate_motion(const vo_p_match* matches, int32_t N, const vo_mono_params&
 
   // ---- RANSAC: the hypotheses are independent, so they are scored by a pool of threads; the winner is
   //      the FIRST hypothesis with the largest inlier count == the sequential `if (curr.size() > best.size())`.
-  std::vector<int32_t> counts(iters, 0);
+  std::vector<int32_t> counts(best_k_in == kScoreHere ? iters : 0, 0);
   auto score = [&](int k0, int k1) {
     std::vector<double> A, G;
     std::vector<int32_t> inl;
@@ -379,7 +290,9 @@ bool estimate_motion(const vo_p_match* matches, int32_t N, const vo_mono_params&
     }
   };
   const int nt = std::max(1, std::min(eg->threads, iters / 64 + 1));
-  if (nt == 1) {
+  if (best_k_in != kScoreHere) {
+    // scored elsewhere (vo_ransac.cu runs the same arithmetic, one GPU thread per hypothesis)
+  } else if (nt == 1) {
     score(0, iters);
   } else {
     std::vector<std::thread> th;
@@ -387,8 +300,10 @@ bool estimate_motion(const vo_p_match* matches, int32_t N, const vo_mono_params&
     for (auto& t : th) t.join();
   }
   int best_k = -1, best_n = 0;
-  for (int k = 0; k < iters; k++)
-    if (counts[k] > best_n) { best_n = counts[k]; best_k = k; }
+  if (best_k_in != kScoreHere) best_k = (best_k_in < iters) ? best_k_in : -1;
+  else
+    for (int k = 0; k < iters; k++)
+      if (counts[k] > best_n) { best_n = counts[k]; best_k = k; }
   std::vector<double> A, G;
   double F[9];
   if (best_k >= 0) {
@@ -496,6 +411,32 @@ vo_status vo_estimate_motion_mono_samples(const vo_p_match* matches, int32_t n, 
     std::memcpy(inliers, inl.data(), sizeof(int32_t) * inl.size());
   }
   return VO_OK;
+}
+
+// As vo_estimate_motion_mono_samples with the RANSAC winner already known (vo_ransac_gpu_score): best_k = index of the first
+// hypothesis with the largest inlier count, -1 if none.
+vo_status vo_estimate_motion_mono_best(const vo_p_match* matches, int32_t n, const vo_mono_params* prm, const int32_t* samples,
+                                       int32_t n_iters, int32_t best_k, double tr_delta[6], int32_t* ok, int32_t* inliers,
+                                       int32_t inliers_cap, int32_t* n_inliers) {
+  if (!prm || !tr_delta || !ok || n < 0 || (n > 0 && !matches) || n_iters < 0 || (n_iters > 0 && !samples) || best_k < -1) return VO_ERR_INVALID;
+  std::vector<int32_t> inl;
+  *ok = estimate_motion(matches, n, *prm, samples, n_iters, 1, inl, tr_delta, best_k) ? 1 : 0;
+  if (n_inliers) *n_inliers = (int32_t)inl.size();
+  if (inliers) {
+    if (inliers_cap < (int32_t)inl.size()) return VO_ERR_CAPACITY;
+    std::memcpy(inliers, inl.data(), sizeof(int32_t) * inl.size());
+  }
+  return VO_OK;
+}
+
+// normalised match coordinates as estimateMotion uses them (src/viso_mono.cpp:187-240): out4n = n x {u1p, v1p, u1c, v1c};
+// returns 0 if the list never reaches RANSAC.  For vo_ransac.cu.
+int32_t vo_egomotion_prepare_points(const vo_p_match* matches, int32_t n, float* out4n) {
+  std::vector<Pt> raw, p;
+  double Tp[9], Tc[9];
+  if (!matches || !out4n || !prepare_points(matches, n, raw, p, Tp, Tc)) return 0;
+  std::memcpy(out4n, p.data(), sizeof(Pt) * (size_t)n);
+  return 1;
 }
 
 vo_status vo_estimate_motion_mono(vo_egomotion* eg, const vo_p_match* matches, int32_t n, const vo_mono_params* prm,

@@ -1170,6 +1170,12 @@ vo_status vo_slot_feature_count(vo_engine* e, int32_t slot, int32_t* n) {
 // instrumentation
 // ---------------------------------------------------------------------------------------------
 
+vo_status vo_engine_device(const vo_engine* e, int32_t* device) {
+  if (!e || !device) return fail(VO_ERR_INVALID, "null argument");
+  *device = e->device;
+  return VO_OK;
+}
+
 vo_status vo_launch_count(const vo_engine* e, int64_t* n) {
   if (!e || !n) return fail(VO_ERR_INVALID, "null argument");
   *n = e->launches;

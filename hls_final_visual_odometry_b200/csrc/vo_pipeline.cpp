@@ -21,6 +21,7 @@
 struct vo_pipeline {
   vo_engine* eng;
   vo_egomotion* ego;
+  vo_ransac_gpu* ransac;    // RANSAC hypotheses of the whole batch are scored on the GPU (null: on the host pool)
   vo_mono_params prm;
   vo_geometry geo;
   int32_t max_features;
@@ -34,8 +35,8 @@ struct vo_pipeline {
   int32_t* counts;          // pinned: 2 x max_pairs
   int32_t bucket_cap;
   std::vector<int32_t> n_raw, n_filtered;
-  double stage_s[6];        // wall seconds spent so far: extract+match (GPU), raw lists to host, removeOutliers (host pool),
-                            // host->bucket->host (GPU), RANSAC sample sets (host, serial), egomotion (host pool)
+  double stage_s[7];        // wall seconds spent so far: extract+match (GPU), raw lists to host, removeOutliers (host pool),
+                            // host->bucket->host (GPU), RANSAC sample sets (host, serial), RANSAC scoring (GPU), egomotion (host pool)
 };
 
 namespace {
@@ -107,6 +108,11 @@ vo_status vo_pipeline_create(vo_engine* e, const vo_mono_params* prm, int32_t ma
   p->raw = (vo_p_match*)a;
   p->bucketed = (vo_p_match*)b;
   p->counts = (int32_t*)c;
+  p->ransac = nullptr;
+  int32_t dev = 0;
+  if (prm->ransac_iters > 0 && vo_engine_device(e, &dev) == VO_OK &&
+      vo_ransac_gpu_create(dev, (int32_t)B, p->bucket_cap, prm->ransac_iters, &p->ransac) != VO_OK)
+    p->ransac = nullptr;  // (out of memory: the host pool scores instead, same results)
   *out = p;
   return VO_OK;
 }
@@ -117,6 +123,7 @@ void vo_pipeline_destroy(vo_pipeline* p) {
   vo_host_free(p->bucketed);
   vo_host_free(p->counts);
   vo_egomotion_destroy(p->ego);
+  vo_ransac_gpu_destroy(p->ransac);
   delete p;
 }
 
@@ -200,18 +207,31 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
       if (st != VO_OK) return st;
     }
     lap(4);
+    // ---- GPU: every hypothesis of every pair scored in one launch; the host keeps what follows the winner ----------
+    std::vector<int32_t> best_k;
+    if (p->ransac && iters > 0) {
+      best_k.assign(np, -1);
+      st = vo_ransac_gpu_score(p->ransac, np, p->bucketed, p->bucket_cap, p->counts + np, &p->prm, samples.data(), iters, drawn.data(),
+                               best_k.data(), nullptr);
+      if (st != VO_OK) return st;
+    }
+    lap(5);
     parallel_for(np, p->threads, [&](int i) {
       const int f = i + skip;
       const int32_t nb = p->counts[np + i];
       n_matches[f] = nb;
-      if (vo_estimate_motion_mono_samples(p->bucketed + (int64_t)i * p->bucket_cap, nb, &p->prm, samples.data() + (size_t)i * iters * 8,
-                                          drawn[i], 1, tr_delta + 6 * (size_t)f, &ok[f], nullptr, 0, &n_inliers[f]) != VO_OK)
+      const vo_p_match* lst = p->bucketed + (int64_t)i * p->bucket_cap;
+      const int32_t* smp = samples.data() + (size_t)i * iters * 8;
+      const vo_status s2 = best_k.empty()
+          ? vo_estimate_motion_mono_samples(lst, nb, &p->prm, smp, drawn[i], 1, tr_delta + 6 * (size_t)f, &ok[f], nullptr, 0, &n_inliers[f])
+          : vo_estimate_motion_mono_best(lst, nb, &p->prm, smp, drawn[i], best_k[i], tr_delta + 6 * (size_t)f, &ok[f], nullptr, 0, &n_inliers[f]);
+      if (s2 != VO_OK)
         bad = 1;
       if (matches_out && nb > 0)
         std::memcpy(matches_out + (int64_t)f * matches_stride, p->bucketed + (int64_t)i * p->bucket_cap, sizeof(vo_p_match) * (size_t)nb);
     });
     if (bad) return VO_ERR_INVALID;
-    lap(5);
+    lap(6);
   }
   p->frames_seen += n;
   p->last_slot = (first + n - 1) % S;
@@ -219,9 +239,9 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
 }
 
 // wall seconds per stage accumulated by vo_pipeline_process since creation (see vo_pipeline::stage_s)
-vo_status vo_pipeline_stage_seconds(const vo_pipeline* p, double* out6) {
-  if (!p || !out6) return VO_ERR_INVALID;
-  for (int i = 0; i < 6; i++) out6[i] = p->stage_s[i];
+vo_status vo_pipeline_stage_seconds(const vo_pipeline* p, double* out7) {
+  if (!p || !out7) return VO_ERR_INVALID;
+  for (int i = 0; i < 7; i++) out7[i] = p->stage_s[i];
   return VO_OK;
 }
 

@@ -103,6 +103,7 @@ typedef struct vo_engine vo_engine;
 vo_status vo_engine_create(const vo_config* cfg, int32_t device, void* stream, vo_engine** out);
 void      vo_engine_destroy(vo_engine* e);
 vo_status vo_engine_geometry(const vo_engine* e, vo_geometry* out);
+vo_status vo_engine_device(const vo_engine* e, int32_t* device);   /* the CUDA device ordinal the engine was created on */
 vo_status vo_engine_synchronize(vo_engine* e);
 /* Fences for the batch-level software pipeline (the double-buffered event graph of the reference's
  * FPGA host, hls_opencl/host/main2.cpp:449-518).  vo_fence_record(idx) marks "everything enqueued
@@ -283,6 +284,24 @@ vo_status vo_estimate_motion_mono_samples(const vo_p_match* matches, int32_t n, 
                                           const int32_t* samples, int32_t n_iters, int32_t threads,
                                           double tr_delta[6], int32_t* ok, int32_t* inliers,
                                           int32_t inliers_cap, int32_t* n_inliers);
+/* ... with the RANSAC winner known already (vo_ransac_gpu_score): best_k = index of the first hypothesis with the largest
+ * inlier count, -1 if no hypothesis has an inlier. */
+vo_status vo_estimate_motion_mono_best(const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
+                                       const int32_t* samples, int32_t n_iters, int32_t best_k, double tr_delta[6],
+                                       int32_t* ok, int32_t* inliers, int32_t inliers_cap, int32_t* n_inliers);
+/* RANSAC hypothesis scoring on the GPU (csrc/vo_ransac.cu): the 2000 hypotheses of estimateMotion's loop
+ * (src/viso_mono.cpp:63-77: fundamentalMatrix of an 8-point sample :242-275, getInlier :277-325) are independent; one
+ * thread each runs the host stage's own arithmetic (csrc/vo_ransac_core.h, no FMA contraction on either side), so the inlier
+ * counts and the winner -- the FIRST hypothesis with the largest count, as in the reference's sequential loop -- are the
+ * host's.  Sample sets still come from vo_egomotion_draw_samples, in frame order.
+ * lists + i*stride: counts[i] matches; samples + i*samples_stride*8: drawn[i] sample sets.  best_k[i] = -1 where no
+ * hypothesis has an inlier or the list never reaches RANSAC (drawn[i] == 0); best_count (optional) = the winner's count. */
+typedef struct vo_ransac_gpu vo_ransac_gpu;
+vo_status vo_ransac_gpu_create(int32_t device, int32_t max_lists, int32_t max_points, int32_t max_iters, vo_ransac_gpu** out);
+void      vo_ransac_gpu_destroy(vo_ransac_gpu* r);
+vo_status vo_ransac_gpu_score(vo_ransac_gpu* r, int32_t n_lists, const vo_p_match* lists, int64_t stride, const int32_t* counts,
+                              const vo_mono_params* prm, const int32_t* samples, int64_t samples_stride, const int32_t* drawn,
+                              int32_t* best_k, int32_t* best_count);
 /* VisualOdometryStereo::parameters, src/viso_stereo.h:31-43 + VisualOdometry::calibration, src/viso.h:56-64 */
 typedef struct vo_stereo_params {
   double f, cu, cv;          /* calibration */
@@ -325,8 +344,9 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
                               int32_t pitch_bytes, int32_t* ok, double* tr_delta, int32_t* n_matches,
                               int32_t* n_inliers, vo_p_match* matches_out, int64_t matches_stride);
 /* Wall seconds vo_pipeline_process has spent per stage since creation: {extract + match (GPU), raw lists to the host,
-   removeOutliers (host pool), host -> bucketing -> host (GPU), RANSAC sample sets (host, serial), egomotion (host pool)}. */
-vo_status vo_pipeline_stage_seconds(const vo_pipeline* p, double* out6);
+   removeOutliers (host pool), host -> bucketing -> host (GPU), RANSAC sample sets (host, serial), RANSAC scoring (GPU),
+   egomotion after the winner (host pool)}. */
+vo_status vo_pipeline_stage_seconds(const vo_pipeline* p, double* out7);
 
 /* ---------------------------------------------------------------------------------------- */
 /* instrumentation                                                                           */

@@ -98,3 +98,39 @@ def test_pipeline_on_pure_translation():
         raw, _ = orc.matching(feats[k - 1][0], feats[k - 1][1], feats[k][0], feats[k][1])
         want = orc.bucket_features(remove_outliers_host(raw), 2, 50.0, 50.0)
         assert matches_digest(ml[k]) == matches_digest(want)
+
+
+def test_gpu_ransac_scoring_equals_the_host_stage(corridor):
+    """vo_ransac_gpu_score runs the host stage's arithmetic (csrc/vo_ransac_core.h) one thread per hypothesis: the winner, its
+    inlier count, and therefore motion and inlier set are the host's, bit for bit (tolerance 0)."""
+    from hls_final_visual_odometry_b200 import Egomotion, RansacGpu
+    frames, _ = corridor
+    pipe = Pipeline(W, H, batch=len(frames), cam_height=KITTI_HEIGHT, pitch=0.0, **KITTI_CALIB)
+    lists = pipe.process(frames, want_matches=True)[4][1:]                # the bucketed lists of the five pairs
+    pipe.close()
+    rng = np.random.default_rng(3)
+    lists.append(lists[0][rng.permutation(len(lists[0]))[:40]])           # a short list
+    lists.append(lists[1][:9])                                            # never reaches RANSAC (< 10 matches)
+    junk = lists[2].copy()                                                # no geometry at all: low, tied counts -> first-wins rule
+    junk["u1c"] = rng.uniform(0, W, len(junk)).astype(np.float32); junk["v1c"] = rng.uniform(0, H, len(junk)).astype(np.float32)
+    lists.append(junk)
+    ego_a = Egomotion(height=KITTI_HEIGHT, pitch=0.0, ransac_iters=500, **KITTI_CALIB)
+    ego_b = Egomotion(height=KITTI_HEIGHT, pitch=0.0, ransac_iters=500, **KITTI_CALIB)
+    gpu = RansacGpu(max_lists=len(lists), max_points=max(len(l) for l in lists), max_iters=500)
+    try:
+        drawn = [ego_a.draw_samples(l) for l in lists]
+        for l in lists:
+            ego_b.draw_samples(l)                                          # both handles consumed the same stream
+        best_k, best_n = gpu.score(lists, ego_a.prm, [d[0] for d in drawn], [d[1] for d in drawn])
+        assert best_k[-2] == -1 and drawn[-2][1] == 0
+        for i, l in enumerate(lists):
+            tr_h, inl_h = ego_a.estimate_with_samples(l, drawn[i][0], drawn[i][1])
+            tr_g, inl_g = ego_a.estimate_with_samples(l, drawn[i][0], drawn[i][1], best_k=int(best_k[i]))
+            assert (tr_h is None) == (tr_g is None)
+            assert np.array_equal(inl_h, inl_g), f"list {i}: inlier sets differ"
+            if tr_h is not None:
+                assert np.array_equal(tr_h, tr_g), f"list {i}: motion differs"
+            if drawn[i][1] and len(inl_h):
+                assert best_n[i] == len(inl_h)
+    finally:
+        gpu.close(); ego_a.close(); ego_b.close()
