@@ -57,7 +57,7 @@ EXPORTS = [
     "vo_egomotion_create", "vo_egomotion_destroy", "vo_estimate_motion_mono", "vo_egomotion_inliers",
     "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
-    "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_engine_device", "vo_estimate_motion_mono_best",
+    "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_engine_device", "vo_egomotion_draw_samples_batch", "vo_estimate_motion_mono_best",
     "vo_ransac_gpu_create", "vo_ransac_gpu_destroy", "vo_ransac_gpu_score", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
 ]
 
@@ -140,6 +140,7 @@ def load_library() -> C.CDLL:
                                             vp, i32, C.POINTER(i32)],
         "vo_estimate_motion_mono_best": [vp, i32, C.POINTER(VoMonoParams), vp, i32, i32, C.POINTER(C.c_double), C.POINTER(i32),
                                          vp, i32, C.POINTER(i32)],
+        "vo_egomotion_draw_samples_batch": [vp, i32, vp, i64, vp, C.POINTER(VoMonoParams), vp, i64, vp, i32],
         "vo_ransac_gpu_create": [i32, i32, i32, i32, C.POINTER(vp)],
         "vo_ransac_gpu_destroy": [vp],
         "vo_ransac_gpu_score": [vp, i32, vp, i64, vp, C.POINTER(VoMonoParams), vp, i64, vp, vp, vp],
@@ -514,6 +515,24 @@ class Egomotion:
         if st != VO_OK:
             raise VoError(st, "vo_egomotion_draw_samples")
         return smp, n.value
+
+    def draw_samples_batch(self, lists, threads: int = 4):
+        """the same for consecutive lists in one call (vo_egomotion_draw_samples_batch) -> [(samples, iters), ...]"""
+        n = len(lists)
+        cap = max([len(l) for l in lists] + [1])
+        buf = np.zeros((n, cap), dtype=P_MATCH_DTYPE)
+        cnt = np.zeros(n, np.int32)
+        for i, l in enumerate(lists):
+            buf[i, : len(l)] = l
+            cnt[i] = len(l)
+        iters = max(self.prm.ransac_iters, 1)
+        smp = np.zeros((n, iters, 8), np.int32)
+        drawn = np.zeros(n, np.int32)
+        st = self.lib.vo_egomotion_draw_samples_batch(self.h, n, _ptr(buf), cap, _ptr(cnt), C.byref(self.prm), _ptr(smp), iters,
+                                                      _ptr(drawn), threads)
+        if st != VO_OK:
+            raise VoError(st, "vo_egomotion_draw_samples_batch")
+        return [(smp[i], int(drawn[i])) for i in range(n)]
 
     def estimate_with_samples(self, matches: np.ndarray, samples: np.ndarray, iters: int, best_k: int | None = None):
         """-> (tr or None, inlier indices).  best_k: the RANSAC winner if already known (RansacGpu.score), else scored here."""

@@ -22,6 +22,7 @@
 // centroid shift, the scaling and the products of the constraint matrix round to float exactly where
 // src/viso_mono.cpp does.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -396,6 +397,55 @@ vo_status vo_egomotion_draw_samples(vo_egomotion* eg, const vo_p_match* matches,
   std::vector<int32_t> pool;
   for (int k = 0; k < iters; k++) draw_sample(eg->rng, n, pool, samples + (size_t)k * 8);
   *n_iters = iters;
+  return VO_OK;
+}
+
+// The same for the n_lists consecutive frame pairs of a batch.  Only the generator itself is sequential (one add per value);
+// whether a list reaches RANSAC and what its sample sets look like are per-list work, done by `threads` host threads:
+//   1. per list, in parallel: does it reach RANSAC?  (then it consumes ransac_iters * 8 values, else none)
+//   2. serially: that many raw values of the stream, in frame order
+//   3. per list, in parallel: the sample sets from its slice of raw values
+// samples + i * samples_stride * 8 receives drawn[i] sets.  Results equal n_lists calls of vo_egomotion_draw_samples.
+vo_status vo_egomotion_draw_samples_batch(vo_egomotion* eg, int32_t n_lists, const vo_p_match* lists, int64_t stride,
+                                          const int32_t* counts, const vo_mono_params* prm, int32_t* samples,
+                                          int64_t samples_stride, int32_t* drawn, int32_t threads) {
+  if (!eg || !lists || !counts || !prm || !samples || !drawn || n_lists < 0) return VO_ERR_INVALID;
+  const int iters = std::max(0, prm->ransac_iters);
+  if (samples_stride < iters) return VO_ERR_INVALID;
+  auto parallel = [&](auto fn) {
+    const int nt = std::max(1, std::min(threads, (int)n_lists));
+    if (nt == 1) { for (int i = 0; i < n_lists; i++) fn(i); return; }
+    std::atomic<int> next(0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; t++)
+      th.emplace_back([&] { for (int i; (i = next.fetch_add(1)) < n_lists;) fn(i); });
+    for (auto& t : th) t.join();
+  };
+  parallel([&](int i) {
+    std::vector<Pt> raw, p;
+    double Tp[9], Tc[9];
+    drawn[i] = (counts[i] >= 0 && prepare_points(lists + (int64_t)i * stride, counts[i], raw, p, Tp, Tc)) ? iters : 0;
+  });
+  std::vector<size_t> first(n_lists + 1, 0);
+  for (int i = 0; i < n_lists; i++) first[i + 1] = first[i] + (size_t)drawn[i] * 8;
+  std::vector<uint32_t> raw_values(first[n_lists]);
+  for (uint32_t& v : raw_values) v = eg->rng.next();
+  parallel([&](int i) {
+    const uint32_t* rv = raw_values.data() + first[i];
+    int32_t* out = samples + (size_t)i * samples_stride * 8;
+    const int32_t N = counts[i];
+    for (int k = 0; k < drawn[i]; k++, rv += 8, out += 8) {
+      int32_t taken[8];  // ascending; see draw_sample
+      for (int j = 0; j < 8; j++) {
+        int32_t v = (int32_t)(rv[j] % (uint32_t)(N - j));
+        int pos = 0;
+        while (pos < j && taken[pos] <= v) { v++; pos++; }
+        for (int q = j; q > pos; q--) taken[q] = taken[q - 1];
+        taken[pos] = v;
+        out[j] = v;
+      }
+    }
+  });
   return VO_OK;
 }
 

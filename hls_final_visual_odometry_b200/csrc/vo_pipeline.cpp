@@ -199,13 +199,11 @@ vo_status vo_pipeline_process(vo_pipeline* p, int32_t n, const uint8_t* images, 
     // ---- host: sample sets in frame order, then egomotion of every pair in parallel -------------------------------
     const int iters = p->prm.ransac_iters > 0 ? p->prm.ransac_iters : 0;
     std::vector<int32_t> samples((size_t)np * iters * 8), drawn(np, 0);
-    for (int i = 0; i < np; i++) {
-      const int32_t nb = p->counts[np + i];
-      if (nb > p->bucket_cap) return VO_ERR_CAPACITY;
-      st = vo_egomotion_draw_samples(p->ego, p->bucketed + (int64_t)i * p->bucket_cap, nb, &p->prm,
-                                     samples.data() + (size_t)i * iters * 8, &drawn[i]);
-      if (st != VO_OK) return st;
-    }
+    for (int i = 0; i < np; i++)
+      if (p->counts[np + i] > p->bucket_cap) return VO_ERR_CAPACITY;
+    st = vo_egomotion_draw_samples_batch(p->ego, np, p->bucketed, p->bucket_cap, p->counts + np, &p->prm, samples.data(), iters,
+                                         drawn.data(), p->threads);
+    if (st != VO_OK) return st;
     lap(4);
     // ---- GPU: every hypothesis of every pair scored in one launch; the host keeps what follows the winner ----------
     std::vector<int32_t> best_k;

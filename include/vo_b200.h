@@ -280,6 +280,11 @@ vo_status vo_estimate_motion_mono(vo_egomotion* eg, const vo_p_match* matches, i
  * no random numbers either). */
 vo_status vo_egomotion_draw_samples(vo_egomotion* eg, const vo_p_match* matches, int32_t n,
                                     const vo_mono_params* prm, int32_t* samples, int32_t* n_iters);
+/* ... for the n_lists consecutive pairs of a batch at once (lists + i*stride, counts[i] matches; samples + i*samples_stride*8
+ * receives drawn[i] sets): only the generator runs serially, the per-list work runs on `threads` host threads. */
+vo_status vo_egomotion_draw_samples_batch(vo_egomotion* eg, int32_t n_lists, const vo_p_match* lists, int64_t stride,
+                                          const int32_t* counts, const vo_mono_params* prm, int32_t* samples,
+                                          int64_t samples_stride, int32_t* drawn, int32_t threads);
 vo_status vo_estimate_motion_mono_samples(const vo_p_match* matches, int32_t n, const vo_mono_params* prm,
                                           const int32_t* samples, int32_t n_iters, int32_t threads,
                                           double tr_delta[6], int32_t* ok, int32_t* inliers,

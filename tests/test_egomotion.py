@@ -100,3 +100,27 @@ def test_transformation_vector_to_matrix():
     Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
     assert np.allclose(M[:3, :3], Rx @ Ry @ Rz, atol=1e-15)   # src/viso.cpp:76-79 is Rx*Ry*Rz written out
     assert np.allclose(M[:3, 3], t) and np.allclose(M[3], [0, 0, 0, 1])
+
+
+def test_sample_sets_equal_the_references_erase_loop_and_batch_equals_sequential():
+    """getRandomSample (src/viso.cpp:86-106) erases each drawn element from a vector of all N indices; ours ranks the draw among
+    the indices not taken yet.  Checked against a literal restatement of the reference loop on libc's rand(), and the batched
+    drawing (vo_egomotion_draw_samples_batch) against list-by-list drawing, including lists that never reach RANSAC."""
+    lists = _lists(GOLD["cases"][0]["case"])[:3]
+    lists = [lists[0], lists[1][:9], lists[2], lists[0][:0], lists[1]]      # 9 matches / empty: no random numbers consumed
+    a, b = Egomotion(ransac_iters=300), Egomotion(ransac_iters=300)
+    seq = [a.draw_samples(m) for m in lists]
+    bat = b.draw_samples_batch(lists, threads=3)
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(0)
+    for (s1, n1), (s2, n2), m in zip(seq, bat, lists):
+        assert n1 == n2 == (300 if len(m) >= 10 else 0)
+        assert np.array_equal(s1[:n1], s2[:n2])
+        for k in range(n1):
+            pool = list(range(len(m)))
+            want = []
+            for _ in range(8):
+                j = libc.rand() % len(pool)
+                want.append(pool.pop(j))
+            assert list(s1[k]) == want
+    assert a.rand() == b.rand() == libc.rand()                                # all three streams stand at the same place
