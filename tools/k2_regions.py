@@ -24,7 +24,7 @@ ANCHORS = [  # (first line containing the string starts the region)
     ("pass 2: item claim", "// ================= pass 2"),
     ("good task: setup", "// ---------- filter task"),
     ("good task: flush (cooperative evaluation)", "auto flush = [&]() {"),
-    ("good task: row loop", "rows: the chunk around the task"),
+    ("good task: row loop", "// rows in the order own row (of the first lane), then the rest, each claimed"),
     ("good task: filter", "// 32 candidates (8 groups) at a time"),
     ("good task: hits (queue / own loop)", "bool own = true;  // every lane evaluates its own hits"),
     ("P item", "// ---------- P item"),
