@@ -584,8 +584,8 @@ def main():
     args = ap.parse_args()
     if args.config == 5:
         args.width, args.height = args.width or 2048, args.height or 1024
-        args.batch = args.batch or 64
-        args.pool = args.pool or 192
+        args.batch = args.batch or 256   # 32 new frames per sequence and step: at 8 GPUs a rank still has 32 pairs per launch
+        args.pool = args.pool or 512
         if args.steps == 200:
             args.steps = 40
     else:
