@@ -58,7 +58,7 @@ EXPORTS = [
     "vo_egomotion_rand", "vo_transformation_vector_to_matrix", "vo_egomotion_draw_samples",
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
     "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_engine_device", "vo_egomotion_draw_samples_batch", "vo_estimate_motion_mono_best",
-    "vo_ransac_gpu_create", "vo_ransac_gpu_destroy", "vo_ransac_gpu_score", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext",
+    "vo_ransac_gpu_create", "vo_ransac_gpu_destroy", "vo_ransac_gpu_score", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext", "vo_descriptor_signature",
 ]
 
 class VoStereoParams(C.Structure):  # vo_stereo_params: /root/reference/src/viso_stereo.h:31-43
@@ -98,6 +98,7 @@ def load_library() -> C.CDLL:
     sigs = {
         "vo_engine_create": [C.POINTER(VoConfig), i32, vp, C.POINTER(vp)],
         "vo_engine_destroy": [vp],
+        "vo_descriptor_signature": [vp, vp],
         "vo_engine_geometry": [vp, C.POINTER(VoGeometry)],
         "vo_engine_synchronize": [vp],
         "vo_compute_features": [vp, vp, i32, vp, vp, i32],

@@ -477,6 +477,14 @@ extern "C" {
 
 const char* vo_last_error(void) { return g_err.c_str(); }
 const char* vo_version(void) { return "vo_b200 0.1 (sm_100a)"; }
+void vo_descriptor_signature(const uint8_t desc[32], uint32_t sig[2]) {
+  uint4 a, b;
+  memcpy(&a, desc, 16);
+  memcpy(&b, desc + 16, 16);
+  const uint2 q = vo::desc_q(a, b);
+  sig[0] = q.x;
+  sig[1] = q.y;
+}
 
 vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream, vo_engine** out) {
   if (!cfg_in || !out) return fail(VO_ERR_INVALID, "null argument");

@@ -112,6 +112,10 @@ vo_status vo_fence_record(vo_engine* e, int32_t idx);
 vo_status vo_fence_wait(vo_engine* e, int32_t idx);
 const char* vo_last_error(void);            /* thread-local text of the last failure */
 const char* vo_version(void);
+/* Diagnostic, host only: the 8-byte lower-bound signature K1 stores beside every 32-byte descriptor
+ * (src/myComputeFeature.cpp:11-55 defines the bytes) and K2 prunes with: sig[0] + sig[1] compared byte-wise (sum of the
+ * eight absolute differences) never exceeds the SAD of the two descriptors -- tests/test_host_logic.py checks exactly that. */
+void      vo_descriptor_signature(const uint8_t desc[32], uint32_t sig[2]);
 
 /* ---------------------------------------------------------------------------------------- */
 /* 1. operator level (stateless from the caller's point of view; host buffers in, host out)   */

@@ -75,3 +75,55 @@ def test_two_rank_gloo_reduction():
     for _, _, mx, sm in res:
         assert mx == [11.0, 4.0]  # max over ranks of the per-rank time
         assert sm == [8.0]        # every sequence owned exactly once
+
+
+# sample k of the 32-byte descriptor (src/myComputeFeature.cpp:11-55): bytes 2k (du) and 2k+1 (dv); the eight groups of the
+# lower-bound signature as csrc/vo_common.cuh documents them, in the byte order of the two signature words
+_SIG_GROUPS = [
+    [2 * k for k in (0, 1, 12, 13)], [2 * k for k in (4, 5, 14, 15)], [2 * k + 1 for k in (0, 2, 4, 6)],
+    [2 * k + 1 for k in (9, 11, 13, 15)],
+    [2 * k for k in (2, 6, 8, 10)], [2 * k for k in (3, 7, 9, 11)], [2 * k + 1 for k in (1, 3, 5, 7)],
+    [2 * k + 1 for k in (8, 10, 12, 14)],
+]
+
+
+def _sum_code(s):
+    return (min(s, 410) >> 4) + (min(max(s, 410), 610) - 410) + ((max(s, 610) - 610) >> 4)
+
+
+def test_descriptor_signature_is_a_partition_and_a_lower_bound_of_the_sad():
+    """K2 prunes a candidate when Q = sum over the 8 signature bytes of |difference| exceeds the origin's best SAD so far; that
+    is exact only if Q <= SAD for EVERY pair of descriptors (src/myMatch.cpp:103-109 takes the minimum SAD).  Checked on
+    random, extreme and near-equal descriptors, plus the documented group layout."""
+    import ctypes as C
+
+    from hls_final_visual_odometry_b200 import api
+
+    assert sorted(b for g in _SIG_GROUPS for b in g) == list(range(32)), "groups must partition the 32 bytes"
+    lib = api.load_library()
+    rng = np.random.default_rng(5)
+
+    def sig(d):
+        out = (C.c_uint32 * 2)()
+        buf = np.ascontiguousarray(d, dtype=np.uint8)
+        lib.vo_descriptor_signature(buf.ctypes.data_as(C.c_void_p), C.cast(out, C.c_void_p))
+        return np.frombuffer(np.array([out[0], out[1]], dtype="<u4").tobytes(), dtype=np.uint8).astype(np.int64)
+
+    descs = [rng.integers(0, 256, 32), rng.integers(100, 156, 32), np.zeros(32), np.full(32, 255), rng.integers(0, 2, 32) * 255]
+    for _ in range(300):
+        base = rng.integers(90, 166, 32)
+        descs.append(base)
+        descs.append(np.clip(base + rng.integers(-6, 7, 32), 0, 255))
+        descs.append(rng.integers(0, 256, 32))
+    descs = [np.asarray(d, dtype=np.int64) for d in descs]
+    sigs = [sig(d) for d in descs]
+    for d, s in zip(descs[:40], sigs[:40]):
+        want = [_sum_code(int(d[g].sum())) for g in _SIG_GROUPS]
+        assert s.tolist() == want
+    D = np.stack(descs)
+    S = np.stack(sigs)
+    sad = np.abs(D[:, None, :] - D[None, :, :]).sum(-1)
+    q = np.abs(S[:, None, :] - S[None, :, :]).sum(-1)
+    q0 = np.abs(S[:, None, :4] - S[None, :, :4]).sum(-1)
+    assert (q <= sad).all() and (q0 <= q).all()
+    assert (np.diag(q) == 0).all()

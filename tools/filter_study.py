@@ -31,10 +31,12 @@ def sum_code(s):
 
 
 def signature(desc):
-    """desc (n, 32) u8 -> (n, 8) codes: groups {du of samples 4h..4h+3}, {dv of samples 4h..4h+3}"""
-    d = desc.reshape(-1, 4, 4, 2).astype(np.int64)  # (n, h, sample, du/dv)
-    s = d.sum(axis=2)  # (n, h, 2)
-    return sum_code(s.reshape(-1, 8))
+    """desc (n, 32) u8 -> (n, 8) codes, the groups of csrc/vo_common.cuh desc_q (sample k: du = byte 2k, dv = byte 2k+1)"""
+    d = desc.astype(np.int64)
+    du, dv = d[:, 0::2], d[:, 1::2]
+    g = [du[:, [0, 1, 12, 13]], du[:, [4, 5, 14, 15]], dv[:, [0, 2, 4, 6]], dv[:, [9, 11, 13, 15]],
+         du[:, [2, 6, 8, 10]], du[:, [3, 7, 9, 11]], dv[:, [1, 3, 5, 7]], dv[:, [8, 10, 12, 14]]]
+    return sum_code(np.stack([x.sum(axis=1) for x in g], axis=1))
 
 
 def flat(max2, num):
