@@ -46,7 +46,7 @@ namespace vo {
 #define K2CHECK(cond)
 #endif
 #ifdef VO_K2_STATS
-__device__ unsigned long long g_k2_stats[8];
+__device__ unsigned long long g_k2_stats[16];
 #define K2STAT(i, n) atomicAdd(&g_k2_stats[i], (unsigned long long)(n))
 #else
 #define K2STAT(i, n)
@@ -684,6 +684,10 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                   while (qn >= 32) flush();
                 }
               }
+#ifdef VO_K2_STATS
+              if (!kindM) { const int n = __popc(hit); const int mx = __reduce_max_sync(FULL, n), tot = __reduce_add_sync(FULL, n);
+                if (lane == 0) { K2STAT(8, 1); K2STAT(9, tot); K2STAT(10, mx); K2STAT(11, mx > 0 ? 1 : 0); K2STAT(12, two ? 1 : 0); } }
+#endif
               if (own) {
                 while (hit != 0u) {
                   const int z = __clz((int)hit);
@@ -695,6 +699,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             }
             if (valid && bestk < *(volatile uint32_t*)&S.gkey[cc][ei]) atomicMin(&S.gkey[cc][ei], bestk);  // publish
           }
+          if (lane == 0) K2STAT(13, 1);
           if (kindM) {
             __syncwarp();
             while (qn > 0) flush();
@@ -1194,8 +1199,8 @@ cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* qua
 #ifdef VO_K2_STATS
 extern "C" int vo_debug_k2_stats(unsigned long long* out) {
   cudaDeviceSynchronize();
-  cudaError_t e = cudaMemcpyFromSymbol(out, vo::g_k2_stats, sizeof(unsigned long long) * 8);
-  unsigned long long z[8] = {0};
+  cudaError_t e = cudaMemcpyFromSymbol(out, vo::g_k2_stats, sizeof(unsigned long long) * 16);
+  unsigned long long z[16] = {0};
   cudaMemcpyToSymbol(vo::g_k2_stats, z, sizeof(z));
   return (int)e;
 }

@@ -34,7 +34,7 @@ for amp in amps:
         want, _ = orc.matching(*f0, *f1)
         assert matches_digest(eng.batch_get_matches(0, 0)) == matches_digest(want), "parity lost"
     eng.profile_enable(True)
-    for _ in range(5):
+    for _ in range(int(os.environ.get("VO_PROBE_ITERS", "5"))):
         eng.batch_extract_host(0, seq)
         eng.batch_match(prev, prev + 1, 2, 50.0, 50.0)
     eng.synchronize()
