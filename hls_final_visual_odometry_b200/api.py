@@ -59,6 +59,7 @@ EXPORTS = [
     "vo_estimate_motion_mono_samples", "vo_batch_bucket_host", "vo_pipeline_create", "vo_pipeline_destroy",
     "vo_pipeline_process", "vo_pipeline_stage_seconds", "vo_engine_device", "vo_egomotion_draw_samples_batch", "vo_estimate_motion_mono_best",
     "vo_ransac_gpu_create", "vo_ransac_gpu_destroy", "vo_ransac_gpu_score", "vo_estimate_motion_stereo", "vo_batch_match_quad", "vo_batch_refine", "vo_refine_matches", "vo_profile_read_ext", "vo_descriptor_signature",
+    "vo_bucket_matches_noalloc",
 ]
 
 class VoStereoParams(C.Structure):  # vo_stereo_params: /root/reference/src/viso_stereo.h:31-43
@@ -106,6 +107,7 @@ def load_library() -> C.CDLL:
         "vo_matching_iter": [vp, vp, vp, vp, vp, i32, vp, i32, C.POINTER(i32), i32],
         "vo_remove_outliers_bucket": [vp, vp, C.POINTER(i32), vp, i32, C.POINTER(i32)],
         "vo_bucket_matches": [vp, vp, i32, i32, f32, f32, vp, i32, C.POINTER(i32)],
+        "vo_bucket_matches_noalloc": [vp, vp, i32, i32, f32, f32, vp, i32, vp],
         "vo_push_back": [vp, vp, vp, C.POINTER(i32), i32],
         "vo_match_features": [vp, i32],
         "vo_bucket_features": [vp, i32, f32, f32],
@@ -275,6 +277,11 @@ class Engine:
         self._check(self.lib.vo_bucket_matches(self.h, _ptr(matches) if len(matches) else None, len(matches),
                                                max_features, bw, bh, _ptr(out), len(out), C.byref(n)))
         return out[: n.value].copy()
+
+    def bucket_matches_noalloc(self, d_in: int, n_in: int, max_features, bw, bh, d_out: int, out_cap: int, d_result: int):
+        """vo_bucket_matches_noalloc: DEVICE addresses in, nothing allocated, asynchronous on the engine's stream."""
+        self._check(self.lib.vo_bucket_matches_noalloc(self.h, C.c_void_p(d_in), n_in, max_features, bw, bh,
+                                                       C.c_void_p(d_out), out_cap, C.c_void_p(d_result)))
 
     # ---- Matcher level -------------------------------------------------------------------
     def push_back(self, img: np.ndarray, replace: bool = False, img2=None):

@@ -206,4 +206,59 @@ cudaError_t launch_k4(const void* in, int64_t in_stride_matches, const int32_t* 
   return cudaGetLastError();
 }
 
+// ---- allocation-free variant (vo_bucket_matches_noalloc; no counterpart in the reference)
+// ----------------------------------------------------------------------------------------------------
+// Same kernel, but its per-list scratch (histogram | counts | LFSR offsets | output offsets | traced ranks) lives in a
+// file-scope device array instead of engine-owned cudaMalloc memory, so a caller that may not allocate (CUDA graph capture,
+// a serving loop, a harness that forbids it) can bucket a device-resident list.  Every GPU that loads the library holds the
+// array until exit (kNoAllocInts * 4 bytes = 624 KB).  ONE array per device: calls that overlap on the GPU race, and the
+// array keeps the previous call's contents -- the kernel zeroes the histogram it uses and writes every count / offset /
+// rank entry before reading it; the header word (list length) is rewritten by k4_noalloc_prepare on every call.
+constexpr int kNoAllocMaxMatches = 32768;  // stated limit of the entry point (a 1241x376 pair has ~17 k raw matches)
+constexpr int kNoAllocNbMax = 4096;        // buckets per list, as the engine's own scratch
+constexpr int kNoAllocQCap = 16384;        // kept matches per list, as the engine's own scratch
+constexpr int kNoAllocHdr = 64;            // header ints in front of the kernel's scratch (256 bytes: keeps its alignment)
+constexpr int64_t kNoAllocInts = kNoAllocHdr + (int64_t)kNoAllocNbMax * 32 + kNoAllocNbMax + 2 * (int64_t)(kNoAllocNbMax + 1) + kNoAllocQCap;
+static __device__ __align__(256) int32_t g_k4_noalloc[kNoAllocInts];
+
+// In host code `g_k4_noalloc` is only a stand-in for the symbol, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, once per device with that device current (init_k4_device, called by vo_engine_create)
+constexpr int kMaxDevices = 64;
+static int32_t* g_k4_noalloc_dev[kMaxDevices];
+
+// header word 0 = list length (k4_bucket reads it through its n_in pointer); result = {n_out, status} starts at zero
+__global__ void k4_noalloc_prepare(int32_t* __restrict__ hdr, int32_t n_in, int32_t* __restrict__ result) {
+  if (threadIdx.x == 0) { hdr[0] = n_in; result[0] = 0; result[1] = 0; }
+}
+
+cudaError_t init_k4_noalloc_device() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  int32_t* ptr = nullptr;
+  e = cudaGetSymbolAddress((void**)&ptr, g_k4_noalloc);
+  if (e != cudaSuccess) return e;
+  g_k4_noalloc_dev[dev] = ptr;
+  return cudaSuccess;
+}
+
+int k4_noalloc_max_matches() { return kNoAllocMaxMatches; }
+
+// in / out / result are DEVICE pointers of the caller; two launches on `st`, nothing else (no allocation, no synchronisation)
+cudaError_t launch_k4_noalloc(int device, const void* in, int32_t n_in, int32_t max_features, float bw, float bh,
+                              const uint32_t* lfsr, int32_t lfsr_len, void* out, int32_t out_cap, int32_t* result,
+                              cudaStream_t st) {
+  if (device < 0 || device >= kMaxDevices || g_k4_noalloc_dev[device] == nullptr) return cudaErrorNotReady;
+  int32_t* base = g_k4_noalloc_dev[device];
+  k4_noalloc_prepare<<<1, 32, 0, st>>>(base, n_in, result);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const int smem = K4_SMEM_BUCKETS * 32 * (int)sizeof(int32_t);
+  k4_bucket<<<1, K4_THREADS, smem, st>>>((const uint4*)in, (int64_t)n_in, base, max_features, bw, bh, lfsr, lfsr_len,
+                                         base + kNoAllocHdr, kNoAllocInts - kNoAllocHdr, kNoAllocNbMax, kNoAllocQCap,
+                                         (uint4*)out, (int64_t)out_cap, out_cap, result, result + 1, nullptr);
+  return cudaGetLastError();
+}
+
 }  // namespace vo

@@ -20,6 +20,11 @@ void k1_box(int bin_w, int bin_h, int* tw, int* th);
 cudaError_t init_k1_device();
 cudaError_t init_k2_device();
 cudaError_t init_k4_device();
+cudaError_t init_k4_noalloc_device();
+int k4_noalloc_max_matches();
+cudaError_t launch_k4_noalloc(int device, const void* in, int32_t n_in, int32_t max_features, float bw, float bh,
+                              const uint32_t* lfsr, int32_t lfsr_len, void* out, int32_t out_cap, int32_t* result,
+                              cudaStream_t st);
 cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
                       cudaStream_t st);
 cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t* max2, int32_t* max2_num,
@@ -518,6 +523,7 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   CU_TRY(vo::init_k1_device());
   CU_TRY(vo::init_k2_device());
   CU_TRY(vo::init_k4_device());
+  CU_TRY(vo::init_k4_noalloc_device());  // address of the static scratch of vo_bucket_matches_noalloc on this device
 
   vo_engine* e = new (std::nothrow) vo_engine();
   if (!e) return fail(VO_ERR_INVALID, "out of host memory");
@@ -806,6 +812,25 @@ vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, in
                            cudaMemcpyDeviceToHost, e->stream));
     CU_TRY(cudaStreamSynchronize(e->stream));
   }
+  return VO_OK;
+}
+
+// No counterpart in the reference: vo_bucket_matches for callers that may not
+// allocate.  Device-resident list in, device-resident list out, K4's scratch in a static device array of the library
+// (csrc/vo_bucket.cu); two kernel launches on the engine's stream, no cudaMalloc / cudaFree / synchronisation in here.
+vo_status vo_bucket_matches_noalloc(vo_engine* e, const vo_p_match* d_in, int32_t n_in, int32_t max_features, float bucket_w,
+                                    float bucket_h, vo_p_match* d_out, int32_t out_cap, int32_t* d_result) {
+  if (!e || !d_out || !d_result || (!d_in && n_in > 0) || n_in < 0 || out_cap < 0) return fail(VO_ERR_INVALID, "null argument");
+  if (!(bucket_w > 0.f) || !(bucket_h > 0.f)) return fail(VO_ERR_INVALID, "bucket size must be positive");
+  const int limit = vo::k4_noalloc_max_matches() < kLfsrLen ? vo::k4_noalloc_max_matches() : kLfsrLen;
+  if (n_in > limit)
+    return fail(VO_ERR_CAPACITY, "%d matches > %d, the limit of the static scratch of vo_bucket_matches_noalloc", n_in, limit);
+  if (((uintptr_t)d_in | (uintptr_t)d_out) & 15u) return fail(VO_ERR_INVALID, "d_in and d_out must be 16-byte aligned");
+  if (((uintptr_t)d_result) & 3u) return fail(VO_ERR_INVALID, "d_result must be 4-byte aligned");
+  CU_TRY(cudaSetDevice(e->device));
+  CU_TRY(vo::launch_k4_noalloc(e->device, d_in, n_in, max_features, bucket_w, bucket_h, e->d_lfsr, kLfsrLen, d_out, out_cap,
+                               d_result, e->stream));
+  e->launches += 2;
   return VO_OK;
 }
 

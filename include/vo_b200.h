@@ -149,6 +149,21 @@ vo_status vo_bucket_matches(vo_engine* e, const vo_p_match* in, int32_t n_in, in
                             float bucket_w, float bucket_h, vo_p_match* out, int32_t out_cap,
                             int32_t* n_out);
 
+/* NO COUNTERPART IN THE REFERENCE.  vo_bucket_matches for callers that may not
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the same bucketing kernel,
+ * with its scratch in a static device array of the library (624 KB, held by every GPU that loads the library until exit)
+ * instead of engine-owned allocations.  The call allocates nothing, copies nothing and does not synchronise: it enqueues two
+ * kernels on the engine's stream; read the results after vo_engine_synchronize (or your own stream ordering).
+ *   d_in      DEVICE pointer, n_in records of 48 bytes, 16-byte aligned; LIMIT: n_in <= 32768, more -> VO_ERR_CAPACITY
+ *   d_out     DEVICE pointer, room for out_cap records, 16-byte aligned, must not overlap d_in
+ *   d_result  DEVICE pointer to two int32: {number of bucketed matches, status}; status 0 = ok, 2 = more than 4096 buckets,
+ *             3 = more than min(out_cap, 16384) matches kept (then the count is 0)
+ * Same results as vo_bucket_matches on the same list.  Every call on a device shares the one array: calls that OVERLAP on the
+ * GPU (two engines / streams on one device) race -- serialise them.  Nothing has to be cleared between calls. */
+vo_status vo_bucket_matches_noalloc(vo_engine* e, const vo_p_match* d_in, int32_t n_in, int32_t max_features,
+                                    float bucket_w, float bucket_h, vo_p_match* d_out, int32_t out_cap,
+                                    int32_t* d_result);
+
 /* The reference's FPGA operator signatures, 1:1, for a host that drives the three kernels directly
  * (hls_opencl/host/main2.cpp:429-444,477-504):
  *   myMatching(m1p, m1c, n1p, n1c, p_matched, p_matched_num, iter)     hls_opencl/kernel/myMatch.hpp:51-57
