@@ -49,7 +49,7 @@ struct __align__(128) K1SmemT {
   uint16_t duv[T::OH * T::OW];  // du | dv<<8
   uint16_t f1[T::OH * T::OW];   // blob response + kFBias
   uint16_t f2[T::OH * T::OW];   // checkerboard response + kFBias
-  int32_t warp_tot[K1_WARPS][4];
+  __align__(16) int32_t warp_tot[K1_WARPS][4];
   uint32_t work[4][T::NBX * T::NBY];  // per class, in list order: ox | oy<<8 | twin rank<<16 | twin class<<30 | has twin<<31
 };
 
@@ -66,8 +66,11 @@ __device__ __forceinline__ uint32_t sobel_u8x2(uint32_t x) {
   return ((x + neg * 127u) >> 7) & 0x01FF01FFu;
 }
 
+#ifndef VO_K1_MIN_CTAS
+#define VO_K1_MIN_CTAS 4
+#endif
 template <class T>
-__global__ void __launch_bounds__(K1_THREADS)
+__global__ void __launch_bounds__(K1_THREADS, VO_K1_MIN_CTAS)
 k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int first_slot, int z_base) {
   constexpr int BW = T::BW, BH = T::BH, TW = T::TW, TH = T::TH, OW = T::OW, OH = T::OH, NBX = T::NBX, NBY = T::NBY;
   constexpr int kColPairs = T::kColPairs, kStrips = T::kStrips;
@@ -163,30 +166,42 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
 #pragma unroll
     for (int pl = 0; pl < 2; pl++) {
       const uint16_t* f = pl ? s.f2 : s.f1;  // value + kFBias
-      int mn = 65535, mx = -1, pmn = 0, pmx = 0;
+      // strict < / >: the first extremum in raster order wins (:199-224).  The raster index rides in the low four bits of a
+      // key (value * 16 + idx for the minimum, value * 16 + 15 - idx for the maximum: ties resolve to the smallest idx), so
+      // the scan is nine multiply-adds and eight min / max per extremum instead of compare-and-select pairs
+      int kmn = 0x7FFFFFFF, kmx = -1;
 #pragma unroll
       for (int dy = 0; dy < 3; dy++)
 #pragma unroll
         for (int dx = 0; dx < 3; dx++) {
           const int v = f[(oy0 + dy) * OW + ox0 + dx];
-          const int pp = (ox0 + dx) | ((oy0 + dy) << 8);
-          if (v < mn) { mn = v; pmn = pp; }   // strict: first in raster order wins (:199-224)
-          if (v > mx) { mx = v; pmx = pp; }
+          kmn = min(kmn, v * 16 + (dy * 3 + dx));
+          kmx = max(kmx, v * 16 + (15 - (dy * 3 + dx)));
         }
+      const int mn = kmn >> 4, mx = kmx >> 4;
+      const int imn = kmn & 15, imx = 15 - (kmx & 15);
+      const int ymn = (imn * 11) >> 5, ymx = (imx * 11) >> 5;  // idx / 3 for idx in 0..8
+      const int pmn = (ox0 + imn - 3 * ymn) | ((oy0 + ymn) << 8), pmx = (ox0 + imx - 3 * ymx) | ((oy0 + ymx) << 8);
       bool vmn = mn <= (int)kFBias - g.tau, vmx = mx >= (int)kFBias + g.tau;
+      // 5x5 validity (:226-260): no neighbour strictly below the minimum / above the maximum, i.e. the extremum of the 5x5
+      // window around it (which contains it) equals it
       if (vmn) {
-        const int cx = pmn & 255, cy = pmn >> 8;
+        const uint16_t* w = f + ((pmn >> 8) - 2) * OW + (pmn & 255) - 2;
+        int m = 65535;
 #pragma unroll
-        for (int ky = -2; ky <= 2; ky++)
+        for (int ky = 0; ky < 5; ky++)
 #pragma unroll
-          for (int kx = -2; kx <= 2; kx++) vmn &= !(f[(cy + ky) * OW + cx + kx] < mn);
+          for (int kx = 0; kx < 5; kx++) m = min(m, (int)w[ky * OW + kx]);
+        vmn = m >= mn;
       }
       if (vmx) {
-        const int cx = pmx & 255, cy = pmx >> 8;
+        const uint16_t* w = f + ((pmx >> 8) - 2) * OW + (pmx & 255) - 2;
+        int m = 0;
 #pragma unroll
-        for (int ky = -2; ky <= 2; ky++)
+        for (int ky = 0; ky < 5; ky++)
 #pragma unroll
-          for (int kx = -2; kx <= 2; kx++) vmx &= !(f[(cy + ky) * OW + cx + kx] > mx);
+          for (int kx = 0; kx < 5; kx++) m = max(m, (int)w[ky * OW + kx]);
+        vmx = m <= mx;
       }
       flag[2 * pl] = vmn; pos[2 * pl] = pmn;
       flag[2 * pl + 1] = vmx; pos[2 * pl + 1] = pmx;
@@ -204,19 +219,22 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
     if (lane == 0) s.warp_tot[warp][c] = __popc(b);
   }
   __syncthreads();
-  int total[4] = {0, 0, 0, 0};
-#pragma unroll
-  for (int w = 0; w < K1_WARPS; w++)
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-      const int t = s.warp_tot[w][c];
-      if (w < warp) rank[c] += t;
-      total[c] += t;
-    }
+  // lane w holds warp w's four counts; two warp reductions per class give the list total and this warp's offset
+  // (r2t: every thread used to walk all 40 counts, 7.5 % of the kernel's instructions)
+  static_assert(K1_WARPS <= 32, "one lane per warp count");
+  const int4 wt = (lane < K1_WARPS) ? *reinterpret_cast<const int4*>(s.warp_tot[lane]) : make_int4(0, 0, 0, 0);
+  const bool before = lane < warp;
+  int total[4];
+  total[0] = __reduce_add_sync(0xFFFFFFFFu, wt.x); rank[0] += __reduce_add_sync(0xFFFFFFFFu, before ? wt.x : 0);
+  total[1] = __reduce_add_sync(0xFFFFFFFFu, wt.y); rank[1] += __reduce_add_sync(0xFFFFFFFFu, before ? wt.y : 0);
+  total[2] = __reduce_add_sync(0xFFFFFFFFu, wt.z); rank[2] += __reduce_add_sync(0xFFFFFFFFu, before ? wt.z : 0);
+  total[3] = __reduce_add_sync(0xFFFFFFFFu, wt.w); rank[3] += __reduce_add_sync(0xFFFFFFFFu, before ? wt.w : 0);
 
   const int bj_first = max(y0, 9);
   if (bj_first >= g.H - 9) return;  // no block row in this tile (grid is sized to avoid it)
-  const int vd = dest_v_bin(g, bj_first);
+  // dest_v_bin(g, bj_first) with the tile's compile-time bin height (g.bin_h == BH: launch_k1 picks the instantiation by it)
+  const int vrow = bj_first / BH;
+  const int vd = (BH * (vrow + 1) - 3 <= g.j_last) ? vrow : g.v_rem;
   const int bin0 = (vd * g.U + ub) * 4;
   int32_t* cnt = fa.cnt + (int64_t)slot * fa.cnt_stride;
   if (tid < 4) cnt[bin0 + tid] = total[tid];
