@@ -34,7 +34,7 @@ class VoConfig(C.Structure):
                 ("nms_tau", C.c_int32), ("max_frames", C.c_int32), ("max_pairs", C.c_int32),
                 ("max_matches", C.c_int32), ("match_rows_per_cta", C.c_int32), ("match_exhaustive", C.c_int32),
                 ("match_threads", C.c_int32), ("stereo", C.c_int32), ("match_disp_tolerance", C.c_int32),
-                ("match_seed_good", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("match_seed_good", C.c_int32), ("match_radius_u", C.c_int32), ("match_radius_v", C.c_int32)]
 
 
 class VoGeometry(C.Structure):
@@ -187,7 +187,8 @@ class Engine:
     def __init__(self, width: int, height: int, max_frames: int = 2, max_pairs: int = 1, device: int = 0,
                  stream: int | None = None, max_matches: int = 0, match_rows_per_cta: int = 0, nms_tau: int = 0,
                  bin_w: int = 0, bin_h: int = 0, match_exhaustive: bool = False, match_threads: int = 0,
-                 stereo: bool = False, match_disp_tolerance: int = 0, match_seed_good: int = 0):
+                 stereo: bool = False, match_disp_tolerance: int = 0, match_seed_good: int = 0,
+                 match_radius_u: int = 0, match_radius_v: int = 0):
         self.lib = load_library()
         if stereo:
             max_frames = max(max_frames, 4)  # left and right prev/curr ring
@@ -195,7 +196,7 @@ class Engine:
                        max_frames=max_frames, max_pairs=max_pairs, max_matches=max_matches,
                        match_rows_per_cta=match_rows_per_cta, match_exhaustive=int(match_exhaustive),
                        match_threads=match_threads, stereo=int(stereo), match_disp_tolerance=match_disp_tolerance,
-                       match_seed_good=match_seed_good)
+                       match_seed_good=match_seed_good, match_radius_u=match_radius_u, match_radius_v=match_radius_v)
         h = C.c_void_p()
         self.h = None
         self._check(self.lib.vo_engine_create(C.byref(cfg), device, C.c_void_p(stream or 0), C.byref(h)))

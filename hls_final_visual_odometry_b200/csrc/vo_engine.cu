@@ -509,6 +509,8 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
     return fail(VO_ERR_UNSUPPORTED, "bin size %dx%d: the sm_100a tile kernel is built for 60x45 (the reference's, "
                 "src/size.h:10-11), 45x45, 60x30 and 90x30", cfg.bin_w, cfg.bin_h);
   if (cfg.nms_tau < 1 || cfg.nms_tau > 32767) return fail(VO_ERR_INVALID, "nms_tau out of range");
+  if (cfg.match_radius_u < 0 || cfg.match_radius_u > 4095 || cfg.match_radius_v < 0 || cfg.match_radius_v > 4095)
+    return fail(VO_ERR_INVALID, "match_radius %d x %d outside [1,4095] (0 = three bins)", cfg.match_radius_u, cfg.match_radius_v);
   if (cfg.max_frames < 2 || cfg.max_pairs < 1) return fail(VO_ERR_INVALID, "max_frames >= 2 and max_pairs >= 1 required");
 
   int ndev = 0;
@@ -540,7 +542,8 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   g.tau = cfg.nms_tau;
   g.j_last = 9 + 3 * ((g.H - 10 - 9) / 3);
   g.v_rem = g.H / g.bin_h;
-  g.rad_u = 3 * g.bin_w; g.rad_v = 3 * g.bin_h;
+  g.rad_u = cfg.match_radius_u > 0 ? cfg.match_radius_u : 3 * g.bin_w;  // SEARCH_RAD_U / SEARCH_RAD_V, src/size.h:14-15
+  g.rad_v = cfg.match_radius_v > 0 ? cfg.match_radius_v : 3 * g.bin_h;
   if (g.V > 64 || g.col_cap > 65535 || g.U < 2) {
     const int gu = g.U, gv = g.V;
     delete e;

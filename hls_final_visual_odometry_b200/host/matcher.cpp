@@ -24,6 +24,8 @@ bool Matcher::ensureEngine(int32_t width, int32_t height) {
   // a drop-in does the same unless the caller opts in to the (unpinned) live parameter
   cfg.nms_tau = live_nms_tau ? param.nms_tau : 0;
   cfg.bin_w = live_bin_w;
+  cfg.match_radius_u = live_rad_u;
+  cfg.match_radius_v = live_rad_v;
   cfg.bin_h = live_bin_h;
   cfg.stereo = stereo ? 1 : 0;
   cfg.match_disp_tolerance = param.match_disp_tolerance;

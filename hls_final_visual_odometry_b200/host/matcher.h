@@ -98,6 +98,12 @@ class Matcher {
   // search window stays 3 bins either way (SEARCH_RAD_U/V, src/size.h:14-15).  Call before the first pushBack.
   void useBinSize(int32_t bin_w, int32_t bin_h) { live_bin_w = bin_w; live_bin_h = bin_h; }
 
+  // Opt-in: a live search radius in pixels (`match_radius`, src/matcher.h:50: dead on the reference's executed path, where the
+  // |du| / |dv| window of find_match is SEARCH_RAD_U x SEARCH_RAD_V = 3 bins, src/size.h:14-15).  Bit-exact against the
+  // reference compiled with those numbers (tests/golden/golden.json "*_r<RU>x<RV>"); the bin range of the search stays
+  // 3 bins (src/myMatch.cpp:90-99).  0 = the reference's value.  Call before the first pushBack.
+  void useMatchRadius(int32_t rad_u, int32_t rad_v) { live_rad_u = rad_u; live_rad_v = rad_v; }
+
   // last C-ABI status (0 = ok) and message, for callers that want more than the reference's cerr line
   int lastStatus() const { return last_status; }
   const char* lastError() const;
@@ -112,6 +118,7 @@ class Matcher {
   int last_status;
   bool live_nms_tau = false;
   int32_t live_bin_w = 0, live_bin_h = 0;  // 0 = the reference's 60 x 45
+  int32_t live_rad_u = 0, live_rad_v = 0;  // 0 = the reference's three bins
   std::function<void(std::vector<Matcher::p_match>&)> outlier_filter;
 };
 

@@ -77,7 +77,13 @@ typedef struct vo_config {
   int32_t match_seed_good;    /* tuning: an origin whose starting bound (SAD of its seed or hint) is above this is matched by
                                  evaluating every candidate exactly instead of filtering (0 = library default 96).
                                  Results do not depend on it. */
-  int32_t reserved[2];
+  /* live search radius in pixels (Matcher::parameters::match_radius, src/matcher.h:50): SEARCH_RAD_U /
+   * SEARCH_RAD_V of src/size.h:14-15, the |du| / |dv| window of find_match (src/myMatch.cpp:84-87,101).  0 = the
+   * reference's 3*bin_w / 3*bin_h; else 1..4095.  The bin range of the search stays 3 bins (src/myMatch.cpp:90-99), as in
+   * the reference compiled with other numbers, against which the results are bit-exact (tests/golden/golden.json
+   * "*_r<RU>x<RV>"). */
+  int32_t match_radius_u;
+  int32_t match_radius_v;
 } vo_config;
 
 /* Derived geometry (what src/size.h spells as macros). */

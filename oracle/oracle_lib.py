@@ -18,7 +18,7 @@ _SO = os.path.join(_HERE, "liboracle.so")
 
 class Geom(C.Structure):
     _fields_ = [(n, C.c_int32) for n in
-                ("width", "height", "pitch", "bin_w", "bin_h", "u_bins", "v_bins", "cap", "tau")]
+                ("width", "height", "pitch", "bin_w", "bin_h", "u_bins", "v_bins", "cap", "tau", "rad_u", "rad_v")]
 
 
 def build(force: bool = False) -> str:
@@ -34,10 +34,14 @@ def _p(a):
 
 
 class Oracle:
-    def __init__(self, width: int, height: int, bin_w: int = 60, bin_h: int = 45):
+    def __init__(self, width: int, height: int, bin_w: int = 60, bin_h: int = 45, rad_u: int = 0, rad_v: int = 0):
         self.lib = C.CDLL(build())
         self.g = Geom()
         self.lib.vo_oracle_geom_init_bins(C.byref(self.g), width, height, width, bin_w, bin_h)
+        if rad_u > 0:  # SEARCH_RAD_U / SEARCH_RAD_V other than BIN_W*3 / BIN_H*3 (src/size.h:14-15): the live search radius
+            self.g.rad_u = rad_u
+        if rad_v > 0:
+            self.g.rad_v = rad_v
         self.W, self.H = width, height
         self.U, self.V, self.CAP = self.g.u_bins, self.g.v_bins, self.g.cap
         self.lib.vo_oracle_rand_number.restype = C.c_uint32

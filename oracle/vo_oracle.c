@@ -34,6 +34,7 @@ typedef struct vo_oracle_geom {
   int32_t u_bins, v_bins;
   int32_t cap;           /* stride of one (bin,class) list in records (MAX_FP_IN_BIN) */
   int32_t tau;           /* 50: src/myComputeFeature.cpp:157 */
+  int32_t rad_u, rad_v;  /* SEARCH_RAD_U / SEARCH_RAD_V: src/size.h:14-15 (BIN_W*3, BIN_H*3) */
 } vo_oracle_geom;
 
 typedef struct vo_oracle_match { /* == Matcher::p_match, src/matcher.h:89-104 */
@@ -53,6 +54,7 @@ void vo_oracle_geom_init_bins(vo_oracle_geom* g, int32_t width, int32_t height, 
   g->u_bins = last_i / g->bin_w + 1;
   g->v_bins = height / g->bin_h + 1;
   g->cap = (g->bin_w / 3) * (g->bin_h / 3);
+  g->rad_u = g->bin_w * 3; g->rad_v = g->bin_h * 3;  /* src/size.h:14-15 */
   g->tau = 50;
 }
 
@@ -256,7 +258,7 @@ static int32_t sad32(const uint8_t* a, const uint8_t* b) {
  * candidate (outside the dead column), stats[2] += candidates range-tested. */
 static void match_direction(const vo_oracle_geom* g, col_list* from, const col_list* to, int64_t* stats, int32_t rad_v) {
   const int32_t U = g->u_bins, V = g->v_bins;
-  const int32_t rad_u = g->bin_w * 3;  /* src/size.h:14; rad_v = bin_h*3 (src/size.h:15) for flow edges */
+  const int32_t rad_u = g->rad_u;  /* SEARCH_RAD_U, src/size.h:14; rad_v = SEARCH_RAD_V (src/size.h:15) for flow edges */
   for (int32_t ub = 0; ub < U; ub++)
     for (int32_t c = 0; c < 4; c++) {
       col_list* L = &from[ub * 4 + c];
@@ -298,8 +300,8 @@ int32_t vo_oracle_matching(const vo_oracle_geom* g, const int32_t* m1p, const in
   col_list* prv = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
   build_columns(g, m1c, n1c, cur);
   build_columns(g, m1p, n1p, prv);
-  match_direction(g, cur, prv, stats, g->bin_h * 3);
-  match_direction(g, prv, cur, stats, g->bin_h * 3);
+  match_direction(g, cur, prv, stats, g->rad_v);
+  match_direction(g, prv, cur, stats, g->rad_v);
 
   uint8_t* taken = (uint8_t*)calloc((size_t)g->width * g->height, 1);  /* M[][] (:133) */
   int32_t n = 0, overflow = 0;
@@ -426,9 +428,9 @@ int32_t vo_oracle_quad_matching(const vo_oracle_geom* g, const int32_t* m1p, con
   col_list* c2 = (col_list*)calloc((size_t)U * 4, sizeof(col_list));
   build_columns(g, m1c, n1c, c1); build_columns(g, m1p, n1p, p1);
   build_columns(g, m2p, n2p, p2); build_columns(g, m2c, n2c, c2);
-  match_direction(g, c1, p1, stats, g->bin_h * 3);   /* flow   1c -> 1p */
+  match_direction(g, c1, p1, stats, g->rad_v);   /* flow   1c -> 1p */
   match_direction(g, p1, p2, stats, disp_tolerance); /* stereo 1p -> 2p */
-  match_direction(g, p2, c2, stats, g->bin_h * 3);   /* flow   2p -> 2c */
+  match_direction(g, p2, c2, stats, g->rad_v);   /* flow   2p -> 2c */
   match_direction(g, c2, c1, stats, disp_tolerance); /* stereo 2c -> 1c */
 
   uint8_t* taken = (uint8_t*)calloc((size_t)g->width * g->height, 1);

@@ -64,17 +64,26 @@ def pair_record(ref: RefLib, prev, curr, with_post=False):
 BIN_TAGS = ["1241x376_b45x45", "1024x284_b60x30", "1241x376_b90x30"]  # live bin size: the reference with other BIN_W / BIN_H
 
 
-def bin_geometries():
-    """geometries of the reference compiled with other bin sizes (oracle/build_ref.sh <W>x<H>_b<BW>x<BH>)"""
+# live search radius: the reference with other SEARCH_RAD_U / SEARCH_RAD_V (96x64: inside the three-bin range;
+# 40x150: the v window reaches past the bin range, which then limits it)
+RAD_TAGS = ["1241x376_r96x64", "1024x284_r40x150"]
+
+
+def bin_geometries(tags=None):
+    """geometries of the reference compiled with other bin sizes / search radii (oracle/build_ref.sh <W>x<H>[_b<BW>x<BH>][_r<RU>x<RV>])"""
     out = {}
-    for tag in BIN_TAGS:
+    for tag in (tags or BIN_TAGS):
         ref = RefLib(tag)
         g = {"W": ref.W, "H": ref.H, "U": ref.U, "V": ref.V, "bin_w": ref.BIN_W, "bin_h": ref.BIN_H, "cases": {}}
+        rad = (0, 0)
+        if "_r" in tag:
+            rad = tuple(int(x) for x in tag.split("_r")[1].split("_")[0].split("x"))
+            g["rad_u"], g["rad_v"] = rad
         seq = make_sequence(ref.W, ref.H, 3, seed=0)
         g["cases"]["textured_seed0_f01"] = pair_record(ref, seq[0], seq[1], with_post=True)
         g["cases"]["textured_seed0_f12"] = pair_record(ref, seq[1], seq[2], with_post=True)
         from oracle.oracle_lib import Oracle
-        orc = Oracle(ref.W, ref.H, ref.BIN_W, ref.BIN_H)
+        orc = Oracle(ref.W, ref.H, ref.BIN_W, ref.BIN_H, rad[0], rad[1])
         for name in ADVERSARIAL:
             a, b = cases.CASES[name](ref.W, ref.H, 0)
             fa, fb = orc.compute_features(a), orc.compute_features(b)
@@ -96,6 +105,14 @@ def main():
         out["geometries"].update(bin_geometries())
         json.dump(out, open(path, "w"), indent=1, sort_keys=True)
         return
+    if "--radius-only" in sys.argv:  # same for the search-radius geometries
+        path = os.path.join(HERE, "golden.json")
+        out = json.load(open(path))
+        for tag in RAD_TAGS:
+            out["geometries"].pop(tag, None)
+        out["geometries"].update(bin_geometries(RAD_TAGS))
+        json.dump(out, open(path, "w"), indent=1, sort_keys=True)
+        return
     out = {"about": "sha256 digests of outputs of the reference sources compiled in place (oracle/_ref)",
            "geometries": {}, "lfsr": {}, "filters": {}, "matcher_flow": {}, "outliers": {}}
     for tag in ["native", "1024x284", "500x150", "1241x376", "2048x1024"]:
@@ -113,6 +130,7 @@ def main():
         out["geometries"][tag] = g
         print(tag, "done", flush=True)
     out["geometries"].update(bin_geometries())
+    out["geometries"].update(bin_geometries(RAD_TAGS))
 
     ref = RefLib("native")
     x, seq_vals = 5, []

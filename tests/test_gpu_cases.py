@@ -63,6 +63,36 @@ def test_bin_sizes_vs_oracle(name, geo):
         eng.close()
 
 
+# live search radius: SEARCH_RAD_U x SEARCH_RAD_V other than three bins, incl. the cases the reference leaves
+# undefined, a radius of a few pixels and one beyond the three-bin range (which then limits the search, src/myMatch.cpp:90-99)
+@pytest.mark.parametrize("geo", [(1241, 376, 96, 64), (1024, 284, 40, 150), (2048, 1024, 30, 200), (640, 200, 300, 300), (1241, 376, 7, 5)],
+                         ids=lambda g: f"{g[0]}x{g[1]}_r{g[2]}x{g[3]}")
+@pytest.mark.parametrize("name", ["holes", "low_contrast", "dense", "periodic", "big_motion"])
+def test_search_radius_vs_oracle(name, geo):
+    w, h, ru, rv = geo
+    prev, curr = cases.CASES[name](w, h, 0)
+    orc = Oracle(w, h, 60, 45, ru, rv)
+    eng = Engine(w, h, max_frames=2, max_pairs=1, match_radius_u=ru, match_radius_v=rv)
+    try:
+        fp = orc.compute_features(prev)[:2]
+        fc = orc.compute_features(curr)[:2]
+        eng.batch_extract_host(0, np.stack([prev, curr]))
+        eng.batch_match([0], [1], max_features=2, bw=50.0, bh=50.0)
+        want, _ = orc.matching(fp[0], fp[1], fc[0], fc[1], cap=1 << 18)
+        assert_matches_equal(eng.batch_get_matches(0, 0), want, name)
+        assert_matches_equal(eng.batch_get_matches(0, 1), orc.bucket_features(want, 2, 50.0, 50.0), f"{name} bucketed")
+    finally:
+        eng.close()
+
+
+def test_search_radius_is_validated():
+    from hls_final_visual_odometry_b200.api import VoError
+    with pytest.raises(VoError):
+        Engine(640, 200, match_radius_u=5000)
+    with pytest.raises(VoError):
+        Engine(640, 200, match_radius_v=-1)
+
+
 def test_engines_on_two_devices_in_one_process():
     """the > 48 KB shared-memory opt-in of K1/K2/K4 is a per-device attribute: an engine on a second GPU of the same
     process must work like the first (round-1 bug: a process-wide `static bool attr_set`)"""
@@ -99,7 +129,8 @@ def test_cuda_matches_reference_golden(tag, name):
     geom = GOLD["geometries"][tag]
     rec = geom["cases"][name]
     prev, curr = _inputs(geom, name)
-    eng = Engine(geom["W"], geom["H"], max_frames=2, max_pairs=1, bin_w=geom.get("bin_w", 0), bin_h=geom.get("bin_h", 0))
+    eng = Engine(geom["W"], geom["H"], max_frames=2, max_pairs=1, bin_w=geom.get("bin_w", 0), bin_h=geom.get("bin_h", 0),
+                 match_radius_u=geom.get("rad_u", 0), match_radius_v=geom.get("rad_v", 0))
     try:
         eng.batch_extract_host(0, np.stack([prev, curr]))
         assert features_digest(*eng.slot_dump_features(0)) == rec["features_prev"]

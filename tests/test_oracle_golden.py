@@ -36,7 +36,7 @@ CASE_IDS = [(tag, name) for tag, g in GOLD["geometries"].items() for name in g["
 def test_oracle_matches_reference_golden(tag, name):
     geom = GOLD["geometries"][tag]
     rec = geom["cases"][name]
-    orc = Oracle(geom["W"], geom["H"], geom.get("bin_w", 60), geom.get("bin_h", 45))
+    orc = Oracle(geom["W"], geom["H"], geom.get("bin_w", 60), geom.get("bin_h", 45), geom.get("rad_u", 0), geom.get("rad_v", 0))
     assert (orc.U, orc.V) == (geom["U"], geom["V"])
     prev, curr = _inputs(geom, name)
     mp, npv, d0 = orc.compute_features(prev)
