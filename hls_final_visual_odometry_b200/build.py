@@ -70,12 +70,12 @@ def build_host(force: bool = False) -> str | None:
     if force or _stale(HOST_LIB, deps):
         subprocess.check_call([
             "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", *inc,
-            "-o", HOST_LIB, *srcs, "-L", _PKG, "-lvo_b200", "-Wl,-rpath,$ORIGIN",
+            "-o", HOST_LIB, *srcs, "-L", _PKG, "-lvo_b200", "-lz", "-Wl,-rpath,$ORIGIN",
         ])
     demo_src = os.path.join(HOST, "demo_main.cpp")
     if os.path.exists(demo_src) and (force or _stale(DEMO, deps + [demo_src, HOST_LIB])):
         subprocess.check_call([
-            "g++", "-O2", "-std=c++17", "-Wall", *inc, "-o", DEMO, demo_src, "-L", _PKG, "-lvo_host", "-lvo_b200",
+            "g++", "-O2", "-std=c++17", "-Wall", *inc, "-o", DEMO, demo_src, "-L", _PKG, "-lvo_host", "-lvo_b200", "-lz",
             "-Wl,-rpath,$ORIGIN",
         ])
     return HOST_LIB

@@ -278,6 +278,17 @@ def test_cpp_shim_demo(tmp_path):
         want.append(len(orc.bucket_features(remove_outliers_host(raw), 2, 50.0, 50.0)))
     assert counts == want
     assert "mean flow: -3 -1" in out.stdout
+    # I/O adapter of SURVEY.md row F4: the same frames as KITTI-style PNG files (image_0/%06d.png, mixed row filters), size
+    # taken from the files -- the demo must print exactly what it printed for the raw frames
+    from hls_final_visual_odometry_b200 import image_io
+    kitti = tmp_path / "kitti" / "image_0"
+    kitti.mkdir(parents=True)
+    rng = np.random.default_rng(0)
+    for f in range(n):
+        (kitti / f"{f:06d}.png").write_bytes(image_io.encode_png(seq[f], filters=rng.integers(0, 5, h)))
+    out_png = subprocess.run([build.DEMO, str(tmp_path / "kitti"), "0", "0", str(n)], capture_output=True, text=True, timeout=120)
+    assert out_png.returncode == 0, out_png.stderr
+    assert out_png.stdout == out.stdout
 
 
 def test_matcher_facade_matches_reference_golden():
