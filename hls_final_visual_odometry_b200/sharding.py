@@ -13,6 +13,20 @@ def assign_sequences(n_sequences: int, world: int, rank: int) -> list[int]:
     return [s for s in range(n_sequences) if s % world == rank]
 
 
+def split_frame_ranges(n_frames: int, world: int, rank: int) -> tuple[int, int]:
+    """Second way to shard: ONE sequence split into contiguous frame ranges.  Matching pair p
+    needs only frames (p-1, p), so rank r takes the pairs [a, b) of a balanced partition of 1..n_frames-1 and extracts
+    the frames [a-1, b): the boundary frame a-1 is extracted twice (by this rank and by the one before it), nothing is
+    exchanged.  Returns (first_frame, end_frame) with end exclusive; its pairs are first_frame+1 .. end_frame-1.  A rank
+    without pairs gets an empty range (first == end)."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError(f"bad rank {rank} of {world}")
+    n_pairs = max(n_frames - 1, 0)
+    a = 1 + n_pairs * rank // world
+    b = 1 + n_pairs * (rank + 1) // world
+    return (a - 1, b) if b > a else (a - 1, a - 1)
+
+
 def sequence_seed(sequence: int, base: int = 1) -> int:
     """Synthetic sequence s uses texture seed base + s (seeds 1..8 for the 8 sharded sequences)."""
     return base + sequence

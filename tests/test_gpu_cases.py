@@ -93,6 +93,30 @@ def test_search_radius_is_validated():
         Engine(640, 200, match_radius_v=-1)
 
 
+def test_one_sequence_split_into_frame_ranges_equals_the_unsplit_run():
+    """SURVEY.md section 8 row E, second half: contiguous frame ranges of ONE sequence with a one-frame overlap, each range on
+    its own engine (one per rank in tools/split_sequence.py; here three engines in one process) -- every pair's raw and
+    bucketed list is bit-identical to the single-engine run."""
+    import importlib.util
+    import os
+    from hls_final_visual_odometry_b200 import sharding
+    spec = importlib.util.spec_from_file_location("split_sequence", os.path.join(os.path.dirname(__file__), "..", "tools", "split_sequence.py"))
+    ss = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ss)
+    w, h, n = 640, 200, 23
+    seq = make_sequence(w, h, n, seed=2)
+    whole, _ = ss.run_range(seq, 0, n, batch=8)
+    assert sorted(whole) == list(range(1, n)) and all(v[0] > 100 for v in whole.values())
+    for world in (2, 3):
+        merged = {}
+        for r in range(world):
+            f0, f1 = sharding.split_frame_ranges(n, world, r)
+            part, _ = ss.run_range(seq, f0, f1, batch=8)
+            assert not (set(part) & set(merged))
+            merged.update(part)
+        assert merged == whole
+
+
 def test_engines_on_two_devices_in_one_process():
     """the > 48 KB shared-memory opt-in of K1/K2/K4 is a per-device attribute: an engine on a second GPU of the same
     process must work like the first (round-1 bug: a process-wide `static bool attr_set`)"""

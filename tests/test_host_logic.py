@@ -37,6 +37,25 @@ def test_assign_sequences_partition():
     assert sharding.sequence_seed(0) == 1 and sharding.sequence_seed(7) == 8
 
 
+def test_split_frame_ranges_partition_the_pairs_with_one_frame_of_overlap():
+    for n_frames in (0, 1, 2, 3, 7, 1000, 1001):
+        for world in (1, 2, 3, 4, 8):
+            pairs = []
+            for r in range(world):
+                f0, f1 = sharding.split_frame_ranges(n_frames, world, r)
+                assert 0 <= f0 <= f1 <= max(n_frames, f0)
+                mine = list(range(f0 + 1, f1))
+                if mine and pairs:
+                    assert f0 == pairs[-1]  # the previous rank's last frame is this rank's first: extracted twice
+                pairs += mine
+            assert pairs == list(range(1, n_frames))  # every pair exactly once, in order
+            sizes = [max(sharding.split_frame_ranges(n_frames, world, r)[1] - sharding.split_frame_ranges(n_frames, world, r)[0] - 1, 0)
+                     for r in range(world)]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        sharding.split_frame_ranges(10, 2, 2)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
