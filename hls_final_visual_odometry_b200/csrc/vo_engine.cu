@@ -32,7 +32,7 @@ cudaError_t launch_dump(const Geom& g, const FrameArrays& fa, int slot, int32_t*
 cudaError_t launch_load(const Geom& g, const FrameArrays& fa, int slot, const int32_t* max2, const int32_t* max2_num,
                         int cap_stride, cudaStream_t st);
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                      int rows_per_group, int prune, int threads, int seed_good, int split, cudaStream_t st);
+                      int rows_per_group, int prune, int threads, int seed_good, int split, int lean, cudaStream_t st);
 cudaError_t launch_k3_quad(const Geom& g, const FrameArrays& fa, const int4* quads, const int2* pairs, int n_items,
                            const uint32_t* best, uint8_t* flags, int32_t* list_cnt, uint32_t* qxy, void* out,
                            int64_t out_stride_matches, int32_t max_matches, int32_t* n_raw, int32_t* status,
@@ -93,6 +93,7 @@ struct vo_engine {
   int n_slots = 0, n_pairbuf = 0;       // incl. the operator-level scratch slots / pair
   int op_slot_a = 0, op_slot_b = 0, op_pair = 0;
   int rows_per_group = 0, prune = 1, match_threads = 0;
+  int lean_match = 0;                   // K2 staging layout: 0 = descriptors in shared memory, 1 = in global memory (tall frames)
   int split_match = 1;  // mono pairs: prev->curr in full, then curr->prev from hints (VO_MATCH_SPLIT=0: one joint launch; developer A/B switch)
   vo::FrameArrays fa{};
   CUtensorMap tmap_slots;
@@ -304,7 +305,7 @@ vo_status do_match(vo_engine* e, int pair0, int n_pairs, int max_features, float
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)pair0 * 2, 2 * n_pairs,
                          e->d_best + (int64_t)pair0 * 2 * g.U * 4 * g.col_cap, e->rows_per_group, e->prune,
-                         e->match_threads, e->cfg.match_seed_good, e->split_match, e->stream));
+                         e->match_threads, e->cfg.match_seed_good, e->split_match, e->lean_match, e->stream));
     e->launches += (e->prune && e->split_match) ? 3 : 1;
   }
   {
@@ -412,7 +413,7 @@ vo_status do_match_quad(vo_engine* e, int item0, int n_items, int refinement, in
   {
     Scope sc(e, F_MATCH);
     CU_TRY(vo::launch_k2(g, e->fa, e->d_edges + (int64_t)item0 * 4, 4 * n_items, e->d_best + (int64_t)item0 * 4 * lists,
-                         e->rows_per_group, e->prune, e->match_threads, e->cfg.match_seed_good, 0, e->stream));
+                         e->rows_per_group, e->prune, e->match_threads, e->cfg.match_seed_good, 0, e->lean_match, e->stream));
     e->launches += 1;
   }
   {
@@ -560,7 +561,11 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   e->n_pairbuf = cfg.max_pairs + 1; e->op_pair = cfg.max_pairs;
   // origin v-bin rows per matching CTA: the whole column for KITTI-sized frames, groups of 8 rows for tall frames
   // (2048x1024: V = 23; measured 8.7k -> 9.7k pairs/s), so that a CTA's candidate window fits one staging chunk
-  e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : (g.V <= 12 ? g.V : 8);
+  // tall frames use the lean staging layout (descriptors fetched from global memory by the filter's survivors), whose 4096-candidate
+  // buffer holds the window of 12 origin rows at once.  VO_MATCH_LEAN = 0 / 1 overrides the choice (developer A/B switch).
+  e->lean_match = g.V > 12 ? 1 : 0;
+  if (const char* lm = getenv("VO_MATCH_LEAN")) e->lean_match = atoi(lm) != 0;
+  e->rows_per_group = cfg.match_rows_per_cta > 0 ? cfg.match_rows_per_cta : (g.V <= 12 ? g.V : (e->lean_match ? 12 : 8));
   e->prune = cfg.match_exhaustive ? 0 : 1;
   if (const char* sp = getenv("VO_MATCH_SPLIT")) e->split_match = atoi(sp) != 0;
   e->epi = cfg.stereo ? 4 : 2;

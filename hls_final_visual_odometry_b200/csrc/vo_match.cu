@@ -85,7 +85,36 @@ struct K2Tables {
   int32_t lagEnd[kOC][kMaxV];         // origins o < lagEnd[v] of row v may carry a lagging v_bin
 };
 
-struct __align__(128) K2Smem {
+// Staged candidates, two layouts (template parameter LEAN of the kernel):
+//   fat  (frames whose windows fit: V <= 12 bin rows, e.g. 1241x376) -- descriptor, window word, rank and signature in shared
+//        memory, 48 bytes per candidate, 1896 candidates per chunk;
+//   lean (tall frames, e.g. 2048x1024: V = 23) -- the 32 descriptor bytes stay in global memory (L2-resident: a frame's
+//        records are 1-3 MB) and are fetched by the few candidates that pass the filter; shared memory keeps 20 bytes per
+//        candidate (window word, rank, record index, signature), 4096 candidates per chunk, so a whole window of 16 origin rows
+//        is staged at once instead of in chunks that every origin has to be set up for again.
+template <bool LEAN> struct K2Cands;
+template <> struct K2Cands<false> {
+  static constexpr int kCap = kCandCap, kPosBits = 11;
+  using QEntry = uint16_t;
+  QEntry queue[kMaxWarps][kQueue];    // M tasks: filter hits awaiting exact evaluation, owner lane << kPosBits | staged position
+  __align__(16) uint4 lo[kCap];       // descriptor bytes 0..15
+  uint4 hi[kCap];                     // descriptor bytes 16..31
+  uint2 xr[kCap];                     // {xy + 0x80008000, u_rel<<16 | col_idx}
+  __align__(16) uint32_t q[kCap];     // signature word 0 (desc_q); read four at a time
+  __align__(16) uint32_t q1[kCap];    // signature word 1
+};
+template <> struct K2Cands<true> {
+  static constexpr int kCap = 4096, kPosBits = 12;
+  using QEntry = uint32_t;
+  QEntry queue[kMaxWarps][kQueue];
+  uint2 xr[kCap];
+  uint32_t rec[kCap];                 // record index of the candidate inside its frame slot (descriptor = desc[2 * rec], [2 * rec + 1])
+  __align__(16) uint32_t q[kCap];
+  __align__(16) uint32_t q1[kCap];
+};
+
+template <bool LEAN>
+struct __align__(128) K2SmemT : K2Cands<LEAN> {
   K2Tables t;
   int32_t n_z[kOC], n_n[kOC], n_p[kOC];  // entries of the three lists of this segment
   int32_t next_item;                  // pass 2: next unclaimed task
@@ -96,15 +125,11 @@ struct __align__(128) K2Smem {
   uint16_t plist[kOC][kListCap];      // M: origins with a poor bound or none (exhaustive mode: every origin)
   uint8_t cls[kOC][kListCap];         // pass 1 -> ordered scan: 0 nothing to search, 1 Z, 2 N, 3 M
   uint32_t sbest[kMaxWarps][32];      // M tasks: best key of the warp's 32 origins (results of the cooperative evaluations)
-  uint16_t queue[kMaxWarps][kQueue];  // M tasks: filter hits awaiting exact evaluation, owner lane << 11 | staged position
-  __align__(16) uint4 lo[kCandCap];   // descriptor bytes 0..15
-  uint4 hi[kCandCap];                 // descriptor bytes 16..31
-  uint2 xr[kCandCap];                 // {xy + 0x80008000, u_rel<<16 | col_idx}
-  __align__(16) uint32_t q[kCandCap];  // signature word 0: 4 coded group sums of bytes 0..15; read four at a time
-  __align__(16) uint32_t q1[kCandCap]; // signature word 1: bytes 16..31
 };
-static_assert(kCandCap <= 2048, "queue entries pack the staged position into 11 bits");
-static_assert(sizeof(K2Smem) <= 113 * 1024, "two K2 CTAs per SM need <= 113 KB each (227 KB minus the per-CTA reserve)");
+static_assert(K2Cands<false>::kCap <= (1 << K2Cands<false>::kPosBits) && K2Cands<true>::kCap <= (1 << K2Cands<true>::kPosBits),
+              "queue entries pack the staged position into kPosBits bits");
+static_assert(sizeof(K2SmemT<false>) <= 113 * 1024 && sizeof(K2SmemT<true>) <= 113 * 1024,
+              "two K2 CTAs per SM need <= 113 KB each (227 KB minus the per-CTA reserve)");
 
 // acc + sum of |a_i - b_i| over the four packed bytes: one VABSDIFF4.U8.ACC
 __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t acc) {
@@ -126,11 +151,18 @@ __device__ __forceinline__ uint32_t sad32(const uint4& a, const uint4& b, const 
 
 // key of one staged candidate for an origin (a, b, window lo_p/hi_p), kNone if outside the window.
 // packed window test: both 16-bit fields carry a guard bit (bit 15); DESIGN.md "window test"
-__device__ __forceinline__ uint32_t cand_key(const K2Smem& S, int p, const uint4& a, const uint4& b, uint32_t lo_p,
-                                             uint32_t hi_p) {
-  K2CHECK(p >= 0 && p < kCandCap);
+template <bool LEAN>
+__device__ __forceinline__ uint32_t cand_key(const K2SmemT<LEAN>& S, const uint4* __restrict__ desc_to, int p, const uint4& a,
+                                             const uint4& b, uint32_t lo_p, uint32_t hi_p) {
+  K2CHECK(p >= 0 && p < K2Cands<LEAN>::kCap);
   const uint2 xr = S.xr[p];
-  const uint32_t sad = sad32(a, b, S.lo[p], S.hi[p]);
+  uint32_t sad;
+  if constexpr (LEAN) {
+    const uint32_t rec = S.rec[p];
+    sad = sad32(a, b, __ldg(&desc_to[2 * rec]), __ldg(&desc_to[2 * rec + 1]));
+  } else {
+    sad = sad32(a, b, S.lo[p], S.hi[p]);
+  }
   const uint32_t t1 = xr.x - lo_p, t2 = xr.x - hi_p;
   const uint32_t key = sad * 0x80000u + xr.y;
   return (((t1 & ~t2) & 0x80008000u) == 0x80008000u) ? key : kNone;
@@ -160,13 +192,15 @@ struct K2Origin {
 // Matches the origins of columns [ub0, ub0+noc) x rows of group `grp`.  Returns false (having
 // written nothing) when a row of the shared (noc+5)-column window does not fit the staging buffer;
 // the caller then runs the columns one at a time (a 6-column row always fits).
-template <bool PRUNE, int THREADS>
-__device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
+template <bool PRUNE, int THREADS, bool LEAN>
+__device__ __forceinline__ bool k2_columns(K2SmemT<LEAN>& S, const Geom& g, const FrameArrays& fa, int from_slot, int to_slot,
                                            uint32_t* __restrict__ best_dir, int c, int ub0, int noc, int grp,
                                            int rows_per_group, int rad_v, int reach, int seed_good, bool hinted,
                                            uint32_t* __restrict__ clear_dir) {
   constexpr int NW = THREADS / 32;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
+  constexpr int kCap = K2Cands<LEAN>::kCap, kPosBits = K2Cands<LEAN>::kPosBits;  // staged candidates per chunk
+  using QEntry = typename K2Cands<LEAN>::QEntry;
   K2Tables& t = S.t;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int U = g.U, V = g.V;
@@ -241,7 +275,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
   const int row_hi = min(min(r1 + 3, V - 1), r1 + reach);
   if (noc > 1)
     for (int v = row_lo; v < row_hi; v++)
-      if (t.rowTot[v] > kCandCap) return false;
+      if (t.rowTot[v] > kCap) return false;
 
   const uint32_t* xy_from = fa.xy + (int64_t)from_slot * fa.rec_stride;
   const uint4* desc_from = fa.desc + (int64_t)from_slot * fa.rec_stride * 2;
@@ -258,7 +292,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
   for (int ra = row_lo;;) {
     // ---- chunk = as many whole rows as fit the staging buffer ------------------------------
     int rb = ra, staged = 0;
-    while (rb < row_hi && staged + t.rowTot[rb] <= kCandCap) { staged += t.rowTot[rb]; rb++; }
+    while (rb < row_hi && staged + t.rowTot[rb] <= kCap) { staged += t.rowTot[rb]; rb++; }
     const bool last_chunk = rb >= row_hi;
     __syncthreads();  // previous chunk fully consumed (and lagEnd visible)
     if (tid <= rb - ra) {
@@ -280,19 +314,27 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
       const int dst = t.segOff[v][j];
       const int64_t src = (int64_t)((v * U + ulo + j) * 4 + c) * g.cap;
       const uint32_t rank0 = ((uint32_t)j << 16) | (uint32_t)t.colT[j][v];
-      K2CHECK(dst >= 0 && dst + npad <= kCandCap && n <= g.cap);
+      K2CHECK(dst >= 0 && dst + npad <= kCap && n <= g.cap);
       for (int k = lane; k < npad; k += 32) {
         if (k < n) {
-          const uint4 d0 = desc_to[(src + k) * 2], d1 = desc_to[(src + k) * 2 + 1];
-          S.lo[dst + k] = d0;
-          S.hi[dst + k] = d1;
+          if constexpr (LEAN) {
+            S.rec[dst + k] = (uint32_t)(src + k);
+          } else {
+            const uint4 d0 = desc_to[(src + k) * 2], d1 = desc_to[(src + k) * 2 + 1];
+            S.lo[dst + k] = d0;
+            S.hi[dst + k] = d1;
+          }
           S.xr[dst + k] = make_uint2(xy_to[src + k] + 0x80008000u, rank0 + (uint32_t)k);
           const uint2 qv = q_to[src + k];
           S.q[dst + k] = qv.x;
           S.q1[dst + k] = qv.y;
         } else {
-          S.lo[dst + k] = make_uint4(0, 0, 0, 0);
-          S.hi[dst + k] = make_uint4(0, 0, 0, 0);
+          if constexpr (LEAN) {
+            S.rec[dst + k] = 0u;  // (never fetched: a dummy cannot pass the filter, and its window word rejects it anyway)
+          } else {
+            S.lo[dst + k] = make_uint4(0, 0, 0, 0);
+            S.hi[dst + k] = make_uint4(0, 0, 0, 0);
+          }
           S.xr[dst + k] = make_uint2(kNone, kNone);
           S.q[dst + k] = kNone;
           S.q1[dst + k] = kNone;
@@ -421,7 +463,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           }
           if (k1 != kNone && rows_here && need_seed) {
             const int p = (int)(k1 & 0xFFFFFu);
-            if (p >= t.rowStart[og.vlo] && p < t.rowStart[og.vhi]) bestk = min(bestk, cand_key(S, p, og.a, og.b, og.lo_p, og.hi_p));
+            if (p >= t.rowStart[og.vlo] && p < t.rowStart[og.vhi]) bestk = min(bestk, cand_key(S, desc_to, p, og.a, og.b, og.lo_p, og.hi_p));
           }
         }
         // ---- class: Z (bound 0), N (bound <= seed_good), M (everything else that has rows to search) ----
@@ -529,7 +571,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           // queue at positions from a warp scan; 32 queued (origin, candidate) pairs are then evaluated at once, one per
           // lane, the origin's record coming from its owner lane by shuffle and the result going back through shared memory.
           uint32_t* sbest = S.sbest[warp];
-          uint16_t* queue = S.queue[warp];
+          QEntry* queue = S.queue[warp];
           int qn = 0;  // queued hits (warp-uniform)
           if (kindM) { sbest[lane] = bestk; __syncwarp(); }
           auto flush = [&]() {
@@ -538,7 +580,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             const bool on = lane < n;
             K2CHECK(qn >= 0 && qn + n <= kQueue);
             const uint32_t e = on ? (uint32_t)queue[qn + lane] : 0u;
-            const int owner = (int)(e >> 11), p = (int)(e & 0x7FFu);
+            const int owner = (int)(e >> kPosBits), p = (int)(e & ((1u << kPosBits) - 1u));
             uint4 oa, ob;
             oa.x = __shfl_sync(FULL, a.x, owner); oa.y = __shfl_sync(FULL, a.y, owner);
             oa.z = __shfl_sync(FULL, a.z, owner); oa.w = __shfl_sync(FULL, a.w, owner);
@@ -546,7 +588,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             ob.z = __shfl_sync(FULL, b.z, owner); ob.w = __shfl_sync(FULL, b.w, owner);
             const uint32_t olo = __shfl_sync(FULL, lo_p, owner), ohi = __shfl_sync(FULL, hi_p, owner);
             if (on) {
-              const uint32_t k = cand_key(S, p, oa, ob, olo, ohi);
+              const uint32_t k = cand_key(S, desc_to, p, oa, ob, olo, ohi);
               if (k < sbest[owner]) atomicMin(&sbest[owner], k);
             }
             if (lane == 0) K2STAT(7, 1);
@@ -571,7 +613,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
             const bool act = (r >= vlo) && (r < vhi);
             int pg = t.segOff[r][j0] >> 2;            // candidate groups of 4 (every bin list is padded to 4)
             const int pg1 = t.segOff[r][j1] >> 2;
-            K2CHECK(pg >= 0 && pg1 * 4 <= kCandCap);
+            K2CHECK(pg >= 0 && pg1 * 4 <= kCap);
             // 32 candidates (8 groups) at a time: bias + Q has its sign bit set exactly when Q exceeds the lane's bound (lane not
             // searching this row: always; no bound yet: never), and one funnel shift per candidate collects the signs
             for (; pg < pg1; pg += 8) {
@@ -654,7 +696,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                   ob.z = __shfl_sync(FULL, b.z, L); ob.w = __shfl_sync(FULL, b.w, L);
                   const uint32_t olo = __shfl_sync(FULL, lo_p, L), ohi = __shfl_sync(FULL, hi_p, L);
                   uint32_t k = kNone;
-                  if ((mL << lane) & 0x80000000u) { k = cand_key(S, (pg << 2) + lane, oa, ob, olo, ohi); }
+                  if ((mL << lane) & 0x80000000u) { k = cand_key(S, desc_to, (pg << 2) + lane, oa, ob, olo, ohi); }
                   k = __reduce_min_sync(FULL, k);
                   if (lane == L) {
                     hit = 0u; n = 0;
@@ -671,13 +713,13 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                 const int total = __shfl_sync(FULL, incl, 31);
                 own = qn + total > kQueue;  // lanes still without a bound hit everything: too many for the queue at once
                 if (!own && total > 0) {
-                  uint16_t* qw = queue + (qn + incl - n);
-                  const uint32_t ebase = ((uint32_t)lane << 11) | (uint32_t)(pg << 2);
+                  QEntry* qw = queue + (qn + incl - n);
+                  const uint32_t ebase = ((uint32_t)lane << kPosBits) | (uint32_t)(pg << 2);
                   K2CHECK(qn + incl <= kQueue);
                   while (hit != 0u) {
                     const int z = __clz((int)hit);
                     hit &= ~(0x80000000u >> z);
-                    *qw++ = (uint16_t)(ebase + (uint32_t)z);
+                    *qw++ = (QEntry)(ebase + (uint32_t)z);
                   }
                   qn += total;
                   __syncwarp();
@@ -692,7 +734,7 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
                 while (hit != 0u) {
                   const int z = __clz((int)hit);
                   hit &= ~(0x80000000u >> z);
-                  const uint32_t k = cand_key(S, (pg << 2) + z, a, b, lo_p, hi_p);
+                  const uint32_t k = cand_key(S, desc_to, (pg << 2) + z, a, b, lo_p, hi_p);
                   if (k < bestk) { bestk = k; tq = (int)(k >> 19); }
                 }
               }
@@ -748,10 +790,10 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
           const uint4 a = og.a, b = og.b;
           const uint32_t lo_p = og.lo_p, hi_p = og.hi_p;
           const int p0 = t.segOff[r][j0], p1 = t.segOff[r][j1];
-          K2CHECK(p0 >= 0 && p1 <= kCandCap);
+          K2CHECK(p0 >= 0 && p1 <= kCap);
           uint32_t k = kNone;
 #pragma unroll 2
-          for (int p = p0; p < p1; p++) k = min(k, cand_key(S, p, a, b, lo_p, hi_p));
+          for (int p = p0; p < p1; p++) k = min(k, cand_key(S, desc_to, p, a, b, lo_p, hi_p));
           if (act && k != kNone) atomicMin(&bo[o], k - ((uint32_t)j0 << 16));
         }
       }
@@ -777,12 +819,12 @@ __device__ __forceinline__ bool k2_columns(K2Smem& S, const Geom& g, const Frame
   return true;
 }
 
-template <bool PRUNE, int THREADS>
+template <bool PRUNE, int THREADS, bool LEAN>
 __global__ void __launch_bounds__(THREADS, 2)
 k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __restrict__ best, int rows_per_group,
          int ngroups, int seed_good, int mode) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
-  K2Smem& S = *reinterpret_cast<K2Smem*>(smem_raw);
+  K2SmemT<LEAN>& S = *reinterpret_cast<K2SmemT<LEAN>*>(smem_raw);
   const int cg = blockIdx.x / ngroups, grp = blockIdx.x - cg * ngroups;
   // mode 0: grid.y = class x {even, odd edge}, every search in full.  Modes 1 and 2 split a mono pair's two directions
   // over two launches (grid.y = class): 1 = the odd edges (prev -> curr) in full, 2 = the even edges (curr -> prev)
@@ -796,7 +838,7 @@ k2_match(Geom g, FrameArrays fa, const int4* __restrict__ edges, uint32_t* __res
   uint32_t* best_dir = best + (int64_t)edge * g.U * 4 * g.col_cap;
   // joint pass over both columns; if a row of the shared window does not fit, one pass per column
   for (int it = -1;;) {
-    const bool ok = k2_columns<PRUNE, THREADS>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
+    const bool ok = k2_columns<PRUNE, THREADS, LEAN>(S, g, fa, from_slot, to_slot, best_dir, c, it < 0 ? ub0 : ub0 + it,
                                                it < 0 ? noc : 1, grp, rows_per_group, ed.z, ed.w, seed_good, mode == 2,
                                                mode == 1 ? best + (int64_t)(edge - 1) * g.U * 4 * g.col_cap : nullptr);
     if (it < 0 && ok) break;
@@ -1129,46 +1171,54 @@ k3_emit(Geom g, FrameArrays fa, const int2* __restrict__ pairs, const uint32_t* 
   }
 }
 
-template <bool PRUNE, int THREADS>
+template <bool PRUNE, int THREADS, bool LEAN>
 static cudaError_t launch_k2_t(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
                                int rows_per_group, int seed_good, bool split, cudaStream_t st) {
-  const int bytes = (int)sizeof(K2Smem);
+  const int bytes = (int)sizeof(K2SmemT<LEAN>);
   const int ngroups = (g.V + rows_per_group - 1) / rows_per_group;
   const int cgroups = (g.U - 1 + kOC - 1) / kOC;
   const int budget = seed_good > 0 ? seed_good : kSeedGood;
   if (!split) {
     dim3 grid(cgroups * ngroups, 8, n_edges / 2);  // edges come in twos (mono: curr->prev, prev->curr; quad: four)
-    k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 0);
+    k2_match<PRUNE, THREADS, LEAN><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 0);
     return cudaGetLastError();
   }
   // mono pairs: prev -> curr in full (its CTAs also reset best[curr -> prev]), hints, then curr -> prev from the hints
   dim3 grid(cgroups * ngroups, 4, n_edges / 2), hgrid((g.U - 1) * 4, n_edges / 2);
-  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 1);
+  k2_match<PRUNE, THREADS, LEAN><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 1);
   k2_hint_scatter<<<hgrid, KH_THREADS, 0, st>>>(g, fa, edges, best);
-  k2_match<PRUNE, THREADS><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 2);
+  k2_match<PRUNE, THREADS, LEAN><<<grid, THREADS, bytes, st>>>(g, fa, edges, best, rows_per_group, ngroups, budget, 2);
   return cudaGetLastError();
 }
 
-// staged candidates per chunk: a window row of one origin column (six bin lists, each padded to 4) must fit
+// staged candidates per chunk: a window row of one origin column (six bin lists, each padded to 4) must fit either layout
 int k2_cand_cap() { return kCandCap; }
 
 // per-device opt-in to K2's dynamic shared memory, every instantiation launch_k2 can pick (see init_k1_device)
 cudaError_t init_k2_device() {
-  const int bytes = (int)sizeof(K2Smem);
-  cudaError_t e = cudaFuncSetAttribute(k2_match<false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 384>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  const int fat = (int)sizeof(K2SmemT<false>), lean = (int)sizeof(K2SmemT<true>);
+  cudaError_t e = cudaFuncSetAttribute(k2_match<false, 256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fat);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fat);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 384, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fat);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 512, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fat);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<false, 256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k2_match<true, 512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean);
   return e;
 }
 
+// lean != 0: the staging layout for tall frames (descriptors stay in global memory, K2Cands<true>); built for the default
+// thread count only
 cudaError_t launch_k2(const Geom& g, const FrameArrays& fa, const int4* edges, int n_edges, uint32_t* best,
-                      int rows_per_group, int prune, int threads, int seed_good, int split, cudaStream_t st) {
+                      int rows_per_group, int prune, int threads, int seed_good, int split, int lean, cudaStream_t st) {
   // split != 0: the edges are mono pairs (curr->prev, prev->curr) and may run as two dependent launches
-  if (!prune) return launch_k2_t<false, 256>(g, fa, edges, n_edges, best, rows_per_group, seed_good, false, st);
-  if (threads == 256) return launch_k2_t<true, 256>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
-  if (threads == 384) return launch_k2_t<true, 384>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
-  return launch_k2_t<true, 512>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
+  if (lean) {
+    if (!prune) return launch_k2_t<false, 256, true>(g, fa, edges, n_edges, best, rows_per_group, seed_good, false, st);
+    return launch_k2_t<true, 512, true>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
+  }
+  if (!prune) return launch_k2_t<false, 256, false>(g, fa, edges, n_edges, best, rows_per_group, seed_good, false, st);
+  if (threads == 256) return launch_k2_t<true, 256, false>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
+  if (threads == 384) return launch_k2_t<true, 384, false>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
+  return launch_k2_t<true, 512, false>(g, fa, edges, n_edges, best, rows_per_group, seed_good, split, st);
 }
 
 cudaError_t launch_k3(const Geom& g, const FrameArrays& fa, const int2* pairs, int n_pairs, const uint32_t* best,
