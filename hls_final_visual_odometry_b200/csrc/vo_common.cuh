@@ -8,6 +8,7 @@
 //                                        (class<<16 | index in its list) or 0xFFFFFFFF
 //   desc  uint4[bin_num][cap][2]         the 32 descriptor bytes in reference byte order
 //   q     uint2[bin_num][cap]            2 x 4 coded group sums of the descriptor (SAD lower bound, K2)
+//   duv   u16 [H][pitch]                 stereo engines only: Sobel responses du | dv << 8 per pixel (K1 -> K5)
 // This is the reference's max2/max2_num (src/size.h:17-20) as padded SoA; vo_dump_features
 // converts back to the 12 x int32 AoS records for parity.
 #pragma once
@@ -38,6 +39,8 @@ struct FrameArrays {   // base pointers of slot 0; slot s is at + s * stride
   uint32_t* meta;
   uint4* desc;                            // 2 * rec_stride uint4 per slot
   uint2* q;                               // rec_stride uint2 per slot: lower-bound signature (desc_q)
+  uint16_t* duv;  int64_t duv_stride;     // optional (stereo engines; else nullptr): du | dv << 8 of every pixel, u16[H][pitch] per
+                                          // slot, written by K1 from the planes it holds anyway and read by K5 (sub-pixel refinement)
 };
 
 // destination v-bin of block-row origin j (see oracle/vo_oracle.c dest_v_bin;

@@ -604,6 +604,11 @@ vo_status vo_engine_create(const vo_config* cfg_in, int32_t device, void* stream
   ALLOC(e->fa.meta, sizeof(uint32_t) * S * e->fa.rec_stride);
   ALLOC(e->fa.desc, sizeof(uint4) * 2 * S * e->fa.rec_stride);
   ALLOC(e->fa.q, sizeof(uint2) * S * e->fa.rec_stride);
+  if (cfg.stereo) {  // Sobel response planes K1 -> K5 (sub-pixel refinement of quad lists), 2 bytes per pixel and slot
+    e->fa.duv_stride = (int64_t)g.pitch * g.H;
+    ALLOC(e->fa.duv, sizeof(uint16_t) * S * e->fa.duv_stride);
+    cudaMemsetAsync(e->fa.duv, 0, sizeof(uint16_t) * S * e->fa.duv_stride, e->stream);
+  }
   cudaMemsetAsync(e->fa.cnt, 0, sizeof(int32_t) * S * e->fa.cnt_stride, e->stream);
   cudaMemsetAsync(e->fa.img, 0, (size_t)(S * e->fa.img_stride + 256), e->stream);
   const int64_t lists = (int64_t)g.U * 4 * g.col_cap;
@@ -670,7 +675,7 @@ void vo_engine_destroy(vo_engine* e) {
   for (cudaEvent_t ev : {e->ev_h2d_done, e->ev_k1_done, e->ev_compute_done, e->ev_d2h_done}) if (ev) cudaEventDestroy(ev);
   for (auto& f : e->fences) if (f) cudaEventDestroy(f);
   for (auto& r : e->readers) if (r.ev) cudaEventDestroy(r.ev);
-  cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc); cudaFree(e->fa.q);
+  cudaFree(e->fa.img); cudaFree(e->fa.cnt); cudaFree(e->fa.xy); cudaFree(e->fa.meta); cudaFree(e->fa.desc); cudaFree(e->fa.q); cudaFree(e->fa.duv);
   cudaFree(e->d_pairs_base); cudaFree(e->d_best); cudaFree(e->d_flags); cudaFree(e->d_list_cnt); cudaFree(e->d_raw); cudaFree(e->d_side);
   cudaFree(e->d_bucketed); cudaFree(e->d_n_raw); cudaFree(e->d_n_bucketed); cudaFree(e->d_status);
   cudaFree(e->d_scratch); cudaFree(e->d_lfsr); cudaFree(e->d_max2); cudaFree(e->d_max2b); cudaFree(e->d_num);

@@ -155,6 +155,18 @@ k1_extract(const __grid_constant__ CUtensorMap tmap, Geom g, FrameArrays fa, int
   }
   __syncthreads();
 
+  // ---- optional: the du | dv plane of this tile's own pixels goes to global memory (stereo engines: K5 refines sub-pixel
+  //      positions on exactly these responses and would otherwise recompute them per match) ------------------------------
+  if (fa.duv != nullptr) {
+    uint16_t* plane = fa.duv + (int64_t)slot * fa.duv_stride;
+    for (int i = tid; i < BW * BH; i += K1_THREADS) {
+      const int dy = i / BW, dx = i - dy * BW;  // compile-time divisor
+      const int x = x0 + dx, y = y0 + dy;
+      if (x < g.W && y < g.H) plane[(int64_t)y * g.pitch + x] = s.duv[(dy + 5) * OW + dx + 5];
+    }
+    if (ub >= g.U || r > g.j_last / BH) return;  // a tile launched only to cover the image's last rows / columns: no 3x3 block in it
+  }
+
   // ---- NMS: one thread per 3x3 block, block-raster order == thread order -------------------
   const int bx = tid % NBX, by = tid / NBX;
   const int bi = x0 + 3 * bx, bj = y0 + 3 * by;  // block origin (i, j) of the reference loops
@@ -371,8 +383,12 @@ cudaError_t init_k1_device() {
 
 cudaError_t launch_k1(const CUtensorMap& tmap, const Geom& g, const FrameArrays& fa, int first_slot, int z_base, int n,
                       cudaStream_t st) {
-  const int rows = g.j_last / g.bin_h + 1;  // tile rows that contain at least one block row
-  dim3 grid(g.U, rows, n);
+  int cols = g.U, rows = g.j_last / g.bin_h + 1;  // tile rows that contain at least one block row
+  if (fa.duv != nullptr) {  // the response planes must cover every pixel K5 can touch: x <= W-6, y <= H-6
+    cols = max(cols, (g.W - 5 + g.bin_w - 1) / g.bin_w);
+    rows = max(rows, (g.H - 5 + g.bin_h - 1) / g.bin_h);
+  }
+  dim3 grid(cols, rows, n);
 #define X(w, h)                                                                                                          \
   if (g.bin_w == w && g.bin_h == h) {                                                                                    \
     k1_extract<K1Tile<w, h>><<<grid, K1_THREADS, sizeof(K1SmemT<K1Tile<w, h>>), st>>>(tmap, g, fa, first_slot, z_base);  \

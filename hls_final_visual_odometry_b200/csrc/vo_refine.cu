@@ -14,6 +14,7 @@
 // registers), lanes 0..24 each take one shift's SAD (one VABSDIFF4 per byte against the anchor descriptor held in
 // registers), a warp min picks the first minimum in raster order, and the fit is exact double arithmetic.  k5_compact then drops rejected matches, order preserved.
 #include "vo_common.cuh"
+#include <cstdlib>
 
 namespace vo {
 
@@ -70,6 +71,26 @@ __device__ __forceinline__ void responses(K5Warp& w, const uint8_t* __restrict__
   __syncwarp();
 }
 
+// The same responses read back from the du | dv plane K1 left in global memory (stereo engines, FrameArrays::duv): identical
+// bytes (K1 computes the reference's Sobel on the whole frame), none of the patch loads and filter arithmetic above.
+template <int R>
+__device__ __forceinline__ void responses_from_plane(K5Warp& w, const uint16_t* __restrict__ plane, int pitch, int cx, int cy, int lane) {
+  constexpr int S = 2 * R + 1;
+  const uint16_t* src = plane + (int64_t)(cy - R) * pitch + (cx - R);
+  __syncwarp();
+#pragma unroll
+  for (int i0 = 0; i0 < S * S; i0 += 32) {
+    const int i = i0 + lane;
+    if (i < S * S) {
+      const int r = i / S, c = i - r * S;
+      const uint32_t v = __ldg(&src[(int64_t)r * pitch + c]);
+      w.du[i] = (uint8_t)(v & 255u);
+      w.dv[i] = (uint8_t)(v >> 8);
+    }
+  }
+  __syncwarp();
+}
+
 // |a - b| + acc on zero-extended bytes: one VABSDIFF4
 __device__ __forceinline__ uint32_t absdiff_acc(uint32_t a, uint32_t b, uint32_t acc) {
   uint32_t d;
@@ -78,13 +99,15 @@ __device__ __forceinline__ uint32_t absdiff_acc(uint32_t a, uint32_t b, uint32_t
 }
 
 // one parabolicFitting call: anchor descriptor in d1[] (registers), target frame `img`, (u2, v2) updated
-__device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const uint8_t* __restrict__ img, const uint32_t (&d1)[16],
+template <bool PLANES>
+__device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const FrameArrays& fa, int slot, const uint32_t (&d1)[16],
                                            float& u2, float& v2, int lane) {
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   const float margin = 7.f;  // src/matcher.cpp:38
   if (u2 - 2.f < margin || u2 + 2.f > (float)(g.W - 1) - margin || v2 - 2.f < margin || v2 + 2.f > (float)(g.H - 1) - margin)
     return false;
-  responses<4>(w, img, g.pitch, (int)u2, (int)v2, lane);
+  if constexpr (PLANES) responses_from_plane<4>(w, fa.duv + (int64_t)slot * fa.duv_stride, g.pitch, (int)u2, (int)v2, lane);
+  else responses<4>(w, fa.img + (int64_t)slot * fa.img_stride, g.pitch, (int)u2, (int)v2, lane);
   int cost = 0x7FFFFF;
   if (lane < 25) {
     const int a = lane % 5, b = lane / 5;
@@ -123,7 +146,11 @@ __device__ __forceinline__ bool fit_target(K5Warp& w, const Geom& g, const uint8
 }
 
 // quads[item] = {1p, 2p, 1c, 2c} slots (2p/2c = -1 for flow lists)
-__global__ void __launch_bounds__(K5_WARPS * 32, 4)
+#ifndef VO_K5_PLANES_CTAS
+#define VO_K5_PLANES_CTAS 4
+#endif
+template <bool PLANES>
+__global__ void __launch_bounds__(K5_WARPS * 32, PLANES ? VO_K5_PLANES_CTAS : 4)
 k5_refine(Geom g, FrameArrays fa, const int4* __restrict__ quads, float* __restrict__ lists, int64_t stride_matches,
           const int32_t* __restrict__ n_list, uint8_t* __restrict__ keep) {
   __shared__ K5Warp sw[K5_WARPS];
@@ -140,17 +167,17 @@ k5_refine(Geom g, FrameArrays fa, const int4* __restrict__ quads, float* __restr
     const int cx = (int)u1c, cy = (int)v1c;
     bool ok = cx >= 4 && cy >= 4 && cx <= g.W - 5 && cy <= g.H - 5;  // the anchor's descriptor must lie inside the image
     if (ok) {
-      responses<2>(w, fa.img + (int64_t)qd.z * fa.img_stride, g.pitch, cx, cy, lane);
+      if constexpr (PLANES) responses_from_plane<2>(w, fa.duv + (int64_t)qd.z * fa.duv_stride, g.pitch, cx, cy, lane);
+      else responses<2>(w, fa.img + (int64_t)qd.z * fa.img_stride, g.pitch, cx, cy, lane);
       uint32_t d1[16];  // the anchor's small descriptor, zero-extended bytes (every lane holds all 16)
 #pragma unroll
       for (int s = 0; s < 16; s++) {
         const int idx = (2 + c_small_dy[s]) * 5 + (2 + c_small_dx[s]);
         d1[s] = (s < 12) ? w.du[idx] : w.dv[idx];
       }
-      ok = fit_target(w, g, fa.img + (int64_t)qd.x * fa.img_stride, d1, u1p, v1p, lane);
+      ok = fit_target<PLANES>(w, g, fa, qd.x, d1, u1p, v1p, lane);
       if (ok && u2c >= 0.f && qd.y >= 0 && qd.w >= 0)
-        ok = fit_target(w, g, fa.img + (int64_t)qd.w * fa.img_stride, d1, u2c, v2c, lane) &&
-             fit_target(w, g, fa.img + (int64_t)qd.y * fa.img_stride, d1, u2p, v2p, lane);
+        ok = fit_target<PLANES>(w, g, fa, qd.w, d1, u2c, v2c, lane) && fit_target<PLANES>(w, g, fa, qd.y, d1, u2p, v2p, lane);
     }
     __syncwarp();
     if (lane == 0) {
@@ -197,8 +224,11 @@ k5_compact(uint4* __restrict__ lists, int64_t stride_matches, int32_t* __restric
 cudaError_t launch_k5(const Geom& g, const FrameArrays& fa, const int4* quads, int n_items, void* lists,
                       int64_t stride_matches, int32_t max_n, int32_t* n_list, uint8_t* keep, cudaStream_t st) {
   if (max_n < 1) return cudaSuccess;
-  k5_refine<<<dim3(min((max_n + K5_WARPS - 1) / K5_WARPS, 592), n_items), K5_WARPS * 32, 0, st>>>(g, fa, quads, (float*)lists,
-                                                                                         stride_matches, n_list, keep);
+  const dim3 grid(min((max_n + K5_WARPS - 1) / K5_WARPS, 592), n_items);
+  if (fa.duv != nullptr && !getenv("VO_REFINE_RECOMPUTE"))  // (developer A/B switch: recompute the responses as a mono engine does)
+    k5_refine<true><<<grid, K5_WARPS * 32, 0, st>>>(g, fa, quads, (float*)lists, stride_matches, n_list, keep);
+  else
+    k5_refine<false><<<grid, K5_WARPS * 32, 0, st>>>(g, fa, quads, (float*)lists, stride_matches, n_list, keep);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   k5_compact<<<n_items, K5C_THREADS, 0, st>>>((uint4*)lists, stride_matches, n_list, keep);
