@@ -40,22 +40,53 @@ def _sources(d: str, exts) -> list[str]:
     return sorted(os.path.join(d, f) for f in os.listdir(d) if f.endswith(exts))
 
 
-def _stale(target: str, deps: list[str]) -> bool:
+def _digest(deps: list[str], flags: list[str]) -> str:
+    import hashlib
+    h = hashlib.sha256(" ".join(flags).encode())
+    for d in sorted(deps):
+        if os.path.exists(d):
+            h.update(os.path.basename(d).encode())
+            h.update(open(d, "rb").read())
+    return h.hexdigest()
+
+
+def _stale(target: str, deps: list[str], flags: list[str] | None = None) -> bool:
+    """A target is current when the digest of its sources (written beside it when it was built) matches: file times do not
+    survive the snapshot that carries the tree to a GPU box, contents do.  Without a digest file: modification times."""
     if not os.path.exists(target):
         return True
+    side = target + ".srchash"
+    if flags is not None and os.path.exists(side):
+        return open(side).read().strip() != _digest(deps, flags)
     t = os.path.getmtime(target)
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
+def _stamp(target: str, deps: list[str], flags: list[str]) -> None:
+    tmp = f"{target}.srchash.{os.getpid()}.tmp"
+    with open(tmp, "w") as f:
+        f.write(_digest(deps, flags))
+    os.replace(tmp, target + ".srchash")
+
+
 def build_library(force: bool = False, verbose: bool = False) -> str:
     srcs = _sources(CSRC, (".cu", ".cpp"))
-    deps = srcs + _sources(CSRC, (".cuh",)) + [os.path.join(_ROOT, "include", "vo_b200.h")]
-    if force or _stale(LIB, deps):
-        cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", LIB, *srcs]
+    deps = srcs + _sources(CSRC, (".cuh", ".h")) + [os.path.join(_ROOT, "include", "vo_b200.h")]
+    if force or _stale(LIB, deps, NVCC_FLAGS):
+        # several ranks of one job may find the library stale at the same time (a fresh snapshot can carry sources newer than
+        # the .so): every builder writes its own file and renames it into place, so a reader never maps a half-written library
+        tmp = f"{LIB}.{os.getpid()}.tmp"
+        cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", tmp, *srcs]
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")
-        subprocess.check_call(cmd)
+        try:
+            subprocess.check_call(cmd)
+            os.replace(tmp, LIB)
+            _stamp(LIB, deps, NVCC_FLAGS)
+        finally:
+            if os.path.exists(tmp):
+                os.remove(tmp)
     return LIB
 
 
@@ -68,10 +99,16 @@ def build_host(force: bool = False) -> str | None:
     deps = srcs + _sources(HOST, (".h",)) + [LIB]
     inc = ["-I", os.path.join(_ROOT, "include"), "-I", HOST]
     if force or _stale(HOST_LIB, deps):
-        subprocess.check_call([
-            "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", *inc,
-            "-o", HOST_LIB, *srcs, "-L", _PKG, "-lvo_b200", "-lz", "-Wl,-rpath,$ORIGIN",
-        ])
+        tmp = f"{HOST_LIB}.{os.getpid()}.tmp"
+        try:
+            subprocess.check_call([
+                "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", *inc,
+                "-o", tmp, *srcs, "-L", _PKG, "-lvo_b200", "-lz", "-Wl,-rpath,$ORIGIN",
+            ])
+            os.replace(tmp, HOST_LIB)
+        finally:
+            if os.path.exists(tmp):
+                os.remove(tmp)
     demo_src = os.path.join(HOST, "demo_main.cpp")
     if os.path.exists(demo_src) and (force or _stale(DEMO, deps + [demo_src, HOST_LIB])):
         subprocess.check_call([
