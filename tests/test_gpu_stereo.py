@@ -140,7 +140,8 @@ def test_matcher_level_quad_ring():
         eng.close()
 
 
-@pytest.mark.parametrize("w,h", [(500, 150), (1241, 376)])
+# (306 x 186: the response planes K1 leaves for K5 need one more tile column and one more tile row than the feature lists do)
+@pytest.mark.parametrize("w,h", [(500, 150), (1241, 376), (306, 186)])
 def test_refinement_flow_and_quad_vs_oracle(w, h):
     left, right, orc, fl, fr = _quad_case(w, h, 2, 13, n=2, blur_passes=6)
     eng = Engine(w, h, max_frames=4, max_pairs=1, stereo=True)
