@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <limits>
 #include <numeric>
 #include <vector>
@@ -126,7 +127,8 @@ class SweepHull {
     // sort (src/delaunator.cpp:409-424) is stable, so a stable sort gives the same permutation
     std::vector<int> ids(n);
     std::iota(ids.begin(), ids.end(), 0);
-    std::stable_sort(ids.begin(), ids.end(), [&](int a, int b) { return dist[a] < dist[b]; });
+    if (!radix_order(dist, ids))
+      std::stable_sort(ids.begin(), ids.end(), [&](int a, int b) { return dist[a] < dist[b]; });
 
     if (i0 == kNil) return;
     best = kInf;
@@ -213,6 +215,35 @@ class SweepHull {
   real span_ = 0;
   int hash_size_ = 0, hull_start_ = 0;
 
+  // Stable ascending order of non-negative finite-or-infinite float keys: their bit patterns order like unsigned integers,
+  // so three stable counting passes over 11 + 11 + 10 bits give exactly std::stable_sort's permutation (r2u: the comparison
+  // sort was 11 % of the stage).  Refuses (caller falls back) if a key is negative or NaN.
+  static bool radix_order(const std::vector<real>& key, std::vector<int>& ids) {
+    const size_t n = key.size();
+    std::vector<uint32_t> k(n);
+    for (size_t i = 0; i < n; i++) {
+      uint32_t u;
+      static_assert(sizeof(real) == 4, "float keys");
+      std::memcpy(&u, &key[i], 4);
+      if (u > 0x7F800000u) return false;  // sign bit set (incl. -0.0: equal to +0.0 for `<`, different as bits) or NaN
+      k[i] = u;
+    }
+    std::vector<int> tmp(n);
+    int* src = ids.data();
+    int* dst = tmp.data();
+    const int shifts[3] = {0, 11, 22}, bits[3] = {11, 11, 10};
+    for (int pass = 0; pass < 3; pass++) {
+      const uint32_t mask = (1u << bits[pass]) - 1u;
+      std::vector<uint32_t> cnt((size_t)mask + 2, 0);
+      for (size_t i = 0; i < n; i++) cnt[((k[src[i]] >> shifts[pass]) & mask) + 1]++;
+      for (size_t b = 1; b < cnt.size(); b++) cnt[b] += cnt[b - 1];
+      for (size_t i = 0; i < n; i++) dst[cnt[(k[src[i]] >> shifts[pass]) & mask]++] = src[i];
+      std::swap(src, dst);
+    }
+    if (src != ids.data()) std::memcpy(ids.data(), src, n * sizeof(int));  // (three passes: the result sits in tmp)
+    return true;
+  }
+
   int wrap(int i) const { return i >= hash_size_ ? i % hash_size_ : i; }  // fast_mod, src/delaunator.cpp:19-21
 
   // src/delaunator.cpp:568-574: float product, float floor, truncation to int
@@ -232,6 +263,11 @@ class SweepHull {
       if (b == s2) half_.push_back(a);
       else if (b < s2) half_[b] = a;
     }
+  }
+
+  void relink(int a, int b) {
+    half_[a] = b;
+    if (b != kNil) half_[b] = a;
   }
 
   int add_triangle(int i0, int i1, int i2, int a, int b, int c) {  // src/delaunator.cpp:576-592
@@ -270,9 +306,9 @@ class SweepHull {
             e = prev_[e];
           } while (e != hull_start_);
         }
-        link(a, hbl);
-        link(b, half_[ar]);
-        link(ar, bl);
+        relink(a, hbl);  // every half-edge touched here exists already: plain stores (link() also grows the array)
+        relink(b, half_[ar]);
+        relink(ar, bl);
         const int br = b0 + (b + 1) % 3;
         if (depth < stack_.size()) stack_[depth] = br; else stack_.push_back(br);
         depth++;
