@@ -40,7 +40,12 @@ static inline real dist2(const Pt& a, const Pt& b) { return mag2(sub(a, b)); }
 
 // src/delaunator.hpp:60-67: "same point" test relative to the bounding-box diagonal
 static inline bool same_point(const Pt& a, const Pt& b, real span) {
-  const real d = dist2(a, b) / span;
+  const real d2 = dist2(a, b);
+  // shortcuts that decide the quotient test without the division (every hull-walk step runs it twice): 0 / span is 0, and
+  // d2 > span * 1e-19 puts the rounded quotient at 0.99e-19 or more (span * 1e-19f underflowing to 0 only widens the margin)
+  if (d2 == 0.0f) return span == span && span != 0.0f ? true : (d2 / span) < 1e-20;
+  if (d2 > span * 1e-19f) return false;
+  const real d = d2 / span;
   return d < 1e-20;
 }
 
@@ -62,8 +67,12 @@ static inline bool ccw(const Pt& p0, const Pt& p1, const Pt& p2) {
   const real det = cross(v0, v1);
   const real dist = mag2(v0) + mag2(v1);
   if (det == 0) return false;
-  const real rel = std::fabs(dist / det);
-  if (rel > 1e14) return false;
+  // dist <= |det| * 1e13 keeps the rounded quotient below 1.0000002e13 < 1e14: no division needed (always the case on an
+  // integer lattice, where |det| >= 1 and dist < 2^25)
+  if (!(dist <= std::fabs(det) * 1e13f)) {
+    const real rel = std::fabs(dist / det);
+    if (rel > 1e14) return false;
+  }
   return det > 0;
 }
 
@@ -249,7 +258,7 @@ class SweepHull {
   // src/delaunator.cpp:568-574: float product, float floor, truncation to int
   int key(const Pt& p) const {
     const real a = pseudo_angle(p.x - center_.x, p.y - center_.y);
-    const real f = std::floor(a * hash_size_);
+    const real f = a * hash_size_;  // a is in [0, 1]: floor() and the truncation of the cast agree (src: std::floor, then (int))
     if (!(f >= 0.0f)) return 0;  // NaN (point on the circumcentre): undefined in the reference
     return wrap((int)f);
   }
@@ -283,17 +292,18 @@ class SweepHull {
     int ar = 0;
     stack_.clear();
     for (;;) {
+      static const int kNext[3] = {1, 2, 0}, kPrev[3] = {2, 0, 1};  // (x + 1) % 3, (x + 2) % 3
       const int b = half_[a];
-      const int a0 = 3 * (a / 3);
-      ar = a0 + (a + 2) % 3;
+      const int a0 = 3 * (a / 3), ra = a - a0;
+      ar = a0 + kPrev[ra];
       if (b == kNil) {
         if (depth == 0) break;
         a = stack_[--depth];
         continue;
       }
-      const int b0 = 3 * (b / 3);
-      const int al = a0 + (a + 1) % 3;
-      const int bl = b0 + (b + 2) % 3;
+      const int b0 = 3 * (b / 3), rb = b - b0;
+      const int al = a0 + kNext[ra];
+      const int bl = b0 + kPrev[rb];
       const int p0 = triangles[ar], pr = triangles[a], pl = triangles[al], p1 = triangles[bl];
       if (in_circle(p_[p0], p_[pr], p_[pl], p_[p1])) {
         triangles[a] = p1;
@@ -309,7 +319,7 @@ class SweepHull {
         relink(a, hbl);  // every half-edge touched here exists already: plain stores (link() also grows the array)
         relink(b, half_[ar]);
         relink(ar, bl);
-        const int br = b0 + (b + 1) % 3;
+        const int br = b0 + kNext[rb];
         if (depth < stack_.size()) stack_[depth] = br; else stack_.push_back(br);
         depth++;
       } else {
