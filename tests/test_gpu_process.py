@@ -81,6 +81,26 @@ def test_pipeline_equals_frame_by_frame_process(corridor):
             assert np.array_equal(transformation_vector_to_matrix(tr[k]), seq[k][3])   # same code, same samples: bit-exact
 
 
+def test_a_large_batch_equals_small_batches():
+    """The batch size is a schedule, not a parameter of the result: one 40-frame call of vo_pipeline_process must give exactly
+    what eight 5-frame calls give -- same bucketed lists, same sample sets in frame order, hence the same motions bit for bit."""
+    frames, _ = make_corridor_sequence(W, H, n_frames=40, seed=1)
+    big = Pipeline(W, H, batch=40, cam_height=KITTI_HEIGHT, pitch=0.0, **KITTI_CALIB)
+    ok_b, tr_b, nm_b, ni_b, ml_b = big.process(frames, want_matches=True)
+    big.close()
+    small = Pipeline(W, H, batch=5, cam_height=KITTI_HEIGHT, pitch=0.0, **KITTI_CALIB)
+    parts = [small.process(frames[i:i + 5], want_matches=True) for i in range(0, 40, 5)]
+    small.close()
+    ok_s = np.concatenate([q[0] for q in parts]); tr_s = np.concatenate([q[1] for q in parts])
+    nm_s = np.concatenate([q[2] for q in parts]); ni_s = np.concatenate([q[3] for q in parts])
+    ml_s = [m for q in parts for m in q[4]]
+    assert ok_b[1:].all() and (nm_b[1:] > 100).all()
+    assert np.array_equal(ok_b, ok_s) and np.array_equal(nm_b, nm_s) and np.array_equal(ni_b, ni_s)
+    assert np.array_equal(tr_b, tr_s)
+    for k in range(40):
+        assert matches_digest(ml_b[k]) == matches_digest(ml_s[k]), f"frame {k}"
+
+
 def test_pipeline_on_pure_translation():
     """The blurred-noise crops are a pure image translation: a planar, degenerate configuration on which the reference's
     mono egomotion returns false.  (Not replayed through the compiled reference here: its
