@@ -55,11 +55,13 @@ def noisy_frame(frame, amp, rng):
 
 
 def source_hash():
-    """sha256 over the kernel sources + ABI header: ties profiles/traffic.json to the build it was captured from."""
+    """sha256 over the DEVICE sources (csrc/*.cu, *.cuh, *.h) + ABI header: ties profiles/traffic.json to the kernels it was
+    captured from.  The host stages (csrc/*.cpp: Delaunay filter, egomotion, pipeline) do not move a byte of device traffic and
+    are left out, so that work on them does not orphan a capture of unchanged kernels."""
     import hashlib
     h = hashlib.sha256()
     base = os.path.join(ROOT, "hls_final_visual_odometry_b200", "csrc")
-    files = sorted(os.path.join(base, f) for f in os.listdir(base) if f.endswith((".cu", ".cuh", ".cpp")))
+    files = sorted(os.path.join(base, f) for f in os.listdir(base) if f.endswith((".cu", ".cuh", ".h")))
     for f in files + [os.path.join(ROOT, "include", "vo_b200.h")]:
         h.update(os.path.basename(f).encode())
         h.update(open(f, "rb").read())
