@@ -25,7 +25,14 @@ def build(force: bool = False) -> str:
     src = os.path.join(_HERE, "vo_oracle.c")
     if force or not os.path.exists(_SO) or (
             os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(_SO)):
-        subprocess.check_call(["gcc", "-O2", "-fPIC", "-std=c99", "-shared", "-o", _SO, src, "-lm"])
+        # (written to a private file and renamed into place: the CPU legs of bench.py load this from many processes at once)
+        tmp = f"{_SO}.{os.getpid()}.tmp"
+        try:
+            subprocess.check_call(["gcc", "-O2", "-fPIC", "-std=c99", "-shared", "-o", tmp, src, "-lm"])
+            os.replace(tmp, _SO)
+        finally:
+            if os.path.exists(tmp):
+                os.remove(tmp)
     return _SO
 
 
