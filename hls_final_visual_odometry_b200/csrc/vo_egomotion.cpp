@@ -25,6 +25,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -161,8 +162,17 @@ void sampson_inliers(const std::vector<Pt>& p, const double F[9], double thr, st
     if (vo_ransac::sampson_inlier(p[i], F, thr)) out.push_back(i);
 }
 
-// src/viso_mono.cpp:363-401: linear triangulation (null vector of the 4x4 system) and chirality count
-int triangulate(const std::vector<Pt>& p, const double K[9], const double R[9], const double t[3], std::vector<double>& X) {
+// src/viso_mono.cpp:363-401: linear triangulation (null vector of the 4x4 system) and chirality count.
+// `mirror` != nullptr: the homogeneous points of the SAME rotation with the opposite translation, already triangulated.
+// Negating t negates exactly the fourth column of P2 and of every point's 4 x 4 system (the fourth column of P1 is zero), i.e.
+// J' = J D with D = diag(1, 1, 1, -1).  One-sided Jacobi is sign-symmetric under that: every rotation angle of a pair that
+// involves column 4 flips sign, nothing else changes, V' = D V D -- so the null vector is the mirrored one with its fourth
+// component negated (up to the overall sign, which no user of X can see: the chirality products and the x/w ratios are
+// invariant to it), and half of the 4 N small SVDs per frame are not run (r2v: they were 70 % of the egomotion tail).  The
+// only asymmetry in the arithmetic is the tie zeta == 0 (two columns of exactly equal norm), where either result is a valid
+// decomposition; -DVO_EGO_CHECK_MIRROR runs both ways and aborts on any other difference.
+int triangulate(const std::vector<Pt>& p, const double K[9], const double R[9], const double t[3], std::vector<double>& X,
+                const std::vector<double>* mirror = nullptr) {
   const int n = (int)p.size();
   X.assign((size_t)4 * n, 0.0);
   double P1[12], P2[12], Rt[12];
@@ -178,6 +188,15 @@ int triangulate(const std::vector<Pt>& p, const double K[9], const double R[9], 
     }
   std::vector<double> G;
   double J[16], w[4], V[16];
+  if (mirror != nullptr) {
+    for (int i = 0; i < n; i++) {
+      for (int k = 0; k < 3; k++) X[(size_t)k * n + i] = (*mirror)[(size_t)k * n + i];
+      X[(size_t)3 * n + i] = -(*mirror)[(size_t)3 * n + i];
+    }
+  }
+#ifndef VO_EGO_CHECK_MIRROR
+  if (mirror == nullptr)
+#endif
   for (int i = 0; i < n; i++) {
     for (int j = 0; j < 4; j++) {
       J[0 * 4 + j] = P1[2 * 4 + j] * p[i].u1p - P1[0 * 4 + j];
@@ -186,6 +205,17 @@ int triangulate(const std::vector<Pt>& p, const double K[9], const double R[9], 
       J[3 * 4 + j] = P2[2 * 4 + j] * p[i].v1c - P2[1 * 4 + j];
     }
     jacobi_svd(J, 4, 4, G, w, V);
+#ifdef VO_EGO_CHECK_MIRROR
+    if (mirror != nullptr) {  // the mirrored vector must be +- the computed one, bit for bit
+      bool same = true, neg = true;
+      for (int k = 0; k < 4; k++) {
+        same = same && X[(size_t)k * n + i] == V[k * 4 + 3];
+        neg = neg && X[(size_t)k * n + i] == -V[k * 4 + 3];
+      }
+      if (!same && !neg) std::abort();
+      continue;
+    }
+#endif
     for (int k = 0; k < 4; k++) X[(size_t)k * n + i] = V[k * 4 + 3];
   }
   int num = 0;
@@ -214,7 +244,7 @@ void e_to_rt(const double E[9], const double K[9], const std::vector<Pt>& p, std
   if (det3(Ra) < 0) for (double& x : Ra) x = -x;
   if (det3(Rb) < 0) for (double& x : Rb) x = -x;
   int best = 0;
-  std::vector<double> Xc;
+  std::vector<double> Xc, Xprev;
   double tb[3] = {t0[0], t0[1], t0[2]};  // the reference leaves t = +t0 and R, X empty when no candidate has an inlier
   std::memset(R, 0, sizeof(double) * 9);
   X.clear();
@@ -222,7 +252,8 @@ void e_to_rt(const double E[9], const double K[9], const std::vector<Pt>& p, std
     const double* Ri = (i < 2) ? Ra : Rb;
     const double sg = (i & 1) ? -1.0 : 1.0;
     const double ti[3] = {sg * t0[0], sg * t0[1], sg * t0[2]};
-    const int num = triangulate(p, K, Ri, ti, Xc);
+    const int num = (i & 1) ? triangulate(p, K, Ri, ti, Xc, &Xprev) : triangulate(p, K, Ri, ti, Xc);
+    if (!(i & 1)) Xprev = Xc;  // candidates come as (R, +t), (R, -t): the second is the mirror image of the first
     if (num > best) {
       best = num;
       X = Xc;
