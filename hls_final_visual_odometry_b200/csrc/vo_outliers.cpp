@@ -212,7 +212,7 @@ class SweepHull {
       }
       prev_[i] = e; hull_start_ = e;
       prev_[nxt] = i; next_[e] = i; next_[i] = nxt;
-      hash_[key(pi)] = i;
+      hash_[hk] = i;  // key(pi), computed above (center_ and hash_size_ do not change inside the loop)
       hash_[key(p_[e])] = e;
     }
   }
@@ -274,6 +274,13 @@ class SweepHull {
     }
   }
 
+  // add_triangle's three links: a new triangle's half-edges t, t+1, t+2 are appended in that order and their partners
+  // (a, b, c) are older edges or kNil, so link()'s case analysis reduces to "append, then point the partner back"
+  void link_new(int t, int partner) {
+    half_.push_back(partner);
+    if (partner != kNil) half_[partner] = t;
+  }
+
   void relink(int a, int b) {
     half_[a] = b;
     if (b != kNil) half_[b] = a;
@@ -282,7 +289,11 @@ class SweepHull {
   int add_triangle(int i0, int i1, int i2, int a, int b, int c) {  // src/delaunator.cpp:576-592
     const int t = (int)triangles.size();
     triangles.push_back(i0); triangles.push_back(i1); triangles.push_back(i2);
-    link(t, a); link(t + 1, b); link(t + 2, c);
+    if ((int)half_.size() == t && (a == kNil || a < t) && (b == kNil || b < t) && (c == kNil || c < t)) {
+      link_new(t, a); link_new(t + 1, b); link_new(t + 2, c);
+    } else {  // (never taken by run(); kept so that the function stays the reference's for any caller)
+      link(t, a); link(t + 1, b); link(t + 2, c);
+    }
     return t;
   }
 
